@@ -1,0 +1,192 @@
+"""Generate tests/golden/* by RUNNING THE REFERENCE'S OWN CODE (imported from
+/root/reference; nothing is copied) on seeded synthetic inputs.  TEST INFRASTRUCTURE.
+
+Run in the build container only (the reference tree does not exist on the GPU box):
+
+    python oracle/make_golden.py
+
+Adapters used, none of which edits reference source:
+  * wrappers are built with object.__new__ + attribute assignment, because their __init__
+    calls from_pretrained (network);
+  * transformers 5.x decoder layers return a bare tensor whereas the reference indexes
+    `layer(...)[0]`; a forward hook re-wraps the output in a tuple on the wrapper's model;
+  * Qwen2-0.5B/main.py does not parse as a module; its get_importance_order (lines 21-98)
+    is extracted with `ast` and executed on its own.
+"""
+from __future__ import annotations
+
+import ast
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference/Experiments"
+sys.path[:0] = [os.path.join(REF, "Pythia-70M"), os.path.join(REF, "Qwen2-0.5B"),
+                os.path.join(ROOT, "llm-inference-in-distributed-edge-networks_b200")]
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+import last_row_exp  # noqa: E402  (reference)
+import pythia_model  # noqa: E402  (reference)
+import qwen_layer_wise  # noqa: E402  (reference)
+from splitq import compat  # noqa: E402
+
+
+def qwen_get_importance_order():
+    src = open(os.path.join(REF, "Qwen2-0.5B", "main.py")).read().split('if __name__ == "__main__":')[0]
+    # keep only the function definition (module-level imports include a broken sibling import)
+    tree = ast.parse(src)
+    fn = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "get_importance_order"][0]
+    ns = {"torch": torch}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "qwen_main_extract", "exec"), ns)
+    return ns["get_importance_order"]
+
+
+def synth_attention(gen, L, H, S, tau):
+    """trained-like causal attention probabilities: softmax(N(0,1)*tau + causal mask)."""
+    maps = []
+    mask = torch.full((S, S), float("-inf")).triu(1)
+    for _ in range(L):
+        logits = torch.randn(1, H, S, S, generator=gen) * tau + mask
+        maps.append(torch.softmax(logits, dim=-1, dtype=torch.float32))
+    return maps
+
+
+def tuple_shim(model):
+    for layer in model.base_model.layers:
+        layer.register_forward_hook(lambda m, i, o: (o,) if torch.is_tensor(o) else o)
+
+
+def make_pythia_wrapper(model, ratios):
+    w = object.__new__(pythia_model.Pythia70Model)
+    w.model, w.device, w.tokenizer = model, "cpu", None
+    w.num_layers = len(model.base_model.layers)
+    w.gpt_neox = model.base_model
+    w.final_layer_norm = model.gpt_neox.final_layer_norm
+    w.rotary_emb = w.gpt_neox.rotary_emb
+    w.ratios = ratios
+    return w
+
+
+def make_qwen_wrapper(model):
+    w = object.__new__(qwen_layer_wise.QwenPointFiveBModel)
+    w.model, w.device, w.tokenizer = model, "cpu", None
+    w.num_layers = len(model.base_model.layers)
+    w.qwen = model.base_model
+    w.final_layer_norm = model.model.norm
+    w.rotary_emb = w.qwen.rotary_emb
+    return w
+
+
+def golden_importance():
+    gen = torch.Generator().manual_seed(1234)
+    qwen_gio = qwen_get_importance_order()
+    out = {}
+    for tag, (L, H, S, tau) in {"a": (3, 4, 64, 1.0), "b": (2, 7, 37, 3.0), "c": (2, 8, 128, 2.0)}.items():
+        maps = synth_attention(gen, L, H, S, tau)
+        hw = (torch.randn(L, H, generator=gen) * 0.3 + 0.07).tolist()
+        out[f"{tag}_A"] = torch.stack(maps).numpy()  # (L,1,H,S,S)
+        out[f"{tag}_head_w"] = np.asarray(hw, dtype=np.float64)
+        for method in ("regular_importance", "last_row", "aggregate_till"):
+            res = last_row_exp.get_importance_order(method, maps, L)
+            out[f"{tag}_{method}"] = torch.stack(res).numpy()
+            res_q = qwen_gio(method, maps, L, hw)
+            assert all(torch.equal(x, y) for x, y in zip(res, res_q))
+        out[f"{tag}_weighted_importance"] = torch.stack(qwen_gio("weighted_importance", maps, L, hw)).numpy()
+    for bad in (last_row_exp.get_importance_order, lambda m, a, n: qwen_gio(m, a, n, None)):
+        try:
+            bad("nope", [torch.zeros(1, 1, 2, 2)], 1)
+            raise AssertionError("reference accepted an unknown method")
+        except ValueError as e:
+            out["unknown_method_message"] = np.asarray(str(e))
+    np.savez_compressed(os.path.join(GOLD, "importance.npz"), **out)
+
+
+def capture_boundary(wrapper, layers, final_norm, ids, imp, ratio, loi):
+    """h right after layer `loi` (before the in-place quant) and what the next module sees."""
+    grabbed = {}
+    h1 = layers[loi].register_forward_hook(
+        lambda m, i, o: grabbed.__setitem__("pre", (o[0] if isinstance(o, tuple) else o).clone()))
+    nxt = layers[loi + 1] if loi + 1 < len(layers) else final_norm
+    h2 = nxt.register_forward_pre_hook(lambda m, a: grabbed.__setitem__("post", a[0].clone()))
+    nll = wrapper.activation_quantization(ids, ids.clone(), imp, ratio, loi)
+    h1.remove(), h2.remove()
+    return grabbed["pre"], grabbed["post"], nll
+
+
+def golden_wrappers():
+    gen = torch.Generator().manual_seed(4321)
+    fq = {}
+    nll_book = {}
+    specs = [
+        ("pythia_tiny", "gpt_neox", compat.PYTHIA_TINY, 48, [0, 1, 2]),
+        ("qwen_tiny", "qwen2", compat.QWEN2_TINY, 48, [0, 1, 2]),
+        ("pythia_70m", "gpt_neox", compat.PYTHIA_70M, 128, [2, 5]),
+        ("qwen2_05b", "qwen2", compat.QWEN2_05B, 64, [11]),
+    ]
+    ratios = [0, 0.25, 0.5, 0.75, 1]
+    for name, family, cfg, S, lois in specs:
+        model = compat.build_causal_lm(family, cfg, seed=0, attn_implementation="sdpa")
+        eager = compat.clone_with_attention(model, "eager")
+        tuple_shim(model)
+        wrapper = make_pythia_wrapper(model, ratios) if family == "gpt_neox" else make_qwen_wrapper(model)
+        final_norm = wrapper.final_layer_norm
+        layers = model.base_model.layers
+        ids = torch.randint(0, cfg["vocab_size"], (1, S), generator=gen)
+        with torch.no_grad():
+            att = eager(input_ids=ids, output_attentions=True).attentions
+            hf_loss = eager(input_ids=ids, labels=ids).loss.item()
+        L = len(layers)
+        book = {"S": S, "ids": ids[0].tolist(), "hf_loss": hf_loss, "nll": {}}
+        for method in ("regular_importance", "last_row"):
+            imp = last_row_exp.get_importance_order(method, att, L)
+            for loi in lois:
+                for ratio in ratios:
+                    pre, post, nll = capture_boundary(wrapper, layers, final_norm, ids, imp[loi], ratio, loi)
+                    book["nll"][f"{method}|{loi}|{ratio}"] = nll.item()
+                    if name.endswith("tiny") or (name == "pythia_70m" and loi == 2 and method == "regular_importance"):
+                        key = f"{name}|{method}|{loi}|{ratio}"
+                        fq[key + "|pre"] = pre[0].numpy()
+                        fq[key + "|post"] = post[0].numpy()
+                        fq[key + "|imp"] = imp[loi].numpy()
+        if family == "qwen2":
+            with torch.no_grad():
+                book["layer_by_layer_impl"] = wrapper.layer_by_layer_impl(ids, ids.clone()).item()
+        nll_book[name] = book
+        print(name, "hf_loss", hf_loss, "r0", book["nll"][f"regular_importance|{lois[0]}|0"], flush=True)
+        del model, eager, wrapper
+    # a degenerate block: every selected activation is zero -> reference divides 0/0
+    np.savez_compressed(os.path.join(GOLD, "fake_quant.npz"), **fq)
+    with open(os.path.join(GOLD, "wrapper_nll.json"), "w") as f:
+        json.dump(nll_book, f, indent=1)
+
+
+def golden_degenerate():
+    """The reference's unguarded 0/0: run its exact block on an all-zero selected set by driving
+    the tiny wrapper with zeroed embeddings is not possible without editing it, so record the
+    ATen facts the restatement relies on instead."""
+    x = torch.zeros(1, 3, 4)
+    m = torch.max(torch.abs(x))
+    scaled = torch.clamp(x / m * 7.0, -8.0, 7.0)
+    q = torch.round(scaled)
+    deq = q / 7.0 * m
+    facts = {
+        "zero_block_dequant_is_nan": bool(torch.isnan(deq).all()),
+        "round_half_even": torch.round(torch.tensor([0.5, 1.5, 2.5, -0.5, -1.5])).tolist(),
+        "argsort_ties_stable": torch.argsort(torch.tensor([1.0, 0.0, 1.0, 0.0, 0.0, 2.0]), stable=True).tolist(),
+        "int_ratio": [int(r * s) for r, s in [(0.25, 511), (0.75, 2047), (0.1, 30), (1, 77)]],
+    }
+    with open(os.path.join(GOLD, "aten_facts.json"), "w") as f:
+        json.dump(facts, f, indent=1)
+
+
+if __name__ == "__main__":
+    os.makedirs(GOLD, exist_ok=True)
+    torch.set_num_threads(8)
+    golden_importance()
+    golden_degenerate()
+    golden_wrappers()
+    print("golden fixtures written to", GOLD)
