@@ -1,0 +1,125 @@
+/*
+ * splitq.h -- C ABI of the B200 (sm_100a) split-inference boundary path.
+ *
+ * Drop-in boundary for sv-goat/LLM-Inference-in-Distributed-Edge-Networks.  The reference is
+ * pure Python/ATen and has no FFI; each entry point below names the reference lines whose
+ * work it replaces (paths relative to Experiments/ in the reference tree).  A maintainer
+ * binds these with ctypes; the shipped binding is
+ * llm-inference-in-distributed-edge-networks_b200/splitq/_native.py.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - the caller owns every buffer (inputs, outputs, payload, workspace); nothing here
+ *     allocates, frees or synchronises; work is enqueued on `stream` (a cudaStream_t);
+ *   - functions return SPLITQ_OK or a negative SPLITQ_ERR_* code and record a message that
+ *     splitq_last_error() returns (thread-local); no C++ exception crosses this boundary;
+ *   - tensors are dense, row-major, fp32; batch B = number of evaluation windows processed
+ *     by one call (the reference always has B = 1, last_row_exp.py:20).
+ *
+ * Payload ("SPQ1", little-endian, one per window; windows of a batch are `payload_stride`
+ * bytes apart; every section starts on a 16-byte boundary):
+ *   [0,32)   u32 magic 'SPQ1', u32 scale_mode, u32 S, u32 D, u32 n_scales, u32 codes_offset,
+ *            u32 payload_bytes, u32 0
+ *   bits     u8[S]   per-token width: 2, 4, 8 or 32 (= raw fp32 row)
+ *   row_off  u32[S]  row start, in 16-byte units from codes_offset
+ *   scales   f32[n_scales]  group mode: 4 slots (8-bit, 4-bit, 2-bit, unused); token mode: S
+ *   codes    rows in ascending token order; a b-bit row holds D two's-complement fields,
+ *            element e at bit e*b (LSB first), padded to 16 bytes; a raw row is D floats.
+ */
+#ifndef SPLITQ_H_
+#define SPLITQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPLITQ_OK 0
+#define SPLITQ_ERR_ARG (-1)       /* bad shape / null pointer / unsupported size */
+#define SPLITQ_ERR_ALIGN (-2)     /* pointer or stride not aligned as documented */
+#define SPLITQ_ERR_WORKSPACE (-3) /* workspace or payload buffer too small */
+#define SPLITQ_ERR_ARCH (-4)      /* current device is not compute capability 10.x */
+#define SPLITQ_ERR_CUDA (-5)      /* a CUDA runtime call failed; see splitq_last_error() */
+
+#define SPLITQ_MAGIC 0x31515053u
+#define SPLITQ_HEADER_BYTES 32
+#define SPLITQ_SCALE_GROUP 0 /* one absmax per width class (reference: one per selected set) */
+#define SPLITQ_SCALE_TOKEN 1 /* one absmax per token (extension) */
+#define SPLITQ_BITS_RAW 32
+#define SPLITQ_MAX_LADDER 3
+#define SPLITQ_MAX_HEADS 128
+#define SPLITQ_MAX_SELECT_S 32768
+#define SPLITQ_NORM_LAYERNORM 0
+#define SPLITQ_NORM_RMSNORM 1
+#define SPLITQ_FLAG_CAUSAL_HINT 1u /* caller guarantees A[i][j] == 0 for j > i (HF causal eager) */
+
+typedef void* splitq_stream_t; /* cudaStream_t */
+
+int splitq_version(void);
+const char* splitq_last_error(void);
+
+/* ---- importance over materialised attention (K1) ---------------------------------------
+ * Replaces get_importance_order's per-layer reductions: "regular_importance"
+ * (Pythia-70M/last_row_exp.py:13-23, Qwen2-0.5B/main.py:46-56), "weighted_importance"
+ * (Qwen2-0.5B/main.py:57-78) and "last_row" (last_row_exp.py:24-30, main.py:80-86).
+ *   A        (B,H,Sq,Sk) attention probabilities
+ *   head_w_host  H host floats or NULL (NULL = 1/H each, i.e. the plain head mean)
+ *   out_col  (B,Sk)  (1/Sq) sum_i sum_h w_h A[b,h,i,j]   or NULL
+ *   out_last (B,Sk)  sum_h w_h A[b,h,Sq-1,j]              or NULL
+ *   ws       scratch of splitq_importance_colmean_workspace_bytes(); contents undefined after */
+size_t splitq_importance_colmean_workspace_bytes(int B, int H, int Sq, int Sk);
+int splitq_importance_colmean(const float* A, int B, int H, int Sq, int Sk, const float* head_w_host,
+                              float* out_col, float* out_last, void* ws, size_t ws_bytes,
+                              unsigned flags, splitq_stream_t stream);
+
+/* ---- selection (K3a) -------------------------------------------------------------------
+ * Replaces torch.argsort(importance)[:int(ratio*S)] (Pythia-70M/pythia_model.py:169-170,
+ * Qwen2-0.5B/qwen_layer_wise.py:57), generalised to a ladder: the ladder_k_host[0] least
+ * important tokens get ladder_bits_host[0] bits, the next ladder_k_host[1] get
+ * ladder_bits_host[1], ...; all others stay fp32.  Ties go to the lower token index.
+ *   imp (B,S); bits_out u8 (B,S); row_off_out u32 (B,S) in 16-byte units.  S <= 32768. */
+int splitq_select_bits(const float* imp, int B, int S, int D, const int* ladder_k_host,
+                       const int* ladder_bits_host, int n_ladder, uint8_t* bits_out,
+                       uint32_t* row_off_out, splitq_stream_t stream);
+
+/* ---- absmax + quantise + bit-pack (K3) -------------------------------------------------
+ * Replaces the scale/clamp/round block (pythia_model.py:176-184, qwen_layer_wise.py:60-66)
+ * and emits what the reference never materialises: integer codes packed into one payload.
+ * Codes are round_half_even(clamp(h / m * L, -(L+1), L)), L = 2^(bits-1) - 1, with IEEE
+ * division and no contraction, so they are bit-identical to the ATen sequence. */
+size_t splitq_payload_bytes(int S, int D, const int* ladder_k_host, const int* ladder_bits_host,
+                            int n_ladder, int scale_mode);
+size_t splitq_quant_pack_workspace_bytes(int B, int S, int D, int scale_mode);
+int splitq_quant_pack(const float* h, int B, int S, int D, const uint8_t* bits,
+                      const uint32_t* row_off, int scale_mode, uint8_t* payload,
+                      size_t payload_stride, void* ws, size_t ws_bytes, splitq_stream_t stream);
+
+/* ---- dequantise (K4) -------------------------------------------------------------------
+ * Replaces quantized/7*max + index_put (pythia_model.py:186-188, qwen_layer_wise.py:68-70):
+ * h_out (B,S,D) = every token of the window, raw rows copied, coded rows as (q / L) * m.
+ * Group mode with a zero class scale yields NaN rows, as the reference's 0/0 does. */
+int splitq_dequant(const uint8_t* payload, size_t payload_stride, int B, int S, int D,
+                   float* h_out, splitq_stream_t stream);
+
+/* Same, fused with the first normalisation of the downstream half (the input_layernorm of
+ * layer i+1, or the final norm when the split is after the last layer; reached through
+ * pythia_model.py:165,193 / qwen_layer_wise.py:52,75).  Emits the fp32 residual stream and
+ * the normalised activations; gamma2/beta2/normed2_out (nullable) give the second LayerNorm
+ * GPT-NeoX's parallel-residual layer applies to the same input. */
+int splitq_dequant_norm(const uint8_t* payload, size_t payload_stride, int B, int S, int D,
+                        int norm_kind, const float* gamma, const float* beta, float eps,
+                        const float* gamma2, const float* beta2, float* resid_out,
+                        float* normed_out, float* normed2_out, splitq_stream_t stream);
+
+/* ---- transfer --------------------------------------------------------------------------
+ * The device hop the reference only simulates (in-place quant->dequant,
+ * pythia_model.py:176-188).  cudaMemcpyPeerAsync over NVLink; src/dst may be one device. */
+int splitq_transfer_peer(void* dst, int dst_device, const void* src, int src_device, size_t bytes,
+                         splitq_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLITQ_H_ */

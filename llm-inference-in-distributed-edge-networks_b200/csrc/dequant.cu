@@ -1,0 +1,284 @@
+// K4: dequantise the boundary payload, optionally fused with the downstream half's first norm.
+//
+// Reference: `quantized_values / 7 * max_val` scattered back with index_put
+// (Experiments/Pythia-70M/pythia_model.py:186-188, Experiments/Qwen2-0.5B/qwen_layer_wise.py:68-70),
+// after which the next decoder layer immediately re-reads the tensor to normalise it
+// (input_layernorm / final norm, reached through pythia_model.py:165,193 and
+// qwen_layer_wise.py:52,75).  Here one warp owns one token: it reads the packed row once,
+// rebuilds the fp32 row in registers as (q / L) * m (IEEE division and multiplication, same
+// order as ATen, so the values are bit-identical), writes the residual stream, and -- in the
+// fused variants -- computes LayerNorm / RMSNorm statistics with warp shuffles and writes the
+// normalised activations without a second trip to HBM.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace splitq {
+
+constexpr int kDWarps = 8;
+enum { MODE_PLAIN = 0, MODE_LAYERNORM = 1, MODE_RMSNORM = 2 };
+
+struct NormArgs {
+    const float* gamma;
+    const float* beta;
+    const float* gamma2;
+    const float* beta2;
+    float eps;
+    float* normed;
+    float* normed2;
+};
+
+__device__ __forceinline__ float decode_field(uint32_t w, int i, int nb, float L, float m) {
+    const int q = (int)(w << (32 - nb * (i + 1))) >> (32 - nb);  // sign-extend field i
+    return __fmul_rn(__fdiv_rn((float)q, L), m);
+}
+
+struct RowInfo {
+    int nb;
+    float m, L;
+    bool nan_row, bad;
+    const uint8_t* src;
+};
+
+__device__ __forceinline__ RowInfo row_info(const uint8_t* P, int S, int D, int t) {
+    RowInfo r;
+    const uint32_t* hdr = reinterpret_cast<const uint32_t*>(P);
+    const int mode = (int)hdr[1];
+    r.bad = hdr[0] != SPLITQ_MAGIC || hdr[2] != (uint32_t)S || hdr[3] != (uint32_t)D ||
+            (mode != SPLITQ_SCALE_GROUP && mode != SPLITQ_SCALE_TOKEN);
+    const PayloadLayout lay = payload_layout((uint32_t)S, mode == SPLITQ_SCALE_TOKEN ? SPLITQ_SCALE_TOKEN : SPLITQ_SCALE_GROUP);
+    r.nb = P[lay.bits_off + t];
+    const uint32_t off16 = reinterpret_cast<const uint32_t*>(P + lay.rowoff_off)[t];
+    r.src = P + lay.codes_off + (size_t)off16 * 16u;
+    r.m = 0.f;
+    r.L = 1.f;
+    r.nan_row = false;
+    if (r.nb != SPLITQ_BITS_RAW) {
+        if (r.nb != 2 && r.nb != 4 && r.nb != 8) {
+            r.bad = true;
+            r.nb = 8;
+        }
+        const float* scales = reinterpret_cast<const float*>(P + lay.scales_off);
+        r.m = mode == SPLITQ_SCALE_GROUP ? scales[slot_of_bits(r.nb)] : scales[t];
+        r.L = (float)((1 << (r.nb - 1)) - 1);
+        // reference semantics: one scale for the set, all zeros -> 0/0 -> NaN rows
+        r.nan_row = mode == SPLITQ_SCALE_GROUP && r.m == 0.f;
+    }
+    return r;
+}
+
+template <int MAXCH, int MODE>
+__global__ void __launch_bounds__(kDWarps * 32)
+dequant_kernel(const uint8_t* __restrict__ payload, size_t stride, int S, int D, float* __restrict__ h_out,
+               NormArgs na) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * kDWarps + warp;
+    const int b = blockIdx.y;
+    if (t >= S) return;
+    const uint8_t* P = payload + (size_t)b * stride;
+    const RowInfo r = row_info(P, S, D, t);
+    const int nch = D >> 2;
+    const size_t tok = (size_t)b * S + t;
+    const float qnan = __uint_as_float(0x7fc00000u);
+
+    float4 v[MAXCH];
+    if (r.bad) {
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) v[u] = make_float4(qnan, qnan, qnan, qnan);
+    } else if (r.nb == SPLITQ_BITS_RAW) {
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            v[u] = c < nch ? ld_stream_f4(reinterpret_cast<const float4*>(r.src) + c)
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    } else {
+        uint32_t w[MAXCH];
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            w[u] = 0u;
+            if (c < nch) {
+                if (r.nb == 8) w[u] = __ldg(reinterpret_cast<const uint32_t*>(r.src) + c);
+                else if (r.nb == 4) w[u] = __ldg(reinterpret_cast<const uint16_t*>(r.src) + c);
+                else w[u] = __ldg(r.src + c);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            v[u].x = decode_field(w[u], 0, r.nb, r.L, r.m);
+            v[u].y = decode_field(w[u], 1, r.nb, r.L, r.m);
+            v[u].z = decode_field(w[u], 2, r.nb, r.L, r.m);
+            v[u].w = decode_field(w[u], 3, r.nb, r.L, r.m);
+            if (r.nan_row) v[u] = make_float4(qnan, qnan, qnan, qnan);
+        }
+    }
+
+    if (h_out) {
+        float4* dst = reinterpret_cast<float4*>(h_out + tok * D);
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            if (c < nch) dst[c] = v[u];
+        }
+    }
+    if (MODE == MODE_PLAIN) return;
+
+    const float invD = 1.0f / (float)D;
+    float mean = 0.f;
+    if (MODE == MODE_LAYERNORM) {
+        float s = 0.f;
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u)
+            if (lane + 32 * u < nch) s += (v[u].x + v[u].y) + (v[u].z + v[u].w);
+        mean = warp_sum(s) * invD;
+    }
+    float ss = 0.f;
+#pragma unroll
+    for (int u = 0; u < MAXCH; ++u) {
+        if (lane + 32 * u < nch) {
+            const float a = v[u].x - mean, bb = v[u].y - mean, cc = v[u].z - mean, d = v[u].w - mean;
+            ss += (a * a + bb * bb) + (cc * cc + d * d);
+        }
+    }
+    const float var = warp_sum(ss) * invD;
+    const float rstd = 1.0f / sqrtf(var + na.eps);
+
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass) {
+        const float* gamma = pass == 0 ? na.gamma : na.gamma2;
+        const float* beta = pass == 0 ? na.beta : na.beta2;
+        float* out = pass == 0 ? na.normed : na.normed2;
+        if (!out) continue;
+        float4* dst = reinterpret_cast<float4*>(out + tok * D);
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            if (c < nch) {
+                const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + c);
+                float4 o;
+                if (MODE == MODE_LAYERNORM) {
+                    const float4 be = beta ? __ldg(reinterpret_cast<const float4*>(beta) + c)
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+                    o.x = (v[u].x - mean) * rstd * g.x + be.x;
+                    o.y = (v[u].y - mean) * rstd * g.y + be.y;
+                    o.z = (v[u].z - mean) * rstd * g.z + be.z;
+                    o.w = (v[u].w - mean) * rstd * g.w + be.w;
+                } else {
+                    o.x = g.x * (v[u].x * rstd);
+                    o.y = g.y * (v[u].y * rstd);
+                    o.z = g.z * (v[u].z * rstd);
+                    o.w = g.w * (v[u].w * rstd);
+                }
+                dst[c] = o;
+            }
+        }
+    }
+}
+
+// any D / unaligned outputs: scalar accesses, row re-decoded per use (stays in L1)
+template <int MODE>
+__global__ void __launch_bounds__(kDWarps * 32)
+dequant_generic_kernel(const uint8_t* __restrict__ payload, size_t stride, int S, int D,
+                       float* __restrict__ h_out, NormArgs na) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * kDWarps + warp;
+    const int b = blockIdx.y;
+    if (t >= S) return;
+    const uint8_t* P = payload + (size_t)b * stride;
+    const RowInfo r = row_info(P, S, D, t);
+    const size_t tok = (size_t)b * S + t;
+    const float qnan = __uint_as_float(0x7fc00000u);
+    auto value = [&](int d) -> float {
+        if (r.bad || r.nan_row) return qnan;
+        if (r.nb == SPLITQ_BITS_RAW) return reinterpret_cast<const float*>(r.src)[d];
+        const int per = 8 / r.nb;
+        const uint32_t byte = r.src[d / per];
+        return decode_field(byte, d % per, r.nb, r.L, r.m);
+    };
+    if (h_out)
+        for (int d = lane; d < D; d += 32) h_out[tok * D + d] = value(d);
+    if (MODE == MODE_PLAIN) return;
+    const float invD = 1.0f / (float)D;
+    float mean = 0.f;
+    if (MODE == MODE_LAYERNORM) {
+        float s = 0.f;
+        for (int d = lane; d < D; d += 32) s += value(d);
+        mean = warp_sum(s) * invD;
+    }
+    float ss = 0.f;
+    for (int d = lane; d < D; d += 32) {
+        const float a = value(d) - mean;
+        ss += a * a;
+    }
+    const float rstd = 1.0f / sqrtf(warp_sum(ss) * invD + na.eps);
+    for (int pass = 0; pass < 2; ++pass) {
+        const float* gamma = pass == 0 ? na.gamma : na.gamma2;
+        const float* beta = pass == 0 ? na.beta : na.beta2;
+        float* out = pass == 0 ? na.normed : na.normed2;
+        if (!out) continue;
+        for (int d = lane; d < D; d += 32) {
+            const float x = value(d);
+            out[tok * D + d] = MODE == MODE_LAYERNORM ? (x - mean) * rstd * gamma[d] + (beta ? beta[d] : 0.f)
+                                                      : gamma[d] * (x * rstd);
+        }
+    }
+}
+
+template <int MODE>
+static int launch_dequant(const uint8_t* payload, size_t stride, int B, int S, int D, float* h_out,
+                          const NormArgs& na, bool vec, cudaStream_t st) {
+    dim3 grid(cdiv(S, kDWarps), B);
+    if (!vec) {
+        dequant_generic_kernel<MODE><<<grid, kDWarps * 32, 0, st>>>(payload, stride, S, D, h_out, na);
+    } else {
+        const int nch = D / 4;
+        if (nch <= 32 * 4) dequant_kernel<4, MODE><<<grid, kDWarps * 32, 0, st>>>(payload, stride, S, D, h_out, na);
+        else if (nch <= 32 * 8) dequant_kernel<8, MODE><<<grid, kDWarps * 32, 0, st>>>(payload, stride, S, D, h_out, na);
+        else if (nch <= 32 * 16) dequant_kernel<16, MODE><<<grid, kDWarps * 32, 0, st>>>(payload, stride, S, D, h_out, na);
+        else dequant_kernel<32, MODE><<<grid, kDWarps * 32, 0, st>>>(payload, stride, S, D, h_out, na);
+    }
+    SPLITQ_LAUNCH_CHECK("dequant_kernel");
+    return SPLITQ_OK;
+}
+
+static int check_payload_args(const char* who, const uint8_t* payload, size_t stride, int B, int S, int D) {
+    SPLITQ_REQUIRE(payload, SPLITQ_ERR_ARG, "%s: NULL payload", who);
+    SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0 && B <= 65535, SPLITQ_ERR_ARG, "%s: bad shape B=%d S=%d D=%d", who,
+                   B, S, D);
+    SPLITQ_REQUIRE(aligned16(payload) && stride % 16 == 0, SPLITQ_ERR_ALIGN,
+                   "%s: payload and payload_stride must be 16-byte aligned", who);
+    return check_arch();
+}
+
+}  // namespace splitq
+
+using namespace splitq;
+
+extern "C" int splitq_dequant(const uint8_t* payload, size_t payload_stride, int B, int S, int D,
+                              float* h_out, splitq_stream_t stream) {
+    if (int rc = check_payload_args("dequant", payload, payload_stride, B, S, D)) return rc;
+    SPLITQ_REQUIRE(h_out, SPLITQ_ERR_ARG, "dequant: NULL output");
+    NormArgs na = {};
+    const bool vec = (D % 4 == 0) && D <= 4096 && aligned16(h_out);
+    return launch_dequant<MODE_PLAIN>(payload, payload_stride, B, S, D, h_out, na, vec, (cudaStream_t)stream);
+}
+
+extern "C" int splitq_dequant_norm(const uint8_t* payload, size_t payload_stride, int B, int S, int D,
+                                   int norm_kind, const float* gamma, const float* beta, float eps,
+                                   const float* gamma2, const float* beta2, float* resid_out,
+                                   float* normed_out, float* normed2_out, splitq_stream_t stream) {
+    if (int rc = check_payload_args("dequant_norm", payload, payload_stride, B, S, D)) return rc;
+    SPLITQ_REQUIRE(norm_kind == SPLITQ_NORM_LAYERNORM || norm_kind == SPLITQ_NORM_RMSNORM, SPLITQ_ERR_ARG,
+                   "dequant_norm: unknown norm_kind %d", norm_kind);
+    SPLITQ_REQUIRE(gamma && normed_out, SPLITQ_ERR_ARG, "dequant_norm: gamma / normed_out are NULL");
+    SPLITQ_REQUIRE(!normed2_out || gamma2, SPLITQ_ERR_ARG, "dequant_norm: normed2_out given without gamma2");
+    NormArgs na = {gamma, beta, gamma2, beta2, eps, normed_out, normed2_out};
+    const bool vec = (D % 4 == 0) && D <= 4096 && aligned16(normed_out) && aligned16(gamma) &&
+                     (!resid_out || aligned16(resid_out)) && (!beta || aligned16(beta)) &&
+                     (!normed2_out || (aligned16(normed2_out) && aligned16(gamma2) && (!beta2 || aligned16(beta2))));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (norm_kind == SPLITQ_NORM_LAYERNORM)
+        return launch_dequant<MODE_LAYERNORM>(payload, payload_stride, B, S, D, resid_out, na, vec, st);
+    return launch_dequant<MODE_RMSNORM>(payload, payload_stride, B, S, D, resid_out, na, vec, st);
+}

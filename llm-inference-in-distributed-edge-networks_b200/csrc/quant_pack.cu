@@ -1,0 +1,304 @@
+// K3: absmax scale, quantise, bit-pack the split-layer hidden states into the boundary payload.
+//
+// Reference: the fake-quant block of activation_quantization
+// (Experiments/Pythia-70M/pythia_model.py:176-184, Experiments/Qwen2-0.5B/qwen_layer_wise.py:60-66):
+//     m = max|h[:, idx, :]|;  q = round(clamp(h / m * 7, -8, 7))
+// run there as gather + 5 elementwise ATen kernels and never stored as integers.  Here one warp
+// owns one token row: the row is read once with 128-bit streaming loads and kept in registers,
+// absmax is a single integer warp reduction on the |x| bit patterns, codes are produced with
+// IEEE division / multiplication (no reciprocal, no FMA contraction) so they equal the ATen
+// result bit for bit, and fields are packed in registers and stored straight into the payload.
+// The reference's single scale for the whole selected set ("group" mode) needs the class maximum
+// before any code can be emitted, hence a small first phase over the selected rows only.
+#include "common.cuh"
+
+namespace splitq {
+
+constexpr int kQWarps = 8;
+
+__device__ __forceinline__ int code_of(float x, float m, float L, float lo) {
+    // (x / m) * L with round-to-nearest at each step == ATen `x / m * L`
+    float s = __fmul_rn(__fdiv_rn(x, m), L);
+    // 0/0 (all-zero set): ATen propagates NaN through clamp/round; an integer field cannot, store 0
+    if (!(s == s)) return 0;
+    s = fminf(fmaxf(s, lo), L);
+    return (int)rintf(s);  // round half to even, like torch.round
+}
+
+__device__ __forceinline__ uint32_t pack4(float4 v, float m, float L, float lo, int nb) {
+    const uint32_t mask = (1u << nb) - 1u;
+    const uint32_t q0 = (uint32_t)code_of(v.x, m, L, lo) & mask;
+    const uint32_t q1 = (uint32_t)code_of(v.y, m, L, lo) & mask;
+    const uint32_t q2 = (uint32_t)code_of(v.z, m, L, lo) & mask;
+    const uint32_t q3 = (uint32_t)code_of(v.w, m, L, lo) & mask;
+    return q0 | (q1 << nb) | (q2 << (2 * nb)) | (q3 << (3 * nb));
+}
+
+// Window index written by the warp that owns token 0: header words (all but the total size, which
+// only the owner of the last token knows), zeroed section padding, and the group-scale slots.
+template <bool GROUP>
+__device__ __forceinline__ void write_window_index(uint8_t* P, int S, int D, const PayloadLayout& lay,
+                                                   const uint32_t* class_max_w, int lane) {
+    if (lane < 8 && lane != 6) {
+        uint32_t w = 0;
+        switch (lane) {
+            case 0: w = SPLITQ_MAGIC; break;
+            case 1: w = GROUP ? SPLITQ_SCALE_GROUP : SPLITQ_SCALE_TOKEN; break;
+            case 2: w = (uint32_t)S; break;
+            case 3: w = (uint32_t)D; break;
+            case 4: w = lay.n_scales; break;
+            case 5: w = lay.codes_off; break;
+            default: w = 0; break;
+        }
+        reinterpret_cast<uint32_t*>(P)[lane] = w;
+    }
+    for (uint32_t i = (uint32_t)S + lane; i < pad16((uint32_t)S); i += 32) P[lay.bits_off + i] = 0;
+    for (uint32_t i = 4u * S + lane; i < pad16(4u * S); i += 32) P[lay.rowoff_off + i] = 0;
+    if (GROUP) {
+        if (lane < 4) reinterpret_cast<float*>(P + lay.scales_off)[lane] = __uint_as_float(class_max_w[lane]);
+    } else {
+        for (uint32_t i = 4u * S + lane; i < pad16(4u * S); i += 32) P[lay.scales_off + i] = 0;
+    }
+}
+
+// ---- phase 1 of group mode: absmax per width class over the selected rows ---------------------
+template <bool VEC>
+__global__ void __launch_bounds__(kQWarps * 32)
+class_absmax_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
+                    uint32_t* __restrict__ class_max /* (B,4) |x| bit patterns, pre-zeroed */) {
+    __shared__ uint32_t smax[4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.y;
+    if (threadIdx.x < 4) smax[threadIdx.x] = 0u;
+    __syncthreads();
+    const int t0 = blockIdx.x * (kQWarps * 4);
+    for (int q = 0; q < 4; ++q) {
+        const int t = t0 + q * kQWarps + warp;
+        if (t >= S) break;
+        const int nb = bits[(size_t)b * S + t];
+        if (nb == SPLITQ_BITS_RAW) continue;
+        const float* row = h + ((size_t)b * S + t) * D;
+        uint32_t mx = 0u;
+        if (VEC) {
+            const float4* src = reinterpret_cast<const float4*>(row);
+            for (int c = lane; c < D / 4; c += 32) {
+                float4 v = __ldg(src + c);  // stays in L2 for phase 2
+                mx = max(mx, __float_as_uint(v.x) & 0x7fffffffu);
+                mx = max(mx, __float_as_uint(v.y) & 0x7fffffffu);
+                mx = max(mx, __float_as_uint(v.z) & 0x7fffffffu);
+                mx = max(mx, __float_as_uint(v.w) & 0x7fffffffu);
+            }
+        } else {
+            for (int d = lane; d < D; d += 32) mx = max(mx, __float_as_uint(__ldg(row + d)) & 0x7fffffffu);
+        }
+        mx = __reduce_max_sync(0xffffffffu, mx);
+        if (lane == 0) atomicMax(&smax[slot_of_bits(nb)], mx);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 && smax[threadIdx.x] != 0u) atomicMax(&class_max[b * 4 + threadIdx.x], smax[threadIdx.x]);
+}
+
+// ---- main kernel: one warp per token, row resident in registers -------------------------------
+template <int MAXCH, bool GROUP>
+__global__ void __launch_bounds__(kQWarps * 32)
+quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
+                  const uint32_t* __restrict__ row_off, uint8_t* __restrict__ payload, size_t stride,
+                  const uint32_t* __restrict__ class_max) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * kQWarps + warp;
+    const int b = blockIdx.y;
+    if (t >= S) return;
+    const size_t tok = (size_t)b * S + t;
+    const PayloadLayout lay = payload_layout((uint32_t)S, GROUP ? SPLITQ_SCALE_GROUP : SPLITQ_SCALE_TOKEN);
+    uint8_t* P = payload + (size_t)b * stride;
+    const int nb = bits[tok];
+    const uint32_t off16 = row_off[tok];
+    const int nch = D >> 2;
+
+    const float4* src = reinterpret_cast<const float4*>(h + tok * D);
+    float4 v[MAXCH];
+#pragma unroll
+    for (int u = 0; u < MAXCH; ++u) {
+        const int c = lane + 32 * u;
+        v[u] = c < nch ? ld_stream_f4(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+
+    float* scales = reinterpret_cast<float*>(P + lay.scales_off);
+    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane);
+    if (lane == 0) {
+        P[lay.bits_off + t] = (uint8_t)nb;
+        reinterpret_cast<uint32_t*>(P + lay.rowoff_off)[t] = off16;
+        if (t == S - 1)  // total payload size = end of the last row
+            reinterpret_cast<uint32_t*>(P)[6] = lay.codes_off + 16u * off16 + row_bytes((uint32_t)D, (uint32_t)nb);
+    }
+    uint8_t* dst = P + lay.codes_off + (size_t)off16 * 16u;
+
+    if (nb == SPLITQ_BITS_RAW) {
+        if (!GROUP && lane == 0) scales[t] = 0.f;
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            if (c < nch) reinterpret_cast<float4*>(dst)[c] = v[u];
+        }
+        return;
+    }
+
+    float m;
+    if (GROUP) {
+        m = __uint_as_float(class_max[b * 4 + slot_of_bits(nb)]);
+    } else {
+        uint32_t mx = 0u;
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            mx = max(mx, __float_as_uint(v[u].x) & 0x7fffffffu);
+            mx = max(mx, __float_as_uint(v[u].y) & 0x7fffffffu);
+            mx = max(mx, __float_as_uint(v[u].z) & 0x7fffffffu);
+            mx = max(mx, __float_as_uint(v[u].w) & 0x7fffffffu);
+        }
+        m = __uint_as_float(__reduce_max_sync(0xffffffffu, mx));
+        if (lane == 0) scales[t] = m;
+    }
+    const float L = (float)((1 << (nb - 1)) - 1);
+    const float lo = -(L + 1.f);
+    const uint32_t rb = row_bytes((uint32_t)D, (uint32_t)nb);
+    // chunk c (4 elements) occupies nb/2 bytes at byte c*nb/2; chunks past D pad the row with zeros
+#pragma unroll
+    for (int u = 0; u < MAXCH; ++u) {
+        const int c = lane + 32 * u;
+        const uint32_t byte = (uint32_t)c * (uint32_t)nb >> 1;
+        if (byte < rb) {
+            const uint32_t w = pack4(v[u], m, L, lo, nb);
+            if (nb == 8) reinterpret_cast<uint32_t*>(dst)[c] = w;
+            else if (nb == 4) reinterpret_cast<uint16_t*>(dst)[c] = (uint16_t)w;
+            else dst[c] = (uint8_t)w;
+        }
+    }
+    // rows wider than the register tile never reach here (dispatch guarantees nch <= 32*MAXCH);
+    // padding beyond 32*MAXCH chunks cannot exist because rb <= pad16(nch*nb/2) < (nch+32)*nb/2
+}
+
+// ---- generic path: any D / unaligned rows; one warp per token, scalar accesses ----------------
+template <bool GROUP>
+__global__ void __launch_bounds__(kQWarps * 32)
+quant_pack_generic_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
+                          const uint32_t* __restrict__ row_off, uint8_t* __restrict__ payload,
+                          size_t stride, const uint32_t* __restrict__ class_max) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * kQWarps + warp;
+    const int b = blockIdx.y;
+    if (t >= S) return;
+    const size_t tok = (size_t)b * S + t;
+    const PayloadLayout lay = payload_layout((uint32_t)S, GROUP ? SPLITQ_SCALE_GROUP : SPLITQ_SCALE_TOKEN);
+    uint8_t* P = payload + (size_t)b * stride;
+    const int nb = bits[tok];
+    const uint32_t off16 = row_off[tok];
+    const float* row = h + tok * D;
+    float* scales = reinterpret_cast<float*>(P + lay.scales_off);
+    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane);
+    if (lane == 0) {
+        P[lay.bits_off + t] = (uint8_t)nb;
+        reinterpret_cast<uint32_t*>(P + lay.rowoff_off)[t] = off16;
+        if (t == S - 1)  // total payload size = end of the last row
+            reinterpret_cast<uint32_t*>(P)[6] = lay.codes_off + 16u * off16 + row_bytes((uint32_t)D, (uint32_t)nb);
+    }
+    uint8_t* dst = P + lay.codes_off + (size_t)off16 * 16u;
+    const uint32_t rb = row_bytes((uint32_t)D, (uint32_t)nb);
+    if (nb == SPLITQ_BITS_RAW) {
+        if (!GROUP && lane == 0) scales[t] = 0.f;
+        for (uint32_t d = lane; d < rb / 4; d += 32)
+            reinterpret_cast<float*>(dst)[d] = d < (uint32_t)D ? __ldg(row + d) : 0.f;
+        return;
+    }
+    float m;
+    if (GROUP) {
+        m = __uint_as_float(class_max[b * 4 + slot_of_bits(nb)]);
+    } else {
+        uint32_t mx = 0u;
+        for (int d = lane; d < D; d += 32) mx = max(mx, __float_as_uint(__ldg(row + d)) & 0x7fffffffu);
+        m = __uint_as_float(__reduce_max_sync(0xffffffffu, mx));
+        if (lane == 0) scales[t] = m;
+    }
+    const float L = (float)((1 << (nb - 1)) - 1);
+    const float lo = -(L + 1.f);
+    const int per = 8 / nb;
+    const uint32_t mask = (1u << nb) - 1u;
+    for (uint32_t y = lane; y < rb; y += 32) {
+        uint32_t byte = 0u;
+        for (int i = 0; i < per; ++i) {
+            const uint32_t e = y * per + i;
+            if (e < (uint32_t)D) byte |= ((uint32_t)code_of(__ldg(row + e), m, L, lo) & mask) << (nb * i);
+        }
+        dst[y] = (uint8_t)byte;
+    }
+}
+
+}  // namespace splitq
+
+using namespace splitq;
+
+extern "C" size_t splitq_quant_pack_workspace_bytes(int B, int S, int D, int scale_mode) {
+    (void)S; (void)D;
+    if (B <= 0) return 0;
+    return scale_mode == SPLITQ_SCALE_GROUP ? (size_t)B * 4 * sizeof(uint32_t) : 0;
+}
+
+extern "C" int splitq_quant_pack(const float* h, int B, int S, int D, const uint8_t* bits,
+                                 const uint32_t* row_off, int scale_mode, uint8_t* payload,
+                                 size_t payload_stride, void* ws, size_t ws_bytes,
+                                 splitq_stream_t stream) {
+    SPLITQ_REQUIRE(h && bits && row_off && payload, SPLITQ_ERR_ARG, "quant_pack: NULL buffer");
+    SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0, SPLITQ_ERR_ARG, "quant_pack: bad shape B=%d S=%d D=%d", B, S, D);
+    SPLITQ_REQUIRE(B <= 65535, SPLITQ_ERR_ARG, "quant_pack: B=%d > 65535", B);
+    SPLITQ_REQUIRE(scale_mode == SPLITQ_SCALE_GROUP || scale_mode == SPLITQ_SCALE_TOKEN, SPLITQ_ERR_ARG,
+                   "quant_pack: unknown scale_mode %d", scale_mode);
+    SPLITQ_REQUIRE(aligned16(payload) && payload_stride % 16 == 0, SPLITQ_ERR_ALIGN,
+                   "quant_pack: payload and payload_stride must be 16-byte aligned");
+    // the payload cannot be larger than an all-raw window; the caller sizes it with
+    // splitq_payload_bytes(), we can only bound-check the stride against the smallest legal size
+    const PayloadLayout lay = payload_layout((uint32_t)S, scale_mode);
+    SPLITQ_REQUIRE(B == 1 || payload_stride >= lay.codes_off, SPLITQ_ERR_WORKSPACE,
+                   "quant_pack: payload_stride %zu smaller than the payload index (%u)", payload_stride,
+                   lay.codes_off);
+    if (int rc = check_arch()) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool group = scale_mode == SPLITQ_SCALE_GROUP;
+    const bool vec = (D % 4 == 0) && aligned16(h) && D <= 4096;
+    uint32_t* class_max = nullptr;
+    if (group) {
+        const size_t need = (size_t)B * 4 * sizeof(uint32_t);
+        SPLITQ_REQUIRE(ws && ws_bytes >= need, SPLITQ_ERR_WORKSPACE, "quant_pack: workspace %zu < %zu bytes",
+                       ws_bytes, need);
+        class_max = (uint32_t*)ws;
+        SPLITQ_CUDA(cudaMemsetAsync(class_max, 0, need, st));
+        dim3 g1(cdiv(S, kQWarps * 4), B);
+        if (vec) class_absmax_kernel<true><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
+        else class_absmax_kernel<false><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
+        SPLITQ_LAUNCH_CHECK("class_absmax_kernel");
+    }
+    dim3 grid(cdiv(S, kQWarps), B);
+#define SPLITQ_QP(MAXCH)                                                                          \
+    do {                                                                                          \
+        if (group)                                                                                \
+            quant_pack_kernel<MAXCH, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, \
+                                                                          payload_stride, class_max); \
+        else                                                                                      \
+            quant_pack_kernel<MAXCH, false><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, \
+                                                                           payload_stride, class_max); \
+    } while (0)
+    if (vec) {
+        const int nch = D / 4;
+        if (nch <= 32 * 4) SPLITQ_QP(4);
+        else if (nch <= 32 * 8) SPLITQ_QP(8);
+        else if (nch <= 32 * 16) SPLITQ_QP(16);
+        else SPLITQ_QP(32);
+    } else if (group) {
+        quant_pack_generic_kernel<true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload,
+                                                                       payload_stride, class_max);
+    } else {
+        quant_pack_generic_kernel<false><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload,
+                                                                        payload_stride, class_max);
+    }
+#undef SPLITQ_QP
+    SPLITQ_LAUNCH_CHECK("quant_pack_kernel");
+    return SPLITQ_OK;
+}

@@ -1,0 +1,249 @@
+"""Host side of the boundary path: thin, allocation-aware wrappers over the C ABI.
+
+Stage order (BASELINE.json north_star): importance scoring -> importance-ranked bit-width
+selection -> absmax/quantise/bit-pack into one payload -> transfer -> dequantise (optionally
+fused with the downstream half's first norm).  Every function here takes and returns CUDA
+tensors; the arithmetic happens in lib/libsplitq.so.  Reference lines each stage replaces are
+cited in include/splitq.h.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _native as N
+
+Ladder = Sequence[Tuple[int, int]]  # [(token_count, bits), ...] least-important first
+
+
+def _stream(t: torch.Tensor) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _need_cuda_f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise N.SplitqError(f"{name}: expected a CUDA tensor (there is no CPU path)")
+    if t.dtype != torch.float32:
+        raise N.SplitqError(f"{name}: expected float32, got {t.dtype}")
+    return t.contiguous()
+
+
+class _Workspace:
+    """Grow-only scratch buffers per (device, tag) so steady-state calls never allocate."""
+
+    def __init__(self) -> None:
+        self._bufs = {}
+
+    def get(self, device: torch.device, tag: str, nbytes: int) -> torch.Tensor:
+        key = (device.index, tag)
+        buf = self._bufs.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+            self._bufs[key] = buf
+        return buf
+
+
+_WS = _Workspace()
+
+
+def ladder_for_ratio(ratio: float, S: int, bits: int = 4) -> List[Tuple[int, int]]:
+    """The reference's single rung: int(ratio*S) least-important tokens at 4 bits
+    (pythia_model.py:169-170,179)."""
+    k = int(ratio * S)
+    return [(k, bits)] if k > 0 else []
+
+
+def ladder_from_fractions(fracs: Sequence[Tuple[float, int]], S: int) -> List[Tuple[int, int]]:
+    """[(0.25, 2), (0.25, 4), (0.25, 8)] -> lowest quarter 2-bit, next 4-bit, next 8-bit."""
+    return [(int(f * S), b) for f, b in fracs]
+
+
+def _ladder_arrays(ladder: Ladder):
+    ks = [int(k) for k, _ in ladder]
+    bs = [int(b) for _, b in ladder]
+    return N.int_array(ks), N.int_array(bs), len(ks)
+
+
+def payload_bytes(S: int, D: int, ladder: Ladder, scale_mode: int) -> int:
+    ks, bs, n = _ladder_arrays(ladder)
+    nbytes = N.load().splitq_payload_bytes(S, D, ks, bs, n, scale_mode)
+    if nbytes == 0:
+        raise N.SplitqError(f"payload_bytes: invalid arguments: {N.load().splitq_last_error().decode()}")
+    return nbytes
+
+
+def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
+                              want_last: bool = False, causal_hint: bool = False,
+                              out_col: Optional[torch.Tensor] = None, out_last: Optional[torch.Tensor] = None):
+    """A: (B,H,Sq,Sk) attention probabilities -> (col (B,Sk) or None, last (B,Sk) or None)."""
+    A = _need_cuda_f32(A, "A")
+    if A.dim() != 4:
+        raise N.SplitqError(f"A: expected (B,H,Sq,Sk), got {tuple(A.shape)}")
+    B, H, Sq, Sk = A.shape
+    lib = N.load()
+    if want_col and out_col is None:
+        out_col = torch.empty(B, Sk, dtype=torch.float32, device=A.device)
+    if want_last and out_last is None:
+        out_last = torch.empty(B, Sk, dtype=torch.float32, device=A.device)
+    ws_bytes = lib.splitq_importance_colmean_workspace_bytes(B, H, Sq, Sk) if want_col else 0
+    ws = _WS.get(A.device, "colmean", ws_bytes) if ws_bytes else None
+    hw = None
+    if head_w is not None:
+        hw = N.float_array([float(x) for x in head_w])
+        if len(hw) != H:
+            raise N.SplitqError(f"head_w has {len(hw)} entries for {H} heads")
+    with torch.cuda.device(A.device):
+        N.check(lib.splitq_importance_colmean(_ptr(A), B, H, Sq, Sk, hw, _ptr(out_col if want_col else None),
+                                              _ptr(out_last if want_last else None), _ptr(ws), ws_bytes,
+                                              N.FLAG_CAUSAL_HINT if causal_hint else 0, _stream(A)))
+    return (out_col if want_col else None), (out_last if want_last else None)
+
+
+def select_bits(imp: torch.Tensor, ladder: Ladder, D: int, bits_out: Optional[torch.Tensor] = None,
+                row_off_out: Optional[torch.Tensor] = None):
+    """imp: (B,S) or (S,) -> (bits u8 (B,S), row_off u32-as-int32 (B,S))."""
+    imp = _need_cuda_f32(imp, "importance")
+    if imp.dim() == 1:
+        imp = imp.unsqueeze(0)
+    B, S = imp.shape
+    if bits_out is None:
+        bits_out = torch.empty(B, S, dtype=torch.uint8, device=imp.device)
+    if row_off_out is None:
+        row_off_out = torch.empty(B, S, dtype=torch.int32, device=imp.device)
+    ks, bs, n = _ladder_arrays(ladder)
+    with torch.cuda.device(imp.device):
+        N.check(N.load().splitq_select_bits(_ptr(imp), B, S, D, ks, bs, n, _ptr(bits_out), _ptr(row_off_out),
+                                            _stream(imp)))
+    return bits_out, row_off_out
+
+
+def quant_pack(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, scale_mode: int, nbytes: int,
+               payload: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """h: (B,S,D) -> payload uint8 (B, nbytes).  `nbytes` = payload_bytes(S, D, ladder, scale_mode)."""
+    h = _need_cuda_f32(h, "hidden_states")
+    if h.dim() == 2:
+        h = h.unsqueeze(0)
+    B, S, D = h.shape
+    if payload is None:
+        payload = torch.empty(B, nbytes, dtype=torch.uint8, device=h.device)
+    lib = N.load()
+    ws_bytes = lib.splitq_quant_pack_workspace_bytes(B, S, D, scale_mode)
+    ws = _WS.get(h.device, "quant", ws_bytes) if ws_bytes else None
+    with torch.cuda.device(h.device):
+        N.check(lib.splitq_quant_pack(_ptr(h), B, S, D, _ptr(bits), _ptr(row_off), scale_mode, _ptr(payload),
+                                      payload.stride(0), _ptr(ws), ws_bytes, _stream(h)))
+    return payload
+
+
+def dequant(payload: torch.Tensor, S: int, D: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """payload (B, nbytes) uint8 -> (B,S,D) fp32."""
+    B = payload.shape[0]
+    if out is None:
+        out = torch.empty(B, S, D, dtype=torch.float32, device=payload.device)
+    with torch.cuda.device(payload.device):
+        N.check(N.load().splitq_dequant(_ptr(payload), payload.stride(0), B, S, D, _ptr(out), _stream(payload)))
+    return out
+
+
+def dequant_norm(payload: torch.Tensor, S: int, D: int, kind: int, gamma: torch.Tensor,
+                 beta: Optional[torch.Tensor], eps: float, gamma2: Optional[torch.Tensor] = None,
+                 beta2: Optional[torch.Tensor] = None, want_resid: bool = True, outs=None):
+    """-> (resid or None, normed, normed2 or None), each (B,S,D) fp32."""
+    B = payload.shape[0]
+    dev = payload.device
+    if outs is None:
+        mk = lambda: torch.empty(B, S, D, dtype=torch.float32, device=dev)  # noqa: E731
+        outs = (mk() if want_resid else None, mk(), mk() if gamma2 is not None else None)
+    resid, normed, normed2 = outs
+    with torch.cuda.device(dev):
+        N.check(N.load().splitq_dequant_norm(_ptr(payload), payload.stride(0), B, S, D, kind, _ptr(gamma),
+                                             _ptr(beta), float(eps), _ptr(gamma2), _ptr(beta2), _ptr(resid),
+                                             _ptr(normed), _ptr(normed2), _stream(payload)))
+    return resid, normed, normed2
+
+
+def transfer(dst: torch.Tensor, src: torch.Tensor, nbytes: Optional[int] = None) -> torch.Tensor:
+    """Payload hop between the halves' devices (cudaMemcpyPeerAsync; same device = D2D copy).
+    Enqueued on the current stream of the SOURCE device."""
+    nbytes = src.numel() * src.element_size() if nbytes is None else nbytes
+    with torch.cuda.device(src.device):
+        N.check(N.load().splitq_transfer_peer(_ptr(dst), dst.device.index, _ptr(src), src.device.index, nbytes,
+                                              _stream(src)))
+    return dst
+
+
+@dataclass
+class BoundaryResult:
+    importance: torch.Tensor
+    bits: torch.Tensor
+    payload: torch.Tensor
+    hidden: torch.Tensor
+
+
+class BoundaryPlan:
+    """Pre-sized buffers for repeated passes of the whole path over (B,H,S,S) attention maps and
+    (B,S,D) hidden states; `run` allocates nothing."""
+
+    def __init__(self, B: int, H: int, S: int, D: int, ladder: Ladder, scale_mode: int = N.SCALE_GROUP,
+                 method: str = "regular_importance", src_device="cuda:0", dst_device=None,
+                 causal_hint: bool = False):
+        self.B, self.H, self.S, self.D = B, H, S, D
+        self.ladder, self.scale_mode, self.method, self.causal_hint = list(ladder), scale_mode, method, causal_hint
+        self.src = torch.device(src_device)
+        self.dst = torch.device(dst_device) if dst_device is not None else self.src
+        self.nbytes = payload_bytes(S, D, self.ladder, scale_mode)
+        f32 = dict(dtype=torch.float32, device=self.src)
+        self.imp = torch.empty(B, S, **f32)
+        self.bits = torch.empty(B, S, dtype=torch.uint8, device=self.src)
+        self.row_off = torch.empty(B, S, dtype=torch.int32, device=self.src)
+        self.payload_src = torch.empty(B, self.nbytes, dtype=torch.uint8, device=self.src)
+        self.payload_dst = torch.empty(B, self.nbytes, dtype=torch.uint8, device=self.dst)
+        self.h_out = torch.empty(B, S, D, dtype=torch.float32, device=self.dst)
+        # warm the grow-only workspaces
+        lib = N.load()
+        _WS.get(self.src, "colmean", lib.splitq_importance_colmean_workspace_bytes(B, H, S, S))
+        _WS.get(self.src, "quant", lib.splitq_quant_pack_workspace_bytes(B, S, D, scale_mode))
+
+    def score(self, A: torch.Tensor) -> torch.Tensor:
+        last = self.method == "last_row"
+        importance_from_attention(A, want_col=not last, want_last=last, causal_hint=self.causal_hint,
+                                  out_col=self.imp, out_last=self.imp)
+        return self.imp
+
+    def send(self, h: torch.Tensor) -> torch.Tensor:
+        select_bits(self.imp, self.ladder, self.D, self.bits, self.row_off)
+        quant_pack(h, self.bits, self.row_off, self.scale_mode, self.nbytes, self.payload_src)
+        return self.payload_src
+
+    def hop(self) -> torch.Tensor:
+        transfer(self.payload_dst, self.payload_src)
+        if self.dst != self.src:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.src))
+            torch.cuda.current_stream(self.dst).wait_event(ev)
+        return self.payload_dst
+
+    def receive(self) -> torch.Tensor:
+        return dequant(self.payload_dst, self.S, self.D, self.h_out)
+
+    def run(self, A: torch.Tensor, h: torch.Tensor) -> BoundaryResult:
+        self.score(A)
+        self.send(h)
+        self.hop()
+        self.receive()
+        return BoundaryResult(self.imp, self.bits, self.payload_dst, self.h_out)
+
+    #: kernels launched by one run(): colsum partial + finalize, select, [memset+class absmax,] pack, dequant
+    def launches_per_run(self) -> int:
+        n = 2 if self.method != "last_row" else 1
+        n += 1
+        n += 2 if self.scale_mode == N.SCALE_GROUP else 1
+        n += 1
+        return n

@@ -179,18 +179,19 @@ def fake_quant_reference(h: torch.Tensor, imp: torch.Tensor, ratio: float) -> to
 # --------------------------------------------------------------------------------------
 # packed payload (our format; see header comment)
 # --------------------------------------------------------------------------------------
-def payload_layout(S: int, D: int, scale_mode: int) -> Tuple[int, int, int]:
-    """(bits_off, scales_off, codes_off) byte offsets inside one window's payload."""
+def payload_layout(S: int, D: int, scale_mode: int) -> Tuple[int, int, int, int]:
+    """(bits_off, rowoff_off, scales_off, codes_off) byte offsets inside one window's payload."""
     bits_off = HEADER_BYTES
-    scales_off = bits_off + pad16(S)
+    rowoff_off = bits_off + pad16(S)
+    scales_off = rowoff_off + pad16(4 * S)
     n_scales = GROUP_SLOTS if scale_mode == SCALE_GROUP else S
     codes_off = scales_off + pad16(4 * n_scales)
-    return bits_off, scales_off, codes_off
+    return bits_off, rowoff_off, scales_off, codes_off
 
 
 def payload_bytes(S: int, D: int, counts: Sequence[Tuple[int, int]], scale_mode: int) -> int:
     """Total bytes; depends only on how many tokens take each width."""
-    _, _, codes_off = payload_layout(S, D, scale_mode)
+    codes_off = payload_layout(S, D, scale_mode)[3]
     n = codes_off
     used = 0
     for k, b in counts:
@@ -249,13 +250,16 @@ def row_codes(h_row: torch.Tensor, m: float, bits: int, scale_mode: int) -> np.n
 def pack_payload(h: torch.Tensor, bits: np.ndarray, scale_mode: int) -> np.ndarray:
     """h: (S,D) fp32, bits: (S,) u8 in {2,4,8,32} -> uint8 payload for one window."""
     S, D = h.shape
-    bits_off, scales_off, codes_off = payload_layout(S, D, scale_mode)
+    bits_off, rowoff_off, scales_off, codes_off = payload_layout(S, D, scale_mode)
     total = codes_off + int(sum(row_bytes(D, int(b)) for b in bits))
     buf = np.zeros(total, dtype=np.uint8)
     n_scales = GROUP_SLOTS if scale_mode == SCALE_GROUP else S
     buf[:HEADER_BYTES] = np.frombuffer(
         struct.pack("<8I", MAGIC, scale_mode, S, D, n_scales, codes_off, total, 0), dtype=np.uint8)
     buf[bits_off:bits_off + S] = bits
+    rb = np.array([row_bytes(D, int(b)) for b in bits], dtype=np.int64)
+    row_off16 = ((np.cumsum(rb) - rb) // 16).astype(np.uint32)
+    buf[rowoff_off:rowoff_off + 4 * S] = row_off16.view(np.uint8)
     scales = token_scales(h, bits, scale_mode)
     buf[scales_off:scales_off + 4 * n_scales] = scales.view(np.uint8)
     off = codes_off
@@ -278,14 +282,14 @@ def unpack_payload(buf: np.ndarray) -> torch.Tensor:
     (pythia_model.py:176-186); token mode treats an all-zero row as zeros (our extension)."""
     magic, scale_mode, S, D, n_scales, codes_off, total, _ = struct.unpack("<8I", buf[:HEADER_BYTES].tobytes())
     assert magic == MAGIC and total == buf.size
-    bits_off, scales_off, _ = payload_layout(S, D, scale_mode)
+    bits_off, rowoff_off, scales_off, _ = payload_layout(S, D, scale_mode)
     bits = buf[bits_off:bits_off + S]
+    row_off16 = buf[rowoff_off:rowoff_off + 4 * S].view(np.uint32)
     scales = buf[scales_off:scales_off + 4 * n_scales].view(np.float32)
     out = torch.empty(S, D, dtype=torch.float32)
-    off = codes_off
     for t in range(S):
         b = int(bits[t])
-        rb = row_bytes(D, b)
+        off = codes_off + 16 * int(row_off16[t])
         if b == BITS_RAW:
             out[t] = torch.from_numpy(buf[off:off + 4 * D].view(np.float32).copy())
         else:
@@ -296,7 +300,6 @@ def unpack_payload(buf: np.ndarray) -> torch.Tensor:
                 out[t] = float("nan")
             else:
                 out[t] = dequant_values(q, torch.tensor(m, dtype=torch.float32), L)
-        off += rb
     return out
 
 

@@ -1,0 +1,272 @@
+"""GPU parity tests: every CUDA kernel, called through the C ABI, against the CPU oracle and the
+golden fixtures produced by the reference's own code.
+
+Bars (BASELINE.json north_star): width maps, codes and packed payloads bit-exact; importance
+<= 1e-5 relative; dequantised values bit-exact; fused norm <= 1e-5 (floating point reassociation).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import splitq
+import splitq_oracle as O
+from splitq import _native as N
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+IMP_RTOL = 1e-5
+
+
+def synth_attention(gen, B, H, S, tau=1.0):
+    mask = torch.full((S, S), float("-inf")).triu(1)
+    return torch.softmax(torch.randn(B, H, S, S, generator=gen) * tau + mask, dim=-1, dtype=torch.float32)
+
+
+def synth_hidden(gen, B, S, D, outliers=True):
+    h = torch.randn(B, S, D, generator=gen)
+    if outliers and D >= 8:
+        ch = torch.randperm(D, generator=gen)[: max(1, D // 100)]
+        h[:, :, ch] *= 20.0
+    return h
+
+
+def rel_err(got, want):
+    return ((got - want).abs() / want.abs().clamp_min(1e-30)).max().item()
+
+
+# ------------------------------------------------------------------------------------------
+# K1 importance
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+@pytest.mark.parametrize("method", ["regular_importance", "last_row", "aggregate_till", "weighted_importance"])
+def test_importance_against_reference_fixtures(golden_dir, tag, method):
+    g = np.load(os.path.join(golden_dir, "importance.npz"))
+    A = torch.from_numpy(g[f"{tag}_A"]).to(DEV)
+    maps = [A[l] for l in range(A.shape[0])]
+    got = splitq.get_importance_order(method, maps, len(maps), g[f"{tag}_head_w"].tolist())
+    want = torch.from_numpy(g[f"{tag}_{method}"])
+    for l in range(len(maps)):
+        assert got[l].shape == want[l].shape
+        np.testing.assert_allclose(got[l].cpu().numpy(), want[l].numpy(), rtol=IMP_RTOL, atol=1e-9)
+
+
+@pytest.mark.parametrize("B,H,S", [(1, 8, 512), (2, 14, 300), (1, 3, 1), (3, 5, 130), (1, 8, 2048)])
+def test_importance_colmean_and_last_row_vs_oracle(B, H, S):
+    gen = torch.Generator().manual_seed(B * 1000 + S)
+    A = synth_attention(gen, B, H, S, tau=2.0)
+    col, last = splitq.importance_from_attention(A.to(DEV), want_col=True, want_last=True)
+    for b in range(B):
+        want_c = O.importance_regular(A[b:b + 1])
+        want_l = O.importance_last_row(A[b:b + 1])
+        assert rel_err(col[b].cpu(), want_c) <= IMP_RTOL
+        assert rel_err(last[b].cpu(), want_l) <= IMP_RTOL
+        # ranking parity: the k least important tokens agree wherever the oracle has a clear gap
+        assert abs(col[b].sum().item() - 1.0) < 1e-4
+
+
+def test_importance_causal_hint_and_rectangular():
+    gen = torch.Generator().manual_seed(7)
+    A = synth_attention(gen, 2, 4, 384)
+    full, _ = splitq.importance_from_attention(A.to(DEV))
+    hint, _ = splitq.importance_from_attention(A.to(DEV), causal_hint=True)
+    assert torch.equal(full, hint)  # skipped tiles hold exact zeros
+    R = torch.rand(1, 3, 50, 70, generator=gen)
+    col, last = splitq.importance_from_attention(R.to(DEV), want_last=True)
+    assert rel_err(col[0].cpu(), R.mean(dim=1).mean(dim=1)[0]) <= IMP_RTOL
+    assert rel_err(last[0].cpu(), R[:, :, -1, :].mean(dim=1)[0]) <= IMP_RTOL
+
+
+def test_importance_unaligned_view_uses_scalar_path():
+    gen = torch.Generator().manual_seed(8)
+    base = torch.rand(1 * 2 * 64 * 64 + 1, generator=gen).to(DEV)
+    A = base[1:].view(1, 2, 64, 64)  # 4-byte aligned only
+    col, _ = splitq.importance_from_attention(A)
+    assert rel_err(col[0].cpu(), O.importance_regular(A.cpu())) <= IMP_RTOL
+
+
+# ------------------------------------------------------------------------------------------
+# K3a selection
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("S", [1, 7, 1000, 1024, 1025, 4096, 5000, 16384, 32768])
+def test_select_bits_matches_stable_argsort(S):
+    gen = torch.Generator().manual_seed(S)
+    D = 64
+    imp = torch.rand(3, S, generator=gen)
+    imp[1] = torch.randint(0, 5, (S,), generator=gen).float() / 4.0  # heavy ties
+    imp[2, ::3] = 0.0
+    imp[2, 1::7] = -0.0  # +0 and -0 are equal; ties by index
+    for ladder in ([], [(S // 4, 4)], [(S // 4, 2), (S // 4, 4), (S // 4, 8)], [(0, 4), (S, 8)], [(S, 2)],
+                   [(1, 8), (0, 2), (S // 2, 4)]):
+        bits, row_off = splitq.select_bits(imp.to(DEV), ladder, D)
+        for b in range(3):
+            want = O.ladder_bits(imp[b], ladder)
+            assert np.array_equal(bits[b].cpu().numpy(), want), (S, ladder, b)
+            rb = np.array([O.row_bytes(D, int(x)) for x in want], dtype=np.int64)
+            want_off = (np.cumsum(rb) - rb) // 16
+            assert np.array_equal(row_off[b].cpu().numpy().astype(np.int64), want_off)
+
+
+def test_select_rejects_bad_arguments():
+    imp = torch.rand(1, 8, device=DEV)
+    with pytest.raises(N.SplitqError):
+        splitq.select_bits(imp, [(9, 4)], 16)
+    with pytest.raises(N.SplitqError):
+        splitq.select_bits(imp, [(1, 3)], 16)
+    with pytest.raises(N.SplitqError):
+        splitq.select_bits(torch.rand(1, N.MAX_SELECT_S + 1, device=DEV), [], 16)
+
+
+# ------------------------------------------------------------------------------------------
+# K3 quantise + pack, K4 dequantise
+# ------------------------------------------------------------------------------------------
+CASES = [
+    (1, 48, 64, [(24, 4)]),
+    (2, 100, 512, [(25, 2), (25, 4), (25, 8)]),
+    (1, 64, 896, [(16, 2), (16, 4), (16, 8)]),
+    (1, 33, 20, [(10, 4), (5, 8)]),
+    (2, 19, 5, [(4, 2), (4, 4), (4, 8)]),       # odd D: generic path, sub-byte tails
+    (1, 16, 2052, [(8, 4)]),                    # register tile of 32 chunks... (D/4 = 513 -> MAXCH 32)
+    (1, 9, 4100, [(3, 2), (3, 8)]),             # D > 4096 -> generic path
+    (1, 40, 512, [(40, 4)]),                    # ratio 1: everything quantised
+    (1, 40, 512, []),                           # ratio 0 equivalent: all raw
+]
+
+
+@pytest.mark.parametrize("mode", [O.SCALE_GROUP, O.SCALE_TOKEN])
+@pytest.mark.parametrize("B,S,D,ladder", CASES)
+def test_payload_bit_exact_and_dequant_bit_exact(B, S, D, ladder, mode):
+    gen = torch.Generator().manual_seed(S * 7 + D)
+    h = synth_hidden(gen, B, S, D)
+    imp = torch.rand(B, S, generator=gen)
+    nbytes = splitq.payload_bytes(S, D, ladder, mode)
+    bits, row_off = splitq.select_bits(imp.to(DEV), ladder, D)
+    payload = splitq.quant_pack(h.to(DEV), bits, row_off, mode, nbytes)
+    deq = splitq.dequant(payload, S, D)
+    for b in range(B):
+        want_bits, want_payload, want_deq = O.boundary_roundtrip(h[b], imp[b], ladder, mode)
+        assert want_payload.size == nbytes
+        got = payload[b].cpu().numpy()
+        assert np.array_equal(got, want_payload), f"payload differs at byte {np.nonzero(got != want_payload)[0][:5]}"
+        assert np.array_equal(deq[b].cpu().numpy().view(np.uint32), want_deq.numpy().view(np.uint32))
+
+
+def test_reference_fake_quant_fixtures_bit_exact(golden_dir):
+    """select -> pack -> dequant on the GPU == the reference's in-place block (captured from its
+    own wrapper run), bit for bit, for every recorded (model, method, layer, ratio)."""
+    g = np.load(os.path.join(golden_dir, "fake_quant.npz"))
+    keys = sorted({k.rsplit("|", 1)[0] for k in g.files})
+    checked = 0
+    for key in keys:
+        ratio = float(key.split("|")[3])
+        pre = torch.from_numpy(g[key + "|pre"])
+        imp = torch.from_numpy(g[key + "|imp"])
+        S, D = pre.shape
+        ladder = splitq.ladder_for_ratio(ratio, S)
+        nbytes = splitq.payload_bytes(S, D, ladder, O.SCALE_GROUP)
+        bits, row_off = splitq.select_bits(imp.to(DEV), ladder, D)
+        payload = splitq.quant_pack(pre.to(DEV), bits, row_off, O.SCALE_GROUP, nbytes)
+        post = splitq.dequant(payload, S, D)[0].cpu().numpy()
+        assert np.array_equal(post.view(np.uint32), g[key + "|post"].view(np.uint32)), key
+        checked += 1
+    assert checked >= 30
+
+
+def test_zero_block_reproduces_reference_nan_in_group_mode_only():
+    S, D = 8, 16
+    h = torch.zeros(1, S, D)
+    h[0, 4:] = torch.arange(1, 4 * D + 1).float().view(4, D)
+    imp = torch.arange(S).float().unsqueeze(0)
+    for mode in (O.SCALE_GROUP, O.SCALE_TOKEN):
+        nbytes = splitq.payload_bytes(S, D, [(4, 4)], mode)
+        bits, off = splitq.select_bits(imp.to(DEV), [(4, 4)], D)
+        deq = splitq.dequant(splitq.quant_pack(h.to(DEV), bits, off, mode, nbytes), S, D)[0].cpu()
+        want = O.boundary_roundtrip(h[0], imp[0], [(4, 4)], mode)[2]
+        assert torch.equal(torch.isnan(deq), torch.isnan(want))
+        assert torch.equal(torch.nan_to_num(deq), torch.nan_to_num(want))
+        assert torch.isnan(deq[:4]).all() == (mode == O.SCALE_GROUP)
+
+
+@pytest.mark.parametrize("kind", ["layernorm", "rmsnorm"])
+@pytest.mark.parametrize("S,D", [(50, 512), (33, 896), (7, 20), (5, 6)])
+def test_dequant_fused_norm(kind, S, D):
+    gen = torch.Generator().manual_seed(D)
+    B = 2
+    h = synth_hidden(gen, B, S, D)
+    imp = torch.rand(B, S, generator=gen)
+    ladder = [(S // 4, 2), (S // 4, 4), (S // 4, 8)]
+    mode = O.SCALE_TOKEN
+    nbytes = splitq.payload_bytes(S, D, ladder, mode)
+    bits, off = splitq.select_bits(imp.to(DEV), ladder, D)
+    payload = splitq.quant_pack(h.to(DEV), bits, off, mode, nbytes)
+    g1, b1 = torch.randn(D, generator=gen), torch.randn(D, generator=gen)
+    g2, b2 = torch.randn(D, generator=gen), torch.randn(D, generator=gen)
+    if kind == "layernorm":
+        resid, n1, n2 = splitq.dequant_norm(payload, S, D, N.NORM_LAYERNORM, g1.to(DEV), b1.to(DEV), 1e-5,
+                                            g2.to(DEV), b2.to(DEV))
+    else:
+        resid, n1, n2 = splitq.dequant_norm(payload, S, D, N.NORM_RMSNORM, g1.to(DEV), None, 1e-6)
+    plain = splitq.dequant(payload, S, D)
+    assert torch.equal(resid, plain)
+    for b in range(B):
+        x = O.unpack_payload(payload[b].cpu().numpy())
+        if kind == "layernorm":
+            np.testing.assert_allclose(n1[b].cpu().numpy(), O.layer_norm(x, g1, b1, 1e-5).numpy(), rtol=1e-5, atol=2e-5)
+            np.testing.assert_allclose(n2[b].cpu().numpy(), O.layer_norm(x, g2, b2, 1e-5).numpy(), rtol=1e-5, atol=2e-5)
+        else:
+            assert n2 is None
+            np.testing.assert_allclose(n1[b].cpu().numpy(), O.rms_norm(x, g1, 1e-6).numpy(), rtol=1e-5, atol=2e-5)
+
+
+def test_corrupt_payload_fails_loudly():
+    S, D = 16, 32
+    payload = torch.zeros(1, splitq.payload_bytes(S, D, [], 0), dtype=torch.uint8, device=DEV)
+    out = splitq.dequant(payload, S, D)
+    assert torch.isnan(out).all()
+
+
+def test_transfer_same_device_copy():
+    src = torch.randint(0, 255, (3, 4096), dtype=torch.uint8, device=DEV)
+    dst = torch.zeros_like(src)
+    splitq.transfer(dst, src)
+    torch.cuda.synchronize()
+    assert torch.equal(src, dst)
+
+
+# ------------------------------------------------------------------------------------------
+# full-size properties (BASELINE.json config 3 shapes; oracle too slow here)
+# ------------------------------------------------------------------------------------------
+def test_full_size_roundtrip_properties():
+    B, H, S, D = 2, 14, 4096, 896
+    gen = torch.Generator(device=DEV).manual_seed(3)
+    h = torch.randn(B, S, D, device=DEV, generator=gen)
+    logits = torch.randn(B, H, S, S, device=DEV, generator=gen)
+    A = torch.softmax(logits + torch.full((S, S), float("-inf"), device=DEV).triu(1), dim=-1)
+    del logits
+    ladder = splitq.ladder_from_fractions([(0.25, 2), (0.25, 4), (0.25, 8)], S)
+    plan = splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=O.SCALE_TOKEN)
+    res = plan.run(A, h)
+    torch.cuda.synchronize()
+    ref_imp = A.mean(dim=1).mean(dim=1)
+    assert rel_err(res.importance, ref_imp) <= IMP_RTOL
+    bits = res.bits
+    assert [(bits == w).sum(dim=1).tolist() for w in (2, 4, 8, 32)] == [[1024] * B] * 4
+    # the selected sets are exactly the lowest-ranked tokens of the kernel's own scores
+    order = torch.argsort(res.importance, dim=1, stable=True)
+    for b in range(B):
+        assert (bits[b][order[b, :1024]] == 2).all() and (bits[b][order[b, 3072:]] == 32).all()
+    raw = bits == 32
+    assert torch.equal(res.hidden[raw], h[raw])  # raw rows cross untouched
+    m = h.abs().amax(dim=2, keepdim=True)
+    for w in (2, 4, 8):
+        L = O.levels(w)
+        sel = bits == w
+        err = (res.hidden - h).abs()[sel]
+        assert (err <= (m.expand_as(h)[sel] / L) * 0.5 * (1 + 1e-6) + 1e-12).all()
+    # idempotence: re-quantising the dequantised tensor with the same map reproduces the payload codes
+    p2 = splitq.quant_pack(res.hidden, plan.bits, plan.row_off, O.SCALE_TOKEN, plan.nbytes)
+    lay = O.payload_layout(S, D, O.SCALE_TOKEN)
+    assert torch.equal(p2[:, lay[3]:], res.payload[:, lay[3]:])
+    hdr = res.payload[0, :32].cpu().numpy().view(np.uint32)
+    assert hdr[0] == O.MAGIC and hdr[2] == S and hdr[3] == D and hdr[6] == plan.nbytes
