@@ -199,6 +199,7 @@ class BoundaryPlan:
         self.src = torch.device(src_device)
         self.dst = torch.device(dst_device) if dst_device is not None else self.src
         self.nbytes = payload_bytes(S, D, self.ladder, scale_mode)
+        self.transport = None
         f32 = dict(dtype=torch.float32, device=self.src)
         self.imp = torch.empty(B, S, **f32)
         self.bits = torch.empty(B, S, dtype=torch.uint8, device=self.src)
@@ -223,6 +224,8 @@ class BoundaryPlan:
         return self.payload_src
 
     def hop(self) -> torch.Tensor:
+        if self.transport is not None:  # e.g. transport.PairExchange between ranks
+            return self.transport.send(self.payload_src, self.payload_dst)
         transfer(self.payload_dst, self.payload_src)
         if self.dst != self.src:
             ev = torch.cuda.Event()
@@ -239,6 +242,25 @@ class BoundaryPlan:
         self.hop()
         self.receive()
         return BoundaryResult(self.imp, self.bits, self.payload_dst, self.h_out)
+
+    def run_host(self, A_host: torch.Tensor, h_host: torch.Tensor, out_host: torch.Tensor) -> torch.Tensor:
+        """End-to-end call with HOST buffers (pinned for full speed): H2D of this step's attention
+        maps and hidden states, the whole path, D2H of the dequantised hidden states.  Blocks until
+        the result is in `out_host`."""
+        if getattr(self, "_A_dev", None) is None:
+            self._A_dev = torch.empty(self.B, self.H, self.S, self.S, dtype=torch.float32, device=self.src)
+            self._h_dev = torch.empty(self.B, self.S, self.D, dtype=torch.float32, device=self.src)
+        self._A_dev.copy_(A_host, non_blocking=True)
+        self._h_dev.copy_(h_host, non_blocking=True)
+        self.run(self._A_dev, self._h_dev)
+        with torch.cuda.device(self.dst):
+            out_host.copy_(self.h_out, non_blocking=True)
+            torch.cuda.current_stream(self.dst).synchronize()
+        return out_host
+
+    def host_bytes_per_run(self):
+        """(h2d, d2h) bytes moved by one run_host()."""
+        return 4 * self.B * (self.H * self.S * self.S + self.S * self.D), 4 * self.B * self.S * self.D
 
     #: kernels launched by one run(): colsum partial + finalize, select, [memset+class absmax,] pack, dequant
     def launches_per_run(self) -> int:

@@ -176,6 +176,27 @@ def fake_quant_reference(h: torch.Tensor, imp: torch.Tensor, ratio: float) -> to
     return h
 
 
+def reference_boundary_cpu(A: torch.Tensor, h: torch.Tensor, ladder, scale_mode: int, method="regular_importance"):
+    """The reference's boundary path as it runs on a CPU, vectorised ATen ops only: importance
+    (last_row_exp.py:13-30), argsort selection (pythia_model.py:169-170) and, per ladder rung, the
+    gather / absmax / scale / clamp / round / rescale / index_put block (pythia_model.py:176-188)
+    applied in place.  Used as the timed CPU baseline; it never packs (the reference does not)."""
+    imp = importance_regular(A) if method == "regular_importance" else importance_last_row(A)
+    order = torch.argsort(imp, descending=False)
+    pos = 0
+    for k, b in ladder:
+        idx = order[pos:pos + k]
+        pos += k
+        if k == 0:
+            continue
+        L = float(levels(b))
+        sel = h[:, idx, :]
+        m = torch.max(torch.abs(sel)) if scale_mode == SCALE_GROUP else sel.abs().amax(dim=-1, keepdim=True)
+        q = torch.round(torch.clamp(sel / m * L, -(L + 1.0), L))
+        h[:, idx, :] = q / L * m
+    return imp, h
+
+
 # --------------------------------------------------------------------------------------
 # packed payload (our format; see header comment)
 # --------------------------------------------------------------------------------------

@@ -168,7 +168,12 @@ def test_reference_fake_quant_fixtures_bit_exact(golden_dir):
         bits, row_off = splitq.select_bits(imp.to(DEV), ladder, D)
         payload = splitq.quant_pack(pre.to(DEV), bits, row_off, O.SCALE_GROUP, nbytes)
         post = splitq.dequant(payload, S, D)[0].cpu().numpy()
-        assert np.array_equal(post.view(np.uint32), g[key + "|post"].view(np.uint32)), key
+        # value equality: an integer code has no negative zero, the reference's fp32 fake-quant does
+        # (round(-0.3) = -0.0); -0.0 == +0.0 numerically, every other value must match exactly
+        want = g[key + "|post"]
+        assert np.array_equal(post, want), key
+        nz = want != 0
+        assert np.array_equal(post.view(np.uint32)[nz], want.view(np.uint32)[nz]), key
         checked += 1
     assert checked >= 30
 
@@ -263,7 +268,8 @@ def test_full_size_roundtrip_properties():
         L = O.levels(w)
         sel = bits == w
         err = (res.hidden - h).abs()[sel]
-        assert (err <= (m.expand_as(h)[sel] / L) * 0.5 * (1 + 1e-6) + 1e-12).all()
+        mm = m.expand_as(h)[sel]
+        assert (err <= mm / L * 0.5 + mm * 1e-6).all()  # half a step + fp32 rounding of q/L*m
     # idempotence: re-quantising the dequantised tensor with the same map reproduces the payload codes
     p2 = splitq.quant_pack(res.hidden, plan.bits, plan.row_off, O.SCALE_TOKEN, plan.nbytes)
     lay = O.payload_layout(S, D, O.SCALE_TOKEN)
