@@ -96,6 +96,25 @@ int splitq_quant_pack(const float* h, int B, int S, int D, const uint8_t* bits,
                       const uint32_t* row_off, int scale_mode, uint8_t* payload,
                       size_t payload_stride, void* ws, size_t ws_bytes, splitq_stream_t stream);
 
+/* Group-mode splitq_quant_pack for hosts that cannot allocate device memory.  It has no
+ * counterpart in the reference.  Who needs it: a process whose serving runtime took all of HBM
+ * into its own pool at start-up (cudaMalloc then fails or fragments, and it stalls every stream
+ * of the device while it runs), or a plugin callback that is not allowed to allocate while it
+ * enqueues work -- such callers have nowhere to get the class-maximum workspace from.  Here that
+ * scratch is a fixed array inside the library (16 KiB on every GPU that loads it, held until
+ * exit), so the call takes only inputs and outputs.  Results are identical to
+ * splitq_quant_pack(..., SPLITQ_SCALE_GROUP, ...).
+ *   - at most SPLITQ_NOALLOC_MAX_WINDOWS windows per call; larger B is refused (SPLITQ_ERR_ARG);
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *     with that device current); make that first call before any stream capture begins;
+ *   - every call uses the same array and clears the part it needs first, so two calls whose GPU
+ *     work overlaps (different streams, or different threads) race: serialise them;
+ *   - no cudaMalloc / cudaFree / allocating library routine is called. */
+#define SPLITQ_NOALLOC_MAX_WINDOWS 1024
+int splitq_quant_pack_group_noalloc(const float* h, int B, int S, int D, const uint8_t* bits,
+                                    const uint32_t* row_off, uint8_t* payload, size_t payload_stride,
+                                    splitq_stream_t stream);
+
 /* ---- dequantise (K4) -------------------------------------------------------------------
  * Replaces quantized/7*max + index_put (pythia_model.py:186-188, qwen_layer_wise.py:68-70):
  * h_out (B,S,D) = every token of the window, raw rows copied, coded rows as (q / L) * m.

@@ -10,6 +10,8 @@
 // result bit for bit, and fields are packed in registers and stored straight into the payload.
 // The reference's single scale for the whole selected set ("group" mode) needs the class maximum
 // before any code can be emitted, hence a small first phase over the selected rows only.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace splitq {
@@ -299,6 +301,87 @@ extern "C" int splitq_quant_pack(const float* h, int B, int S, int D, const uint
                                                                         payload_stride, class_max);
     }
 #undef SPLITQ_QP
+    SPLITQ_LAUNCH_CHECK("quant_pack_kernel");
+    return SPLITQ_OK;
+}
+
+// ---- allocation-free group-mode variant -------------------------------------------------------
+// Group mode needs a few words of scratch for the per-class maxima.  Some hosts cannot supply
+// it: a serving runtime that handed every byte of HBM to its own pool at start-up (a late
+// cudaMalloc fails against that pool, and it also stalls every stream on the device), or a
+// plugin hook whose contract forbids allocating while it enqueues work.  For them the scratch
+// lives in the library image instead, once per GPU that loads it, for the life of the process.
+namespace splitq {
+
+static __device__ __align__(256) uint32_t g_static_class_max[SPLITQ_NOALLOC_MAX_WINDOWS * 4];
+
+// In host code `g_static_class_max` is only a handle; the usable device address has to be asked
+// for, with the right device current, once per device.
+static int static_class_max_ptr(uint32_t** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static uint32_t* ptrs[kMaxDevices] = {};
+    int dev = -1;
+    SPLITQ_CUDA(cudaGetDevice(&dev));
+    SPLITQ_REQUIRE(dev >= 0 && dev < kMaxDevices, SPLITQ_ERR_ARG, "quant_pack_group_noalloc: device %d out of range",
+                   dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        SPLITQ_CUDA(cudaGetSymbolAddress(&p, g_static_class_max));
+        SPLITQ_REQUIRE(p != nullptr, SPLITQ_ERR_CUDA, "quant_pack_group_noalloc: no address for the static scratch");
+        ptrs[dev] = static_cast<uint32_t*>(p);
+    }
+    *out = ptrs[dev];
+    return SPLITQ_OK;
+}
+
+}  // namespace splitq
+
+extern "C" int splitq_quant_pack_group_noalloc(const float* h, int B, int S, int D, const uint8_t* bits,
+                                               const uint32_t* row_off, uint8_t* payload,
+                                               size_t payload_stride, splitq_stream_t stream) {
+    SPLITQ_REQUIRE(h && bits && row_off && payload, SPLITQ_ERR_ARG, "quant_pack_group_noalloc: NULL buffer");
+    SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0, SPLITQ_ERR_ARG, "quant_pack_group_noalloc: bad shape B=%d S=%d D=%d",
+                   B, S, D);
+    SPLITQ_REQUIRE(B <= SPLITQ_NOALLOC_MAX_WINDOWS, SPLITQ_ERR_ARG,
+                   "quant_pack_group_noalloc: B=%d windows exceeds the built-in scratch (max %d per call); "
+                   "split the batch or use splitq_quant_pack with a caller workspace",
+                   B, SPLITQ_NOALLOC_MAX_WINDOWS);
+    SPLITQ_REQUIRE(aligned16(payload) && payload_stride % 16 == 0, SPLITQ_ERR_ALIGN,
+                   "quant_pack_group_noalloc: payload and payload_stride must be 16-byte aligned");
+    const PayloadLayout lay = payload_layout((uint32_t)S, SPLITQ_SCALE_GROUP);
+    SPLITQ_REQUIRE(B == 1 || payload_stride >= lay.codes_off, SPLITQ_ERR_WORKSPACE,
+                   "quant_pack_group_noalloc: payload_stride %zu smaller than the payload index (%u)",
+                   payload_stride, lay.codes_off);
+    if (int rc = check_arch()) return rc;
+    uint32_t* class_max = nullptr;
+    if (int rc = static_class_max_ptr(&class_max)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps whatever the previous call left: the maxima must start from zero
+    SPLITQ_CUDA(cudaMemsetAsync(class_max, 0, (size_t)B * 4 * sizeof(uint32_t), st));
+    const bool vec = (D % 4 == 0) && aligned16(h) && D <= 4096;
+    dim3 g1(cdiv(S, kQWarps * 4), B);
+    if (vec) class_absmax_kernel<true><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
+    else class_absmax_kernel<false><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
+    SPLITQ_LAUNCH_CHECK("class_absmax_kernel");
+    dim3 grid(cdiv(S, kQWarps), B);
+    const int nch = D / 4;
+    if (!vec)
+        quant_pack_generic_kernel<true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload,
+                                                                       payload_stride, class_max);
+    else if (nch <= 32 * 4)
+        quant_pack_kernel<4, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
+                                                                  class_max);
+    else if (nch <= 32 * 8)
+        quant_pack_kernel<8, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
+                                                                  class_max);
+    else if (nch <= 32 * 16)
+        quant_pack_kernel<16, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
+                                                                   class_max);
+    else
+        quant_pack_kernel<32, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
+                                                                   class_max);
     SPLITQ_LAUNCH_CHECK("quant_pack_kernel");
     return SPLITQ_OK;
 }

@@ -17,6 +17,7 @@ BITS_RAW = 32
 NORM_LAYERNORM, NORM_RMSNORM = 0, 1
 FLAG_CAUSAL_HINT = 1
 MAX_SELECT_S = 32768
+NOALLOC_MAX_WINDOWS = 1024
 
 _vp, _sz, _i, _u = C.c_void_p, C.c_size_t, C.c_int, C.c_uint
 _ip = C.POINTER(C.c_int)
@@ -32,6 +33,7 @@ SIGNATURES = {
     "splitq_payload_bytes": (_sz, [_i, _i, _ip, _ip, _i, _i]),
     "splitq_quant_pack_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "splitq_quant_pack": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _sz, _vp, _sz, _vp]),
+    "splitq_quant_pack_group_noalloc": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "splitq_dequant": (_i, [_vp, _sz, _i, _i, _i, _vp, _vp]),
     "splitq_dequant_norm": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, C.c_float, _vp, _vp, _vp, _vp, _vp, _vp]),
     "splitq_transfer_peer": (_i, [_vp, _i, _vp, _i, _sz, _vp]),

@@ -142,6 +142,23 @@ def quant_pack(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, scale
     return payload
 
 
+def quant_pack_group_noalloc(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor,
+                             payload: torch.Tensor) -> torch.Tensor:
+    """Group-mode quantise + pack for callers that may not allocate on the device (a runtime that
+    reserved all of HBM for itself, or a hook that must not allocate while enqueuing).  The
+    class-maximum scratch is a fixed array inside the library, so only inputs and the output
+    `payload` (B, nbytes) are passed -- all of them existing tensors; nothing is allocated here.
+    At most _native.NOALLOC_MAX_WINDOWS windows per call.  Calls share that array: do not let two
+    of them overlap on the GPU.  Make the first call on a device before any stream capture."""
+    if not (h.is_cuda and h.dtype == torch.float32 and h.is_contiguous() and h.dim() == 3):
+        raise N.SplitqError("quant_pack_group_noalloc: h must be a contiguous (B,S,D) float32 CUDA tensor")
+    B, S, D = h.shape
+    with torch.cuda.device(h.device):
+        N.check(N.load().splitq_quant_pack_group_noalloc(_ptr(h), B, S, D, _ptr(bits), _ptr(row_off), _ptr(payload),
+                                                         payload.stride(0), _stream(h)))
+    return payload
+
+
 def dequant(payload: torch.Tensor, S: int, D: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """payload (B, nbytes) uint8 -> (B,S,D) fp32."""
     B = payload.shape[0]
