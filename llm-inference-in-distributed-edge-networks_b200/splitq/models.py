@@ -1,0 +1,300 @@
+"""Layer-wise model wrappers with the reference's call surface, running the split-layer
+boundary through the CUDA path.
+
+Reference: `Pythia70Model` (Experiments/Pythia-70M/pythia_model.py:13-206) and
+`QwenPointFiveBModel` (Experiments/Qwen2-0.5B/qwen_layer_wise.py:5-167).  Same constructor
+arguments, attributes (`.model .tokenizer .device .num_layers .gpt_neox/.qwen .final_layer_norm
+.rotary_emb .ratios`) and method signatures; `activation_quantization` returns the 0-dim NLL.
+
+What differs, by design:
+  * the in-place fake quant at `i == layer_of_interest` (pythia_model.py:167-188,
+    qwen_layer_wise.py:54-70) becomes select -> quantise/pack -> transfer -> dequantise, the
+    last step fused with the first norm of layer i+1 (or the final norm);
+  * the two halves may live on two devices (`split_devices=(up, down)`); each device holds a full
+    copy of the (small) model so that any `layer_of_interest` can be evaluated without moving
+    modules, and the payload is what crosses NVLink;
+  * `from_config(...)` builds the architecture with seeded random weights (no network here).
+HF decoder layers, rotary embedding, LM head and the loss stay stock PyTorch/HF.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _native as N
+from . import boundary, compat
+
+
+class _LayerWiseModel:
+    family = ""
+    hub_name = ""
+    default_cfg: dict = {}
+
+    # ---- construction ---------------------------------------------------------------------
+    def _setup(self, device, model, tokenizer=None, split_devices=None, scale_mode="group", bits=4,
+               fuse_norm=True, ladder_fracs=None):
+        self.device = device
+        self.tokenizer = tokenizer
+        self.model = model.to(device).eval()
+        self.scale_mode = N.SCALE_GROUP if scale_mode in ("group", N.SCALE_GROUP) else N.SCALE_TOKEN
+        self.bits = bits
+        self.ladder_fracs = ladder_fracs
+        self.fuse_norm = fuse_norm
+        self.num_layers = len(self.model.base_model.layers)
+        self._bind(self.model)
+        self.down_device = torch.device(device)
+        self._down = self.model
+        if split_devices is not None:
+            up, down = (torch.device(d) for d in split_devices)
+            if up != torch.device(device):
+                raise ValueError("split_devices[0] must equal `device` (the upstream half)")
+            if down != up:
+                import copy
+                self._down = copy.deepcopy(self.model).to(down).eval()
+                self.down_device = down
+        self.last_payload_bytes = 0
+
+    @classmethod
+    def from_config(cls, device, *args, cfg: Optional[dict] = None, seed: int = 0, **kw):
+        """Offline constructor: same architecture, seeded random weights."""
+        self = object.__new__(cls)
+        model = compat.build_causal_lm(cls.family, cfg or cls.default_cfg, seed=seed, attn_implementation="sdpa")
+        self._init_extra(*args)
+        self._setup(device, model, **kw)
+        return self
+
+    @classmethod
+    def from_model(cls, device, model, *args, **kw):
+        self = object.__new__(cls)
+        self._init_extra(*args)
+        self._setup(device, model, **kw)
+        return self
+
+    def _from_pretrained(self, device, **kw):
+        from transformers import AutoModelForCausalLM, AutoTokenizer
+        try:
+            model = AutoModelForCausalLM.from_pretrained(self.hub_name, attn_implementation="sdpa")
+            tokenizer = AutoTokenizer.from_pretrained(self.hub_name)
+        except Exception as e:  # no network / no cache
+            raise RuntimeError(f"cannot load {self.hub_name} ({e}); offline use "
+                               f"{type(self).__name__}.from_config(device, ...)") from e
+        self._setup(device, model, tokenizer, **kw)
+
+    def _init_extra(self, *args):
+        pass
+
+    # family hooks -------------------------------------------------------------------------
+    def _bind(self, model):
+        raise NotImplementedError
+
+    def _embed(self, model, ids):
+        raise NotImplementedError
+
+    def _lm_head(self, model):
+        raise NotImplementedError
+
+    def _final_norm(self, model):
+        raise NotImplementedError
+
+    def _run_prenormed_layer(self, layer, resid, normed, normed2, pos):
+        raise NotImplementedError
+
+    def _first_norm_params(self, layer):
+        raise NotImplementedError
+
+    # ---- shared pieces ----------------------------------------------------------------------
+    def move_to_device(self):  # pythia_model.py:147-148
+        self.model.to(self.device)
+
+    def remove_from_device(self):  # pythia_model.py:150-151
+        self.model.to("cpu")
+
+    def _positions(self, model, hidden, ids):
+        position_ids = torch.arange(ids.size(1), dtype=torch.long, device=ids.device).unsqueeze(0).expand(
+            ids.size(0), -1)
+        return model.base_model.rotary_emb(hidden, position_ids)
+
+    def last_portion(self, post_norm, target, model=None):
+        """LM head + shifted cross entropy (qwen_layer_wise.py:28-40, pythia_model.py:193-203)."""
+        model = model or self._down
+        logits = self._lm_head(model)(post_norm)
+        target = target[:, 1:].to(logits.device)
+        logits = logits[:, :-1, :]
+        return torch.nn.functional.cross_entropy(logits.reshape(-1, logits.size(-1)), target.reshape(-1),
+                                                 ignore_index=-100)
+
+    def ladder(self, ratio: float, S: int):
+        if self.ladder_fracs is not None:  # extension: fixed multi-width ladder scaled by ratio
+            return boundary.ladder_from_fractions([(f * ratio, b) for f, b in self.ladder_fracs], S)
+        return boundary.ladder_for_ratio(ratio, S, self.bits)
+
+    def upstream(self, batched_input_tokens, layer_of_interest):
+        """Embedding + layers 0..layer_of_interest on the upstream device -> (B,S,D) fp32."""
+        ids = batched_input_tokens.to(self.device)
+        hidden = self._embed(self.model, ids)
+        pos = self._positions(self.model, hidden, ids)
+        layers = compat.decoder_layers(self.model.base_model)
+        for i in range(layer_of_interest + 1):
+            hidden = compat.layer_output(layers[i](hidden, position_embeddings=pos))
+        return hidden
+
+    def boundary_send(self, hidden, importance_values, ratio):
+        """select -> quantise -> pack on the upstream device.  Returns (payload, S, D)."""
+        B, S, D = hidden.shape
+        imp = importance_values.to(hidden.device, torch.float32)
+        if imp.dim() == 1:
+            imp = imp.unsqueeze(0).expand(B, S)
+        ladder = self.ladder(ratio, S)
+        nbytes = boundary.payload_bytes(S, D, ladder, self.scale_mode)
+        bits, row_off = boundary.select_bits(imp, ladder, D)
+        payload = boundary.quant_pack(hidden, bits, row_off, self.scale_mode, nbytes)
+        self.last_payload_bytes = B * nbytes
+        return payload
+
+    def boundary_hop(self, payload):
+        if self.down_device == payload.device:
+            return payload
+        dst = torch.empty(payload.shape, dtype=torch.uint8, device=self.down_device)
+        boundary.transfer(dst, payload)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(payload.device))
+        torch.cuda.current_stream(self.down_device).wait_event(ev)
+        return dst
+
+    def downstream(self, ids_shape, target, layer_of_interest, payload=None, hidden=None):
+        """Layers layer_of_interest+1.. + final norm + loss on the downstream device, starting
+        either from a payload (dequantise fused into the first norm) or from raw hidden states."""
+        model = self._down
+        dev = self.down_device
+        B, S = ids_shape
+        D = model.config.hidden_size
+        layers = compat.decoder_layers(model.base_model)
+        ids_stub = torch.empty(B, S, dtype=torch.long, device=dev)
+        nxt = layer_of_interest + 1
+        if payload is not None and self.fuse_norm:
+            if nxt < self.num_layers:
+                kind, g1, b1, eps, g2, b2 = self._first_norm_params(layers[nxt])
+                resid, n1, n2 = boundary.dequant_norm(payload, S, D, kind, g1, b1, eps, g2, b2)
+                pos = self._positions(model, resid, ids_stub)
+                hidden = self._run_prenormed_layer(layers[nxt], resid, n1, n2, pos)
+                nxt += 1
+            else:
+                fn = self._final_norm(model)
+                kind = N.NORM_LAYERNORM if isinstance(fn, torch.nn.LayerNorm) else N.NORM_RMSNORM
+                eps = fn.eps if kind == N.NORM_LAYERNORM else fn.variance_epsilon
+                _, post_norm, _ = boundary.dequant_norm(payload, S, D, kind, fn.weight, getattr(fn, "bias", None),
+                                                        eps, want_resid=False)
+                return self.last_portion(post_norm, target, model)
+        elif payload is not None:
+            hidden = boundary.dequant(payload, S, D)
+        else:
+            hidden = hidden.to(dev)
+        if nxt < self.num_layers:
+            pos = self._positions(model, hidden, ids_stub)
+            for i in range(nxt, self.num_layers):
+                hidden = compat.layer_output(layers[i](hidden, position_embeddings=pos))
+        post_norm = self._final_norm(model)(hidden)
+        return self.last_portion(post_norm, target, model)
+
+    # ---- reference API ------------------------------------------------------------------------
+    def activation_quantization(self, batched_input_tokens, target, importance_values, ratio, layer_of_interest):
+        """Same contract as pythia_model.py:153-206 / qwen_layer_wise.py:42-76."""
+        with torch.no_grad():
+            hidden = self.upstream(batched_input_tokens, layer_of_interest)
+            shape = tuple(batched_input_tokens.shape)
+            if ratio > 0:
+                payload = self.boundary_hop(self.boundary_send(hidden, importance_values, ratio))
+                return self.downstream(shape, target, layer_of_interest, payload=payload)
+            return self.downstream(shape, target, layer_of_interest, hidden=hidden)
+
+    def layer_by_layer_impl(self, batched_input_tokens, target):
+        """No-quant baseline (qwen_layer_wise.py:78-104)."""
+        with torch.no_grad():
+            hidden = self.upstream(batched_input_tokens, self.num_layers - 1)
+            return self.downstream(tuple(batched_input_tokens.shape), target, self.num_layers - 1, hidden=hidden)
+
+
+class Pythia70Model(_LayerWiseModel):
+    """Reference: Experiments/Pythia-70M/pythia_model.py:13 (`Pythia70Model(device, ratios)`)."""
+    family, hub_name, default_cfg = "gpt_neox", "EleutherAI/pythia-70m", compat.PYTHIA_70M
+
+    def __init__(self, device, ratios, **kw) -> None:
+        self.ratios = ratios
+        self._from_pretrained(device, **kw)
+
+    def _init_extra(self, ratios=None):
+        self.ratios = ratios
+
+    def _bind(self, model):
+        self.gpt_neox = model.base_model
+        self.final_layer_norm = model.gpt_neox.final_layer_norm
+        self.rotary_emb = self.gpt_neox.rotary_emb
+
+    def _embed(self, model, ids):
+        return model.base_model.embed_in(ids)
+
+    def _lm_head(self, model):
+        return model.embed_out
+
+    def _final_norm(self, model):
+        return model.gpt_neox.final_layer_norm
+
+    def _first_norm_params(self, layer):
+        ln1, ln2 = layer.input_layernorm, layer.post_attention_layernorm
+        if layer.use_parallel_residual:
+            return N.NORM_LAYERNORM, ln1.weight, ln1.bias, ln1.eps, ln2.weight, ln2.bias
+        return N.NORM_LAYERNORM, ln1.weight, ln1.bias, ln1.eps, None, None
+
+    def _run_prenormed_layer(self, layer, resid, normed, normed2, pos):
+        # GPTNeoXLayer.forward with input_layernorm (and, for parallel residual, the second
+        # LayerNorm) already applied by the fused dequant kernel
+        attn_out, _ = layer.attention(normed, attention_mask=None, position_embeddings=pos)
+        attn_out = layer.post_attention_dropout(attn_out)
+        if layer.use_parallel_residual:
+            mlp_out = layer.post_mlp_dropout(layer.mlp(normed2))
+            return mlp_out + attn_out + resid
+        attn_out = attn_out + resid
+        mlp_out = layer.post_mlp_dropout(layer.mlp(layer.post_attention_layernorm(attn_out)))
+        return mlp_out + attn_out
+
+    def calculate_batched_nll(self, hidden_states, target):
+        """pythia_model.py:36-54: one NLL per entry of self.ratios, ratio used as batch index."""
+        with torch.no_grad():
+            logits = self.model.embed_out(self.final_layer_norm(hidden_states))
+            target = target[:, 1:]
+            logits = logits[:, :-1, :]
+            return [torch.nn.functional.cross_entropy(logits[r, :, :].view(-1, logits.size(-1)), target.view(-1),
+                                                      ignore_index=-100) for r in self.ratios]
+
+
+class QwenPointFiveBModel(_LayerWiseModel):
+    """Reference: Experiments/Qwen2-0.5B/qwen_layer_wise.py:5 (`QwenPointFiveBModel(device)`)."""
+    family, hub_name, default_cfg = "qwen2", "Qwen/Qwen2-0.5B", compat.QWEN2_05B
+
+    def __init__(self, device, **kw) -> None:
+        self._from_pretrained(device, **kw)
+
+    def _bind(self, model):
+        self.qwen = model.base_model
+        self.final_layer_norm = model.model.norm
+        self.rotary_emb = self.qwen.rotary_emb
+
+    def _embed(self, model, ids):
+        return model.base_model.embed_tokens(ids)
+
+    def _lm_head(self, model):
+        return model.lm_head
+
+    def _final_norm(self, model):
+        return model.model.norm
+
+    def _first_norm_params(self, layer):
+        n = layer.input_layernorm
+        return N.NORM_RMSNORM, n.weight, None, n.variance_epsilon, None, None
+
+    def _run_prenormed_layer(self, layer, resid, normed, normed2, pos):
+        # Qwen2DecoderLayer.forward with input_layernorm already applied
+        attn_out, _ = layer.self_attn(hidden_states=normed, attention_mask=None, position_embeddings=pos)
+        hidden = resid + attn_out
+        return hidden + layer.mlp(layer.post_attention_layernorm(hidden))

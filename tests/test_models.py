@@ -1,0 +1,119 @@
+"""Wrapper drop-in tests: `activation_quantization` of splitq.models against NLLs recorded from the
+reference's own wrappers (tests/golden/wrapper_nll.json, made by oracle/make_golden.py).
+Tolerance from BASELINE.json: perplexity (hence NLL) <= 1e-3 relative."""
+import json
+import math
+import os
+
+import pytest
+import torch
+
+import splitq
+from splitq import compat
+from splitq.models import Pythia70Model, QwenPointFiveBModel
+
+NLL_RTOL = 1e-3
+SPECS = {
+    "pythia_tiny": (Pythia70Model, compat.PYTHIA_TINY),
+    "qwen_tiny": (QwenPointFiveBModel, compat.QWEN2_TINY),
+    "pythia_70m": (Pythia70Model, compat.PYTHIA_70M),
+    "qwen2_05b": (QwenPointFiveBModel, compat.QWEN2_05B),
+}
+
+
+@pytest.fixture(scope="module")
+def book(golden_dir):
+    return json.load(open(os.path.join(golden_dir, "wrapper_nll.json")))
+
+
+def build(name, device, **kw):
+    cls, cfg = SPECS[name]
+    args = ([0, 0.25, 0.5, 0.75, 1],) if cls is Pythia70Model else ()
+    return cls.from_config(device, *args, cfg=cfg, seed=0, **kw)
+
+
+@pytest.mark.parametrize("name", ["pythia_tiny", "qwen_tiny"])
+def test_ratio_zero_and_baseline_match_reference_on_cpu(book, name):
+    """ratio == 0 skips the boundary (pythia_model.py:167); runs without a GPU."""
+    w = build(name, "cpu")
+    ids = torch.tensor([book[name]["ids"]])
+    assert w.num_layers == 3 and w.final_layer_norm is not None and w.rotary_emb is not None
+    for key, want in book[name]["nll"].items():
+        method, loi, ratio = key.split("|")
+        if float(ratio) == 0:
+            got = w.activation_quantization(ids, ids.clone(), torch.zeros(ids.shape[1]), 0, int(loi)).item()
+            assert got == pytest.approx(want, rel=1e-6)
+    assert w.layer_by_layer_impl(ids, ids.clone()).item() == pytest.approx(book[name]["hf_loss"], rel=1e-6)
+
+
+def test_reference_constructor_signature_needs_network():
+    with pytest.raises(RuntimeError) as e:
+        QwenPointFiveBModel("cpu")
+    assert "from_config" in str(e.value)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["pythia_tiny", "qwen_tiny", "pythia_70m", "qwen2_05b"])
+def test_activation_quantization_matches_reference_nll(book, name):
+    dev = "cuda:0"
+    w = build(name, dev)
+    eager = compat.clone_with_attention(w.model, "eager").to(dev)
+    ids = torch.tensor([book[name]["ids"]], device=dev)
+    with torch.no_grad():
+        att = eager(input_ids=ids, output_attentions=True).attentions
+    worst = 0.0
+    for method in ("regular_importance", "last_row"):
+        imp = splitq.get_importance_order(method, att, w.num_layers)
+        for key, want in book[name]["nll"].items():
+            m, loi, ratio = key.split("|")
+            if m != method:
+                continue
+            got = w.activation_quantization(ids, ids.clone(), imp[int(loi)], float(ratio), int(loi))
+            assert got.dim() == 0
+            rel = abs(got.item() - want) / abs(want)
+            worst = max(worst, rel)
+            assert rel <= NLL_RTOL, (key, got.item(), want)
+            assert abs(math.expm1(got.item() - want)) <= NLL_RTOL  # perplexity, relative
+    print(f"{name}: worst relative NLL error {worst:.2e}")
+
+
+@pytest.mark.gpu
+def test_unfused_and_fused_downstream_agree(book):
+    dev = "cuda:0"
+    name = "pythia_70m"
+    fused, plain = build(name, dev), build(name, dev, fuse_norm=False)
+    ids = torch.tensor([book[name]["ids"]], device=dev)
+    imp = torch.rand(ids.shape[1], device=dev)
+    for loi in (0, 2, 5):
+        a = fused.activation_quantization(ids, ids.clone(), imp, 0.5, loi).item()
+        b = plain.activation_quantization(ids, ids.clone(), imp, 0.5, loi).item()
+        assert a == pytest.approx(b, rel=1e-5)
+    assert fused.last_payload_bytes == splitq.payload_bytes(ids.shape[1], 512, [(ids.shape[1] // 2, 4)], 0)
+
+
+@pytest.mark.gpu
+def test_ladder_and_token_scale_extension_runs_and_degrades_gracefully(book):
+    dev = "cuda:0"
+    name = "qwen_tiny"
+    ids = torch.tensor([book[name]["ids"]], device=dev)
+    imp = torch.rand(ids.shape[1], device=dev)
+    base = build(name, dev).activation_quantization(ids, ids.clone(), imp, 0, 1).item()
+    ext = build(name, dev, scale_mode="token", ladder_fracs=[(1 / 3, 2), (1 / 3, 4), (1 / 3, 8)])
+    nll = ext.activation_quantization(ids, ids.clone(), imp, 0.75, 1).item()
+    assert math.isfinite(nll) and abs(nll - base) / base < 0.05
+
+
+@pytest.mark.gpu
+def test_two_device_split_equals_single_device(book):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    name = "pythia_70m"
+    one = build(name, "cuda:0")
+    two = build(name, "cuda:0", split_devices=("cuda:0", "cuda:1"))
+    ids = torch.tensor([book[name]["ids"]], device="cuda:0")
+    imp = torch.rand(ids.shape[1], device="cuda:0")
+    for ratio in (0, 0.5):
+        a = one.activation_quantization(ids, ids.clone(), imp, ratio, 2)
+        b = two.activation_quantization(ids, ids.clone(), imp, ratio, 2)
+        assert b.device.index == 1
+        assert a.item() == pytest.approx(b.item(), rel=1e-6)
