@@ -74,6 +74,26 @@ int splitq_importance_colmean(const float* A, int B, int H, int Sq, int Sk, cons
                               float* out_col, float* out_last, void* ws, size_t ws_bytes,
                               unsigned flags, splitq_stream_t stream);
 
+/* ---- fused importance from Q and K (K2) ------------------------------------------------
+ * Replaces the materialisation of attention probabilities by HF eager attention
+ * (output_attentions=True, Pythia-70M/last_row_exp.py:92-95, Qwen2-0.5B/main.py:158-160) AND the
+ * reductions above: column-mean and last-row importance straight from the post-RoPE query/key
+ * states of one layer, two tcgen05 passes (row log-sum-exp, then column sums of exp(s - lse));
+ * the (S,S) matrix is never written.  out_col / out_last as for splitq_importance_colmean.
+ *   Q (B,H,S,hd), K (B,KVH,S,hd): fp32, head_dim contiguous, element strides of (b, head, s) in
+ *   q_strides_host[3] / k_strides_host[3] (so HF's transposed views need no copy); hd must be 64.
+ *   scaling = head_dim^-0.5; causal != 0 applies the lower-triangular mask.
+ *   mode: SPLITQ_FUSED_TF32X3 (hi/lo split, ~fp32 accuracy, meets 1e-5) or SPLITQ_FUSED_TF32X1.
+ *   ws: 256-byte aligned scratch of splitq_importance_fused_workspace_bytes(). */
+#define SPLITQ_FUSED_TF32X3 0
+#define SPLITQ_FUSED_TF32X1 1
+size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd);
+int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
+                            const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
+                            float scaling, int causal, int mode, const float* head_w_host,
+                            float* out_col, float* out_last, void* ws, size_t ws_bytes,
+                            splitq_stream_t stream);
+
 /* ---- selection (K3a) -------------------------------------------------------------------
  * Replaces torch.argsort(importance)[:int(ratio*S)] (Pythia-70M/pythia_model.py:169-170,
  * Qwen2-0.5B/qwen_layer_wise.py:57), generalised to a ladder: the ladder_k_host[0] least

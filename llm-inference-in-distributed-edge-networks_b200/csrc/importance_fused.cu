@@ -1,0 +1,558 @@
+// K2: fused attention-importance scoring -- the S x S probability matrix never reaches HBM.
+//
+// Reference: HF eager attention materialises softmax(Q K^T * scaling + causal mask) for every
+// layer (third-party transformers eager_attention_forward; reference call sites
+// Experiments/Pythia-70M/last_row_exp.py:92-95, Experiments/Qwen2-0.5B/main.py:158-160) only so
+// that get_importance_order can reduce it to one score per token (last_row_exp.py:13-30).
+// Here the same scores are computed from the post-RoPE Q and K directly, flash-style, in two
+// tensor-core passes:
+//   pass 1  row block I (128 queries) x key blocks J<=I : S = Q_I K_J^T  -> per-row log-sum-exp
+//   pass 2  key block J (128 keys) x query blocks I>=J  : S^T = K_J Q_I^T -> p = exp(s - lse_i),
+//           summed over queries per key (one TMEM lane = one key: no cross-thread reduction)
+// QK^T runs on tcgen05 (kind::tf32, accumulators in TMEM, operands staged by TMA with 128-byte
+// swizzle).  The reference computes QK^T in true fp32; a single TF32 product misses the 1e-5
+// importance tolerance for trained-scale logits, so operands are pre-split into tf32 hi + lo
+// parts and each tile accumulates lo*hi + hi*lo + hi*hi (3xTF32); SPLITQ_FUSED_TF32X1 keeps only
+// hi*hi.  Warp roles per CTA: 0 = TMA producer, 1 = MMA issuer (+TMEM alloc), 2..5 = epilogue.
+#include <cuda.h>
+#include <math.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace splitq {
+namespace k2 {
+
+constexpr int kTile = 128;
+constexpr int kHd = 64;
+constexpr uint32_t kSlabBytes = 128 * 128;           // 128 rows x 32 fp32: one swizzle-128B slab
+constexpr uint32_t kPartBytes = 2 * kSlabBytes;      // 128 x 64 fp32 (hi or lo part)
+constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // hi + lo
+constexpr int kStages = 2;                           // ring of streamed operand tiles
+constexpr int kAcc = 2;                              // TMEM accumulator buffers
+constexpr int kThreads = 192;
+constexpr uint32_t kTmemCols = 256;
+constexpr uint32_t kBarOff = (1 + kStages) * kOperandBytes;
+constexpr uint32_t kLseOff = kBarOff + 128;
+constexpr uint32_t kSmemBytes = kLseOff + kAcc * kTile * 4 + 1024;  // + alignment slack
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        if (clock64() - t0 > 4000000000LL) {  // ~2 s: a protocol bug must fault, not hang the GPU
+            printf("splitq K2: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x,
+                   threadIdx.x, bar, parity);
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {32 fp32, 128 rows} TMA box writes)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::tf32, fp32 accumulate, A and B K-major, M = N = 128
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+
+struct Params {
+    int pass;          // 1 = row LSE, 2 = column sums
+    int B, H, KVH, S, nb;
+    int causal, x3;
+    float cs;          // scaling * log2(e)
+    float* lse2;       // (B,H,S) log2-domain log-sum-exp
+    float* part_col;   // (B,H,S) sum_i p[i][j]
+    float* part_last;  // (B,H,S) p[S-1][j]
+};
+
+// Static schedule shared by all warp roles: items ranked by cost (tiles), dealt serpentine.
+struct Item {
+    int bh, blk, t0, t1;  // streamed block range [t0, t1)
+};
+__device__ __forceinline__ bool item_at(const Params& p, int k, Item& it) {
+    const int G = gridDim.x, c = blockIdx.x;
+    const long long total = (long long)p.B * p.H * p.nb;
+    const long long r = (long long)k * G + ((k & 1) ? (G - 1 - c) : c);
+    if (r >= total) return false;
+    const int BH = p.B * p.H;
+    const int rank = (int)(r / BH);
+    it.bh = (int)(r % BH);
+    if (p.pass == 1) {
+        it.blk = p.nb - 1 - rank;  // most key blocks first
+        it.t0 = 0;
+        it.t1 = p.causal ? it.blk + 1 : p.nb;
+    } else {
+        it.blk = rank;             // most query blocks first
+        it.t0 = p.causal ? it.blk : 0;
+        it.t1 = p.nb;
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid_constant__ CUtensorMap mapQlo,
+                        const __grid_constant__ CUtensorMap mapKhi, const __grid_constant__ CUtensorMap mapKlo,
+                        const Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t fixed_s = base;
+    const uint32_t stage_s = base + kOperandBytes;
+    const uint32_t bar0 = base + kBarOff;
+    const uint32_t bar_fixed_full = bar0, bar_fixed_empty = bar0 + 8;
+    const uint32_t bar_full = bar0 + 16, bar_empty = bar0 + 16 + 8 * kStages;
+    const uint32_t bar_tfull = bar_empty + 8 * kStages, bar_tempty = bar_tfull + 8 * kAcc;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 120);
+    float* lse_s = reinterpret_cast<float*>(gen + kLseOff);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t part_tx = p.x3 ? kOperandBytes : kPartBytes;
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar_fixed_full, 1);
+        mbar_init(bar_fixed_empty, 1);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int a = 0; a < kAcc; ++a) {
+            mbar_init(bar_tfull + 8 * a, 1);
+            mbar_init(bar_tempty + 8 * a, 4);  // one arrive per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const CUtensorMap* fix_hi = p.pass == 1 ? &mapQhi : &mapKhi;
+    const CUtensorMap* fix_lo = p.pass == 1 ? &mapQlo : &mapKlo;
+    const CUtensorMap* str_hi = p.pass == 1 ? &mapKhi : &mapQhi;
+    const CUtensorMap* str_lo = p.pass == 1 ? &mapKlo : &mapQlo;
+    const int group = p.H / p.KVH;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t stage = 0, sphase = 0, fphase = 0;
+            Item it;
+            for (int k = 0; item_at(p, k, it); ++k) {
+                const int b = it.bh / p.H, h = it.bh % p.H;
+                const int q_idx = it.bh, k_idx = b * p.KVH + h / group;
+                const int fix_idx = p.pass == 1 ? q_idx : k_idx;
+                const int str_idx = p.pass == 1 ? k_idx : q_idx;
+                mbar_wait(bar_fixed_empty, fphase ^ 1);
+                mbar_expect_tx(bar_fixed_full, part_tx);
+                tma_load_3d(fixed_s, fix_hi, bar_fixed_full, 0, it.blk * kTile, fix_idx);
+                tma_load_3d(fixed_s + kSlabBytes, fix_hi, bar_fixed_full, 32, it.blk * kTile, fix_idx);
+                if (p.x3) {
+                    tma_load_3d(fixed_s + kPartBytes, fix_lo, bar_fixed_full, 0, it.blk * kTile, fix_idx);
+                    tma_load_3d(fixed_s + kPartBytes + kSlabBytes, fix_lo, bar_fixed_full, 32, it.blk * kTile, fix_idx);
+                }
+                fphase ^= 1;
+                for (int t = it.t0; t < it.t1; ++t) {
+                    const uint32_t dst = stage_s + stage * kOperandBytes;
+                    const uint32_t fb = bar_full + 8 * stage;
+                    mbar_wait(bar_empty + 8 * stage, sphase ^ 1);
+                    mbar_expect_tx(fb, part_tx);
+                    tma_load_3d(dst, str_hi, fb, 0, t * kTile, str_idx);
+                    tma_load_3d(dst + kSlabBytes, str_hi, fb, 32, t * kTile, str_idx);
+                    if (p.x3) {
+                        tma_load_3d(dst + kPartBytes, str_lo, fb, 0, t * kTile, str_idx);
+                        tma_load_3d(dst + kPartBytes + kSlabBytes, str_lo, fb, 32, t * kTile, str_idx);
+                    }
+                    if (++stage == kStages) { stage = 0; sphase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            uint32_t stage = 0, sphase = 0, fphase = 0, acc = 0, aphase = 0;
+            Item it;
+            for (int k = 0; item_at(p, k, it); ++k) {
+                mbar_wait(bar_fixed_full, fphase);
+                fphase ^= 1;
+                for (int t = it.t0; t < it.t1; ++t) {
+                    mbar_wait(bar_full + 8 * stage, sphase);
+                    mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
+                    tc_fence_after();
+                    const uint32_t d = tmem_base + acc * kTile;
+                    const uint32_t sb = stage_s + stage * kOperandBytes;
+                    uint32_t first = 0;
+                    // (fixed part, streamed part): lo*hi, hi*lo, hi*hi -- small terms first
+                    const int nprod = p.x3 ? 3 : 1;
+                    for (int pr = 0; pr < nprod; ++pr) {
+                        const uint32_t fpart = (p.x3 && pr == 0) ? kPartBytes : 0u;
+                        const uint32_t spart = (p.x3 && pr == 1) ? kPartBytes : 0u;
+#pragma unroll
+                        for (int kk = 0; kk < 8; ++kk) {
+                            const uint32_t koff = (kk >> 2) * kSlabBytes + (kk & 3) * 32u;
+                            tc_mma_tf32(d, umma_desc(fixed_s + fpart + koff), umma_desc(sb + spart + koff), kIdesc, first);
+                            first = 1;
+                        }
+                    }
+                    tc_commit(bar_empty + 8 * stage);   // smem stage reusable once these MMAs retire
+                    tc_commit(bar_tfull + 8 * acc);     // accumulator ready for the epilogue
+                    if (++stage == kStages) { stage = 0; sphase ^= 1; }
+                    if (++acc == kAcc) { acc = 0; aphase ^= 1; }
+                }
+                tc_commit(bar_fixed_empty);             // fixed operand reusable
+            }
+        }
+    } else {
+        // ===== epilogue: one TMEM lane (= one row of the tile) per thread =====
+        const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
+        const int row = q4 * 32 + lane;
+        const int et = threadIdx.x - 64;            // 0..127 among epilogue threads
+        const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+        uint32_t acc = 0, aphase = 0;
+        Item it;
+        for (int k = 0; item_at(p, k, it); ++k) {
+            const int g = it.blk * kTile + row;     // global index of this thread's row
+            float m = -INFINITY, l = 0.f;           // pass 1
+            float colsum = 0.f, lastp = 0.f;        // pass 2
+            for (int t = it.t0; t < it.t1; ++t) {
+                float* lse_t = lse_s + acc * kTile;
+                if (p.pass == 2) {
+                    const int qi = t * kTile + et;
+                    lse_t[et] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+                mbar_wait(bar_tfull + 8 * acc, aphase);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + acc * kTile + lane_addr;
+                const int c0 = t * kTile;           // global index of tile column 0
+                const bool edge = (p.causal && t == it.blk) || (c0 + kTile > p.S);
+                if (p.pass == 1) {
+                    // columns = keys; valid iff key < S and (not causal or key <= query g)
+                    const int jmax = min(p.S - 1, p.causal ? g : p.S - 1);
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        float v[32];
+                        tc_ld32(taddr + c * 32, v);
+                        if (edge) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (c0 + c * 32 + i > jmax) v[i] = -INFINITY;
+                        }
+                        float cm = v[0];
+#pragma unroll
+                        for (int i = 1; i < 32; ++i) cm = fmaxf(cm, v[i]);
+                        const float mn = fmaxf(m, cm * p.cs);
+                        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 32; i += 2) {
+                            s0 += ex2(fmaf(v[i], p.cs, -mn));
+                            s1 += ex2(fmaf(v[i + 1], p.cs, -mn));
+                        }
+                        l = l * ex2(m - mn) + (s0 + s1);
+                        m = mn;
+                    }
+                } else {
+                    // columns = queries; valid iff query < S (lse = +inf otherwise) and query >= key g
+                    const bool has_last = (p.S - 1) / kTile == t;
+                    const int last_col = (p.S - 1) % kTile;
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        float v[32];
+                        tc_ld32(taddr + c * 32, v);
+                        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            const float4 ls = *reinterpret_cast<const float4*>(lse_t + c * 32 + i);
+                            float p0 = ex2(fmaf(v[i + 0], p.cs, -ls.x));
+                            float p1 = ex2(fmaf(v[i + 1], p.cs, -ls.y));
+                            float p2 = ex2(fmaf(v[i + 2], p.cs, -ls.z));
+                            float p3 = ex2(fmaf(v[i + 3], p.cs, -ls.w));
+                            if (edge && p.causal) {
+                                const int qi = c0 + c * 32 + i;
+                                if (qi + 0 < g) p0 = 0.f;
+                                if (qi + 1 < g) p1 = 0.f;
+                                if (qi + 2 < g) p2 = 0.f;
+                                if (qi + 3 < g) p3 = 0.f;
+                            }
+                            if (has_last) {
+                                const int li = last_col - (c * 32 + i);
+                                if (li == 0) lastp = p0;
+                                if (li == 1) lastp = p1;
+                                if (li == 2) lastp = p2;
+                                if (li == 3) lastp = p3;
+                            }
+                            s0 += p0 + p1;
+                            s1 += p2 + p3;
+                        }
+                        colsum += s0 + s1;
+                    }
+                }
+                // accumulator buffer drained: hand it back to the MMA warp
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                if (++acc == kAcc) { acc = 0; aphase ^= 1; }
+            }
+            if (g < p.S) {
+                const size_t o = (size_t)it.bh * p.S + g;
+                if (p.pass == 1) {
+                    p.lse2[o] = m + log2f(l);
+                } else {
+                    p.part_col[o] = colsum;
+                    p.part_last[o] = lastp;
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
+// ---- operand preparation: fp32 -> tf32 hi + tf32 lo, gathered from arbitrary (b,h,s) strides ----
+__device__ __forceinline__ float tf32_rn(float x) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    return __uint_as_float(u);
+}
+__global__ void __launch_bounds__(256)
+split_tf32_kernel(const float* __restrict__ x, long long sb, long long sh, long long ss, int heads, int S,
+                  long long total4, float* __restrict__ hi, float* __restrict__ lo, int vec) {
+    // one thread per 4 consecutive head-dim elements; output is dense (B,heads,S,64)
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int d4 = (int)(i % (kHd / 4));
+        const long long row = i / (kHd / 4);
+        const int s = (int)(row % S);
+        const long long bh = row / S;
+        const int h = (int)(bh % heads);
+        const long long b = bh / heads;
+        const float* src = x + b * sb + h * sh + s * ss + d4 * 4;
+        float4 v;
+        if (vec) v = __ldg(reinterpret_cast<const float4*>(src));
+        else v = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), __ldg(src + 3));
+        float4 a, r;
+        a.x = tf32_rn(v.x); a.y = tf32_rn(v.y); a.z = tf32_rn(v.z); a.w = tf32_rn(v.w);
+        r.x = tf32_rn(v.x - a.x); r.y = tf32_rn(v.y - a.y); r.z = tf32_rn(v.z - a.z); r.w = tf32_rn(v.w - a.w);
+        reinterpret_cast<float4*>(hi)[i] = a;
+        reinterpret_cast<float4*>(lo)[i] = r;
+    }
+}
+
+struct HeadW {
+    float w[SPLITQ_MAX_HEADS];
+};
+__global__ void __launch_bounds__(256)
+fused_finalize_kernel(const float* __restrict__ part_col, const float* __restrict__ part_last, int H, int S, HeadW hw,
+                      float* __restrict__ out_col, float* __restrict__ out_last) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
+    if (j >= S) return;
+    float c = 0.f, l = 0.f;
+    for (int h = 0; h < H; ++h) {
+        const size_t o = ((size_t)b * H + h) * S + j;
+        c += hw.w[h] * part_col[o];
+        l += hw.w[h] * part_last[o];
+    }
+    if (out_col) out_col[(size_t)b * S + j] = c / (float)S;
+    if (out_last) out_last[(size_t)b * S + j] = l;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// (64, S, n) fp32 tensor, box = 32 x 128 x 1, 128-byte swizzle, rows past S read as zero
+static int make_map(CUtensorMap* map, float* base, int S, long long n) {
+    EncodeTiledFn enc = encode_fn();
+    SPLITQ_REQUIRE(enc != nullptr, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled is unavailable");
+    cuuint64_t dims[3] = {(cuuint64_t)kHd, (cuuint64_t)S, (cuuint64_t)n};
+    cuuint64_t strides[2] = {(cuuint64_t)kHd * 4, (cuuint64_t)S * kHd * 4};
+    cuuint32_t box[3] = {32, (cuuint32_t)kTile, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    SPLITQ_REQUIRE(r == CUDA_SUCCESS, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return SPLITQ_OK;
+}
+
+static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
+
+struct WsLayout {
+    size_t qhi, qlo, khi, klo, lse, pcol, plast, total;
+};
+static WsLayout ws_layout(int B, int H, int KVH, int S) {
+    WsLayout w;
+    const size_t q = align256((size_t)B * H * S * kHd * 4), k = align256((size_t)B * KVH * S * kHd * 4);
+    const size_t v = align256((size_t)B * H * S * 4);
+    w.qhi = 0; w.qlo = q; w.khi = 2 * q; w.klo = 2 * q + k;
+    w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + v; w.total = w.plast + v;
+    return w;
+}
+
+}  // namespace k2
+}  // namespace splitq
+
+using namespace splitq;
+using namespace splitq::k2;
+
+extern "C" size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd) {
+    if (B <= 0 || H <= 0 || KVH <= 0 || S <= 0 || hd != kHd) return 0;
+    return ws_layout(B, H, KVH, S).total;
+}
+
+extern "C" int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
+                                       const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
+                                       float scaling, int causal, int mode, const float* head_w_host,
+                                       float* out_col, float* out_last, void* ws, size_t ws_bytes,
+                                       splitq_stream_t stream) {
+    SPLITQ_REQUIRE(Q && K && (out_col || out_last) && q_strides_host && k_strides_host, SPLITQ_ERR_ARG,
+                   "importance_fused: NULL argument");
+    SPLITQ_REQUIRE(B > 0 && H > 0 && KVH > 0 && S > 0 && H % KVH == 0 && H <= SPLITQ_MAX_HEADS, SPLITQ_ERR_ARG,
+                   "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
+    SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
+                   "materialised path splitq_importance_colmean", hd);
+    SPLITQ_REQUIRE(mode == SPLITQ_FUSED_TF32X3 || mode == SPLITQ_FUSED_TF32X1, SPLITQ_ERR_ARG,
+                   "importance_fused: unknown mode %d", mode);
+    SPLITQ_REQUIRE(scaling > 0.f, SPLITQ_ERR_ARG, "importance_fused: scaling must be positive");
+    const WsLayout wl = ws_layout(B, H, KVH, S);
+    SPLITQ_REQUIRE(ws && ws_bytes >= wl.total, SPLITQ_ERR_WORKSPACE, "importance_fused: workspace %zu < %zu bytes",
+                   ws_bytes, wl.total);
+    SPLITQ_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255u) == 0, SPLITQ_ERR_ALIGN,
+                   "importance_fused: workspace must be 256-byte aligned");
+    if (int rc = check_arch()) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t* w8 = (uint8_t*)ws;
+    float *qhi = (float*)(w8 + wl.qhi), *qlo = (float*)(w8 + wl.qlo), *khi = (float*)(w8 + wl.khi),
+          *klo = (float*)(w8 + wl.klo);
+
+    {   // operand split
+        const long long tq = (long long)B * H * S * (kHd / 4), tk = (long long)B * KVH * S * (kHd / 4);
+        auto vec_ok = [](const float* p, const long long* s) {
+            return aligned16(p) && s[0] % 4 == 0 && s[1] % 4 == 0 && s[2] % 4 == 0;
+        };
+        split_tf32_kernel<<<(unsigned)std::min<long long>((tq + 255) / 256, 148 * 16), 256, 0, st>>>(
+            Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S, tq, qhi, qlo, vec_ok(Q, q_strides_host));
+        split_tf32_kernel<<<(unsigned)std::min<long long>((tk + 255) / 256, 148 * 16), 256, 0, st>>>(
+            K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH, S, tk, khi, klo, vec_ok(K, k_strides_host));
+        SPLITQ_LAUNCH_CHECK("split_tf32_kernel");
+    }
+
+    CUtensorMap mqh, mql, mkh, mkl;
+    if (int rc = make_map(&mqh, qhi, S, (long long)B * H)) return rc;
+    if (int rc = make_map(&mql, qlo, S, (long long)B * H)) return rc;
+    if (int rc = make_map(&mkh, khi, S, (long long)B * KVH)) return rc;
+    if (int rc = make_map(&mkl, klo, S, (long long)B * KVH)) return rc;
+
+    Params p;
+    p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = cdiv(S, kTile);
+    p.causal = causal ? 1 : 0;
+    p.x3 = mode == SPLITQ_FUSED_TF32X3;
+    p.cs = scaling * 1.4426950408889634f;
+    p.lse2 = (float*)(w8 + wl.lse);
+    p.part_col = (float*)(w8 + wl.pcol);
+    p.part_last = (float*)(w8 + wl.plast);
+
+    static bool attr_set[64] = {};
+    int dev = 0, sms = 148;
+    SPLITQ_CUDA(cudaGetDevice(&dev));
+    SPLITQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (dev < 64 && !attr_set[dev]) {
+        SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_set[dev] = true;
+    }
+    const long long items = (long long)B * H * p.nb;
+    const int grid = (int)std::min<long long>(items, sms);
+    for (int pass = 1; pass <= 2; ++pass) {
+        p.pass = pass;
+        fused_importance_kernel<<<grid, kThreads, kSmemBytes, st>>>(mqh, mql, mkh, mkl, p);
+        SPLITQ_LAUNCH_CHECK("fused_importance_kernel");
+    }
+    HeadW hw;
+    for (int h = 0; h < H; ++h) hw.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
+    dim3 fg(cdiv(S, 256), B);
+    fused_finalize_kernel<<<fg, 256, 0, st>>>(p.part_col, p.part_last, H, S, hw, out_col, out_last);
+    SPLITQ_LAUNCH_CHECK("fused_finalize_kernel");
+    return SPLITQ_OK;
+}

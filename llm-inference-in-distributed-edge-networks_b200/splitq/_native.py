@@ -18,10 +18,12 @@ NORM_LAYERNORM, NORM_RMSNORM = 0, 1
 FLAG_CAUSAL_HINT = 1
 MAX_SELECT_S = 32768
 NOALLOC_MAX_WINDOWS = 1024
+FUSED_TF32X3, FUSED_TF32X1 = 0, 1
 
 _vp, _sz, _i, _u = C.c_void_p, C.c_size_t, C.c_int, C.c_uint
 _ip = C.POINTER(C.c_int)
 _fp = C.POINTER(C.c_float)
+_llp = C.POINTER(C.c_longlong)
 
 # name -> (restype, argtypes); must list every symbol include/splitq.h declares
 SIGNATURES = {
@@ -29,6 +31,9 @@ SIGNATURES = {
     "splitq_last_error": (C.c_char_p, []),
     "splitq_importance_colmean_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "splitq_importance_colmean": (_i, [_vp, _i, _i, _i, _i, _fp, _vp, _vp, _vp, _sz, _u, _vp]),
+    "splitq_importance_fused_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "splitq_importance_fused": (_i, [_vp, _llp, _vp, _llp, _i, _i, _i, _i, _i, C.c_float, _i, _i, _fp, _vp, _vp, _vp,
+                                     _sz, _vp]),
     "splitq_select_bits": (_i, [_vp, _i, _i, _i, _ip, _ip, _i, _vp, _vp, _vp]),
     "splitq_payload_bytes": (_sz, [_i, _i, _ip, _ip, _i, _i]),
     "splitq_quant_pack_workspace_bytes": (_sz, [_i, _i, _i, _i]),

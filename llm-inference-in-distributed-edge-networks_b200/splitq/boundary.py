@@ -106,6 +106,37 @@ def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]]
     return (out_col if want_col else None), (out_last if want_last else None)
 
 
+def importance_fused(q: torch.Tensor, k: torch.Tensor, scaling: float, causal: bool = True,
+                     mode: int = N.FUSED_TF32X3, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
+                     want_last: bool = False, out_col: Optional[torch.Tensor] = None,
+                     out_last: Optional[torch.Tensor] = None):
+    """q: (B,H,S,64), k: (B,KVH,S,64) post-RoPE fp32 CUDA tensors (any batch/head/seq strides, e.g.
+    HF's `.view(...).transpose(1, 2)`) -> (col (B,S) or None, last (B,S) or None) without ever
+    materialising the (S,S) attention matrix."""
+    for name, t in (("q", q), ("k", k)):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.dim() == 4 and t.stride(3) == 1):
+            raise N.SplitqError(f"{name}: expected a 4-d float32 CUDA tensor with contiguous head_dim")
+    B, H, S, hd = q.shape
+    KVH = k.shape[1]
+    lib = N.load()
+    if want_col and out_col is None:
+        out_col = torch.empty(B, S, dtype=torch.float32, device=q.device)
+    if want_last and out_last is None:
+        out_last = torch.empty(B, S, dtype=torch.float32, device=q.device)
+    ws_bytes = lib.splitq_importance_fused_workspace_bytes(B, H, KVH, S, hd)
+    if ws_bytes == 0:
+        raise N.SplitqError(f"importance_fused: unsupported shape q={tuple(q.shape)} k={tuple(k.shape)} (head_dim 64 only)")
+    ws = _WS.get(q.device, "fused", ws_bytes)
+    hw = N.float_array([float(x) for x in head_w]) if head_w is not None else None
+    qs = (C.c_longlong * 3)(q.stride(0), q.stride(1), q.stride(2))
+    ks = (C.c_longlong * 3)(k.stride(0), k.stride(1), k.stride(2))
+    with torch.cuda.device(q.device):
+        N.check(lib.splitq_importance_fused(_ptr(q), qs, _ptr(k), ks, B, H, KVH, S, hd, float(scaling), int(causal),
+                                            mode, hw, _ptr(out_col if want_col else None),
+                                            _ptr(out_last if want_last else None), _ptr(ws), ws_bytes, _stream(q)))
+    return (out_col if want_col else None), (out_last if want_last else None)
+
+
 def select_bits(imp: torch.Tensor, ladder: Ladder, D: int, bits_out: Optional[torch.Tensor] = None,
                 row_off_out: Optional[torch.Tensor] = None):
     """imp: (B,S) or (S,) -> (bits u8 (B,S), row_off u32-as-int32 (B,S))."""

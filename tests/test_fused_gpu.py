@@ -1,0 +1,88 @@
+"""K2 (fused tcgen05 importance from Q,K) against the oracle's eager attention + reference
+reductions.  Tolerance: importance <= 1e-5 relative in 3xTF32 mode (BASELINE.json north_star)."""
+import pytest
+import torch
+
+import splitq
+import splitq_oracle as O
+from splitq import _native as N
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def make_qk(gen, B, H, KVH, S, sigma, hf_layout=False):
+    hd = 64
+    if hf_layout:  # (B,S,H,hd) storage viewed as (B,H,S,hd), like q_proj(...).view(...).transpose(1, 2)
+        q = (torch.randn(B, S, H, hd, generator=gen) * sigma).transpose(1, 2)
+        k = (torch.randn(B, S, KVH, hd, generator=gen) * sigma).transpose(1, 2)
+    else:
+        q = torch.randn(B, H, S, hd, generator=gen) * sigma
+        k = torch.randn(B, KVH, S, hd, generator=gen) * sigma
+    return q, k
+
+
+def oracle_scores(q, k, causal):
+    A = O.attention_probs(q.contiguous(), k.contiguous(), 64 ** -0.5, causal)
+    col = torch.stack([O.importance_regular(A[b:b + 1]) for b in range(A.shape[0])])
+    last = torch.stack([O.importance_last_row(A[b:b + 1]) for b in range(A.shape[0])])
+    return col, last
+
+
+def max_rel(got, want):
+    return ((got - want).abs() / want.abs().clamp_min(1e-30)).max().item()
+
+
+@pytest.mark.parametrize("B,H,KVH,S", [(1, 2, 1, 128), (1, 4, 2, 256), (2, 8, 8, 384), (1, 14, 2, 512),
+                                        (1, 3, 3, 200), (2, 2, 1, 77), (1, 2, 2, 1000), (1, 1, 1, 1)])
+@pytest.mark.parametrize("sigma", [0.4, 1.0, 1.5])
+def test_fused_matches_eager_attention_importance(B, H, KVH, S, sigma):
+    gen = torch.Generator().manual_seed(S * 31 + H)
+    q, k = make_qk(gen, B, H, KVH, S, sigma, hf_layout=(S % 2 == 0))
+    col, last = splitq.importance_fused(q.to(DEV), k.to(DEV), 64 ** -0.5, causal=True, want_last=True)
+    torch.cuda.synchronize()
+    want_col, want_last = oracle_scores(q, k, True)
+    assert max_rel(col.cpu(), want_col) <= 1e-5
+    assert max_rel(last.cpu(), want_last) <= 1e-5
+
+
+def test_fused_non_causal_and_head_weights():
+    gen = torch.Generator().manual_seed(5)
+    q, k = make_qk(gen, 1, 4, 2, 300, 1.0)
+    w = [0.5, -0.25, 1.5, 0.1]
+    col, last = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, causal=False, head_w=w, want_last=True)
+    A = O.attention_probs(q, k, 0.125, causal=False)
+    want = O.importance_weighted(A, w)
+    assert ((col[0].cpu() - want).abs().max() / want.abs().max()).item() <= 1e-5
+    want_last = sum(w[h] * A[0, h, -1] for h in range(4))
+    assert ((last[0].cpu() - want_last).abs().max() / want_last.abs().max()).item() <= 1e-5
+
+
+def test_fused_single_tf32_mode_is_close_but_looser():
+    gen = torch.Generator().manual_seed(6)
+    q, k = make_qk(gen, 1, 4, 4, 512, 1.0)
+    col, _ = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, mode=N.FUSED_TF32X1)
+    want, _ = oracle_scores(q, k, True)
+    assert max_rel(col.cpu(), want) <= 2e-2
+
+
+def test_fused_equals_materialised_kernel_on_gpu_attention():
+    """K2 vs fp64 eager probabilities at a size the CPU oracle would be slow on."""
+    gen = torch.Generator(device=DEV).manual_seed(9)
+    B, H, KVH, S = 1, 14, 2, 2048
+    q = torch.randn(B, H, S, 64, device=DEV, generator=gen)
+    k = torch.randn(B, KVH, S, 64, device=DEV, generator=gen)
+    kk = k.repeat_interleave(H // KVH, dim=1)
+    s = torch.matmul(q.double(), kk.double().transpose(2, 3)) * 0.125
+    s = s + torch.full((S, S), float("-inf"), device=DEV, dtype=torch.float64).triu(1)
+    A = torch.softmax(s, dim=-1)
+    want_col, want_last = A.mean(dim=1).mean(dim=1).float(), A[:, :, -1].mean(dim=1).float()
+    col, last = splitq.importance_fused(q, k, 0.125, want_last=True)
+    assert max_rel(col, want_col) <= 1e-5
+    assert max_rel(last, want_last) <= 1e-5
+
+
+def test_fused_rejects_other_head_dims():
+    q = torch.zeros(1, 1, 8, 32, device=DEV)
+    with pytest.raises(N.SplitqError):
+        splitq.importance_fused(q, q, 0.1)
