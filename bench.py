@@ -27,14 +27,14 @@ import torch  # noqa: E402
 WORKLOADS = {
     # BASELINE.json configs[2]: largest single-GPU configuration
     "qwen2-0.5b_split12_colmean_s4096_ladder8-4-2": dict(
-        H=14, S=4096, D=896, method="regular_importance", fracs=[(0.25, 2), (0.25, 4), (0.25, 8)],
-        scale_mode=1, B=4),
+        H=14, KVH=2, S=4096, D=896, method="regular_importance", fracs=[(0.25, 2), (0.25, 4), (0.25, 8)],
+        scale_mode=1, B=4, B_fused=8),
     # configs[1] shapes (last-row importance, int4 on the lower half, per-token scale)
     "pythia-70m_split3_lastrow_s2048_int4": dict(
-        H=8, S=2048, D=512, method="last_row", fracs=[(0.5, 4)], scale_mode=1, B=16),
+        H=8, KVH=8, S=2048, D=512, method="last_row", fracs=[(0.5, 4)], scale_mode=1, B=16, B_fused=32),
     # configs[0] shapes, reference-exact quantiser (one scale for the selected set)
     "pythia-70m_split3_colmean_s512_int4group": dict(
-        H=8, S=512, D=512, method="regular_importance", fracs=[(0.5, 4)], scale_mode=0, B=64),
+        H=8, KVH=8, S=512, D=512, method="regular_importance", fracs=[(0.5, 4)], scale_mode=0, B=64, B_fused=128),
 }
 DEFAULT_WORKLOAD = "qwen2-0.5b_split12_colmean_s4096_ladder8-4-2"
 METRIC = "boundary tokens/sec (score+quant+pack+xfer+dequant)"
@@ -116,23 +116,52 @@ def synth_inputs(cfg, B, device, seed):
     return A, h
 
 
-def cpu_reference_leg(cfg, ladder, A_win, h_win, min_seconds, threads):
-    """Times the oracle's vectorised restatement of the reference's CPU path on ONE window."""
+def synth_qk(cfg, B, device, seed):
+    """Post-RoPE-like Q (B,H,S,64) / K (B,KVH,S,64): N(0,1) entries give logits with unit variance
+    after the 1/8 scaling, i.e. trained-like (peaky) attention rows."""
+    gen = torch.Generator(device=device).manual_seed(seed + 77)
+    q = torch.randn(B, cfg["H"], cfg["S"], 64, device=device, generator=gen)
+    k = torch.randn(B, cfg["KVH"], cfg["S"], 64, device=device, generator=gen)
+    return q, k
+
+
+def cpu_pass(O, cfg, ladder, fused, inputs):
+    """One pass of the reference's CPU path over ONE window (oracle restatement, vectorised ATen)."""
+    if fused:
+        q, k, h = inputs
+        return O.reference_boundary_cpu_from_qk(q, k, h.clone(), 64 ** -0.5, ladder, cfg["scale_mode"], cfg["method"])
+    A, h = inputs
+    return O.reference_boundary_cpu(A, h.clone(), ladder, cfg["scale_mode"], cfg["method"])
+
+
+def cpu_reference_leg(cfg, ladder, fused, inputs, min_seconds, threads):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import splitq_oracle as O
 
     torch.set_num_threads(threads)
-    O.reference_boundary_cpu(A_win, h_win.clone(), ladder, cfg["scale_mode"], cfg["method"])  # warm-up
+    cpu_pass(O, cfg, ladder, fused, inputs)  # warm-up
     times = []
     t_end = time.perf_counter() + min_seconds
     while len(times) < 3 or time.perf_counter() < t_end:
-        hh = h_win.clone()
         t0 = time.perf_counter()
-        O.reference_boundary_cpu(A_win, hh, ladder, cfg["scale_mode"], cfg["method"])
+        cpu_pass(O, cfg, ladder, fused, inputs)
         times.append(time.perf_counter() - t0)
         if len(times) >= 200:
             break
     return times
+
+
+def cpu_inputs(cfg, fused, seed=1234):
+    S = cfg["S"]
+    gen = torch.Generator().manual_seed(seed)
+    h = torch.randn(1, S, cfg["D"], generator=gen)
+    if fused:
+        q = torch.randn(1, cfg["H"], S, 64, generator=gen)
+        k = torch.randn(1, cfg["KVH"], S, 64, generator=gen)
+        return q, k, h
+    mask = torch.full((S, S), float("-inf")).triu(1)
+    A = torch.softmax(torch.randn(1, cfg["H"], S, S, generator=gen) * 2.0 + mask, dim=-1)
+    return A, h
 
 
 def run_reference(args, cfg, name):
@@ -141,29 +170,29 @@ def run_reference(args, cfg, name):
     if rank != 0:
         return
     S = cfg["S"]
+    fused = args.importance == "fused"
     ladder = [(int(f * S), b) for f, b in cfg["fracs"]]
     threads = os.cpu_count() or 1
-    gen = torch.Generator().manual_seed(1234)
-    mask = torch.full((S, S), float("-inf")).triu(1)
-    A = torch.softmax(torch.randn(1, cfg["H"], S, S, generator=gen) * 2.0 + mask, dim=-1)
-    h = torch.randn(1, S, cfg["D"], generator=gen)
+    inputs = cpu_inputs(cfg, fused)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import splitq_oracle as O
 
     torch.set_num_threads(threads)
     for _ in range(args.warmup):
-        O.reference_boundary_cpu(A, h.clone(), ladder, cfg["scale_mode"], cfg["method"])
+        cpu_pass(O, cfg, ladder, fused, inputs)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        O.reference_boundary_cpu(A, h.clone(), ladder, cfg["scale_mode"], cfg["method"])
+        cpu_pass(O, cfg, ladder, fused, inputs)
     dt = time.perf_counter() - t0
     value = args.steps * S / dt
-    sample = f"{args.steps} steps x 1 window of {S} tokens (H={cfg['H']}, D={cfg['D']}), torch CPU fp32"
+    start = "Q,K (eager attention probabilities computed on the CPU, as HF eager does)" if fused else "materialised A"
+    sample = (f"{args.steps} steps x 1 window of {S} tokens (H={cfg['H']}, D={cfg['D']}) from {start}, "
+              f"torch CPU fp32")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": name, "windows_per_step": 1, "importance_impl": "materialised"},
+        "config": {"workload": name, "windows_per_step": 1, "importance_impl": args.importance},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -176,18 +205,23 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="splitq", choices=["splitq", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--importance", default="fused", choices=["fused", "materialised"],
+                    help="fused: scores from the split layer's Q,K (K2, no attention matrix); "
+                         "materialised: scores from attention probabilities already in HBM (K1)")
+    ap.add_argument("--fused-mode", default="tf32x3", choices=["tf32x3", "tf32x1"])
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     cfg = WORKLOADS[args.workload]
-    args.warmup = max(args.warmup, 3) if args.impl == "splitq" else args.warmup
     if args.impl == "reference":
         run_reference(args, cfg, args.workload)
         return
+    args.warmup = max(args.warmup, 3)
 
     import splitq
+    from splitq import _native as N
     from splitq.transport import PairExchange
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -202,18 +236,30 @@ def main() -> None:
         dist.init_process_group("nccl", device_id=device)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch N>1 with torchrun)"
 
-    B = args.batch_windows or cfg["B"]
-    H, S, D = cfg["H"], cfg["S"], cfg["D"]
+    fused = args.importance == "fused"
+    B = args.batch_windows or (cfg["B_fused"] if fused else cfg["B"])
+    H, KVH, S, D = cfg["H"], cfg["KVH"], cfg["S"], cfg["D"]
     ladder = splitq.ladder_from_fractions(cfg["fracs"], S)
     plan = splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=cfg["scale_mode"], method=cfg["method"],
-                               src_device=device)
-    A, h = synth_inputs(cfg, B, device, seed=1234 + rank)
+                               src_device=device, KVH=KVH,
+                               fused_mode=N.FUSED_TF32X3 if args.fused_mode == "tf32x3" else N.FUSED_TF32X1)
     plan.transport = PairExchange(rank, world) if world > 1 else None
+    if fused:
+        q, k = synth_qk(cfg, B, device, seed=1234 + rank)
+        gen = torch.Generator(device=device).manual_seed(1234 + rank)
+        h = torch.randn(B, S, D, device=device, generator=gen)
+        h[:, :, torch.randperm(D, device=device, generator=gen)[: max(1, D // 100)]] *= 20.0
+        A = None
+    else:
+        A, h = synth_inputs(cfg, B, device, seed=1234 + rank)
 
     def step(timed_events=None):
         if timed_events is not None:
             timed_events[0].record()
-        plan.score(A)
+        if fused:
+            plan.score_fused(q, k)
+        else:
+            plan.score(A)
         if timed_events is not None:
             timed_events[1].record()
         plan.send(h)
@@ -229,75 +275,103 @@ def main() -> None:
 
     sampler = ClockSampler(local)
     sampler.start()
-    k1_events = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    k_events = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     for i in range(args.steps):
-        step(k1_events[i])
+        step(k_events[i])
     t1.record()
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
         torch.cuda.synchronize()
     elapsed_ms = t0.elapsed_time(t1)
-    k1_ms = sum(a.elapsed_time(b) for a, b in k1_events) / args.steps
+    score_ms = sum(a.elapsed_time(b) for a, b in k_events) / args.steps
 
     # ---- end to end through the public host-buffer API: H2D of the step's inputs, the path, D2H
-    A_host = torch.empty(A.shape, dtype=torch.float32, pin_memory=True)
-    h_host = torch.empty(h.shape, dtype=torch.float32, pin_memory=True)
-    out_host = torch.empty(h.shape, dtype=torch.float32, pin_memory=True)
-    A_host.copy_(A)
-    h_host.copy_(h)
+    pin = lambda t: torch.empty(t.shape, dtype=torch.float32, pin_memory=True).copy_(t)  # noqa: E731
+    h_host, out_host = pin(h), torch.empty(h.shape, dtype=torch.float32, pin_memory=True)
+    if fused:
+        q_host, k_host = pin(q), pin(k)
+        run_e2e = lambda: plan.run_host_fused(q_host, k_host, h_host, out_host)  # noqa: E731
+    else:
+        A_host = pin(A)
+        run_e2e = lambda: plan.run_host(A_host, h_host, out_host)  # noqa: E731
     torch.cuda.synchronize()
-    plan.run_host(A_host, h_host, out_host)
+    run_e2e()
     if dist is not None:
         dist.barrier()
     e0 = time.perf_counter()
     for _ in range(args.e2e_steps):
-        plan.run_host(A_host, h_host, out_host)
+        run_e2e()
     e2e_s = time.perf_counter() - e0
     clocks = sampler.finish()
 
     if dist is not None:
-        t = torch.tensor([elapsed_ms, e2e_s, k1_ms], dtype=torch.float64, device=device)
+        t = torch.tensor([elapsed_ms, e2e_s, score_ms], dtype=torch.float64, device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms, e2e_s, k1_ms = t.tolist()
+        elapsed_ms, e2e_s, score_ms = t.tolist()
 
     if rank == 0:
-        peak, peak_src = load_peaks()
+        peaks = {}
+        path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(path):
+            peaks = json.load(open(path))
         tokens_per_step = world * B * S
         value = tokens_per_step * args.steps / (elapsed_ms * 1e-3)
-        if cfg["method"] == "last_row":
-            alg_bytes = 4 * B * H * S + 4 * B * S
-            kname = "importance_finalize_kernel (last row)"
+        if fused:
+            nb = (S + 127) // 128
+            tiles = B * H * nb * (nb + 1)  # causal tiles, two passes
+            products = 3 if args.fused_mode == "tf32x3" else 1
+            issued = tiles * 2.0 * 128 * 128 * 64 * products
+            dense_equiv = 4.0 * B * H * S * S * 64
+            bf16 = peaks.get("bf16_tflops", 1590.0)
+            achieved = issued / (score_ms * 1e-3) / 1e12
+            roofline = {
+                "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + tf32 split + finalize",
+                "achieved": achieved, "peak": bf16 / 2, "unit": "TFLOP/s", "frac": achieved / (bf16 / 2), "traffic": None,
+                "peak_source": ("MEASURED_PEAKS.json bf16_tflops / 2" if peaks else "fallback 1590 / 2") +
+                               " (kind::tf32 issues at half the bf16 rate)",
+                "flops_counted": "issued tcgen05 tf32 MMA flops: causal tiles x 2 passes x products",
+                "issued_flops_per_launch": issued, "dense_equivalent_tflops": dense_equiv / (score_ms * 1e-3) / 1e12,
+                "kernel_ms": score_ms,
+                "attention_matrix_bytes_avoided": 4 * B * H * S * S}
+            l2_note = f"inputs per step ({4 * B * S * (64 * (H + KVH) + D) / 1e6:.0f} MB) exceed the 126 MB L2; no flush"
         else:
-            alg_bytes = 4 * B * H * S * S + 4 * B * S
-            kname = "colsum_partial_kernel + importance_finalize_kernel"
-        achieved = alg_bytes / (k1_ms * 1e-3) / 1e9
-        h2d, d2h = plan.host_bytes_per_run()
+            peak, peak_src = load_peaks()
+            if cfg["method"] == "last_row":
+                alg_bytes, kname = 4 * B * H * S + 4 * B * S, "importance_finalize_kernel (last row)"
+            else:
+                alg_bytes, kname = 4 * B * H * S * S + 4 * B * S, "colsum_partial_kernel + importance_finalize_kernel"
+            achieved = alg_bytes / (score_ms * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                        "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": score_ms}
+            l2_note = f"inputs per step ({alg_bytes / 1e6:.0f} MB) exceed the 126 MB L2; no flush"
+        h2d, d2h = plan.host_bytes_per_run(fused)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "windows_per_step_per_gpu": B, "H": H, "S": S, "D": D,
+            "config": {"workload": args.workload, "windows_per_step_per_gpu": B, "H": H, "KVH": KVH, "S": S, "D": D,
                        "ladder": ladder, "scale_mode": "token" if cfg["scale_mode"] else "group",
-                       "importance_impl": "materialised", "payload_bytes_per_window": plan.nbytes,
-                       "transfer": "nccl pair exchange" if world > 1 else "device-to-device copy",
-                       "l2": f"inputs per step ({alg_bytes / 1e6:.0f} MB) exceed the 126 MB L2; no flush"},
-            "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k1_ms},
+                       "importance_impl": args.importance + (f" ({args.fused_mode})" if fused else ""),
+                       "payload_bytes_per_window": plan.nbytes,
+                       "transfer": "nccl pair exchange" if world > 1 else "device-to-device copy", "l2": l2_note},
+            "roofline": roofline,
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps},
-            "gpu_launches": plan.launches_per_run() * args.steps,
+            "gpu_launches": plan.launches_per_run(fused) * args.steps,
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            times = cpu_reference_leg(cfg, ladder, A[0:1].cpu(), h[0:1].cpu(), args.cpu_seconds, threads)
+            inputs = (q[0:1].cpu(), k[0:1].cpu(), h[0:1].cpu()) if fused else (A[0:1].cpu(), h[0:1].cpu())
+            times = cpu_reference_leg(cfg, ladder, fused, inputs, args.cpu_seconds, threads)
             out["cpu_baseline"] = {
                 "value": S / statistics.mean(times), "unit": UNIT, "cores": threads, "kind": "port",
-                "sample": f"{len(times)} passes over 1 window of {S} tokens (same H, D, ladder), torch CPU fp32, "
+                "sample": f"{len(times)} passes over 1 window of {S} tokens (same H, D, ladder; starts from "
+                          f"{'Q,K' if fused else 'materialised attention'}), torch CPU fp32, "
                           f"mean {1e3 * statistics.mean(times):.1f} ms/window"}
         print(json.dumps(out))
     if dist is not None:

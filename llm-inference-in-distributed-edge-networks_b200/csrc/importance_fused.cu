@@ -13,7 +13,7 @@
 // swizzle).  The reference computes QK^T in true fp32; a single TF32 product misses the 1e-5
 // importance tolerance for trained-scale logits, so operands are pre-split into tf32 hi + lo
 // parts and each tile accumulates lo*hi + hi*lo + hi*hi (3xTF32); SPLITQ_FUSED_TF32X1 keeps only
-// hi*hi.  Warp roles per CTA: 0 = TMA producer, 1 = MMA issuer (+TMEM alloc), 2..5 = epilogue.
+// hi*hi.  Warp roles per CTA: 0 = TMA producer, 1 = MMA issuer (+TMEM alloc), 2..9 = epilogue.
 #include <cuda.h>
 #include <math.h>
 
@@ -29,13 +29,14 @@ constexpr int kHd = 64;
 constexpr uint32_t kSlabBytes = 128 * 128;           // 128 rows x 32 fp32: one swizzle-128B slab
 constexpr uint32_t kPartBytes = 2 * kSlabBytes;      // 128 x 64 fp32 (hi or lo part)
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // hi + lo
-constexpr int kStages = 2;                           // ring of streamed operand tiles
+constexpr int kRing = 10;                            // ring of streamed 16 KB slabs (2.5 tiles in flight)
 constexpr int kAcc = 2;                              // TMEM accumulator buffers
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;                         // TMA warp, MMA warp, 8 epilogue warps
 constexpr uint32_t kTmemCols = 256;
-constexpr uint32_t kBarOff = (1 + kStages) * kOperandBytes;
-constexpr uint32_t kLseOff = kBarOff + 128;
-constexpr uint32_t kSmemBytes = kLseOff + kAcc * kTile * 4 + 1024;  // + alignment slack
+constexpr uint32_t kBarOff = kOperandBytes + kRing * kSlabBytes;
+constexpr uint32_t kLseOff = kBarOff + 256;
+constexpr uint32_t kXchOff = kLseOff + kAcc * kTile * 4;
+constexpr uint32_t kSmemBytes = kXchOff + kTile * 8;  // dynamic smem base must be 1024-aligned (checked)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -101,6 +102,26 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+// 64 consecutive columns of this thread's TMEM lane: two 32-column loads in flight, one wait
+__device__ __forceinline__ void tc_ld64(uint32_t taddr, float (&v)[64]) {
+    uint32_t r[64];
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+        uint32_t* q = r + 32 * hlf;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+            "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+            : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7]),
+              "=r"(q[8]), "=r"(q[9]), "=r"(q[10]), "=r"(q[11]), "=r"(q[12]), "=r"(q[13]), "=r"(q[14]), "=r"(q[15]),
+              "=r"(q[16]), "=r"(q[17]), "=r"(q[18]), "=r"(q[19]), "=r"(q[20]), "=r"(q[21]), "=r"(q[22]), "=r"(q[23]),
+              "=r"(q[24]), "=r"(q[25]), "=r"(q[26]), "=r"(q[27]), "=r"(q[28]), "=r"(q[29]), "=r"(q[30]), "=r"(q[31])
+            : "r"(taddr + 32 * hlf));
+    }
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -118,6 +139,7 @@ struct Params {
     int pass;          // 1 = row LSE, 2 = column sums
     int B, H, KVH, S, nb;
     int causal, x3;
+    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue (timing experiments only)
     float cs;          // scaling * log2(e)
     float* lse2;       // (B,H,S) log2-domain log-sum-exp
     float* part_col;   // (B,H,S) sum_i p[i][j]
@@ -129,13 +151,18 @@ struct Item {
     int bh, blk, t0, t1;  // streamed block range [t0, t1)
 };
 __device__ __forceinline__ bool item_at(const Params& p, int k, Item& it) {
+    // Rank r of the k-th item of this CTA.  Items are ordered window by window (so that the CTAs
+    // running at any moment stream one window's operands and those stay in L2), inside a window by
+    // cost (number of streamed tiles, largest first), and dealt to CTAs in serpentine order.
     const int G = gridDim.x, c = blockIdx.x;
     const long long total = (long long)p.B * p.H * p.nb;
     const long long r = (long long)k * G + ((k & 1) ? (G - 1 - c) : c);
     if (r >= total) return false;
-    const int BH = p.B * p.H;
-    const int rank = (int)(r / BH);
-    it.bh = (int)(r % BH);
+    const int per_window = p.H * p.nb;
+    const int b = (int)(r / per_window);
+    const int q = (int)(r % per_window);
+    const int rank = q / p.H;
+    it.bh = b * p.H + q % p.H;
     if (p.pass == 1) {
         it.blk = p.nb - 1 - rank;  // most key blocks first
         it.t0 = 0;
@@ -153,30 +180,31 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
                         const __grid_constant__ CUtensorMap mapKhi, const __grid_constant__ CUtensorMap mapKlo,
                         const Params p) {
     extern __shared__ uint8_t smem_raw[];
-    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t base = smem_u32(smem_raw);
+    if (base & 1023u) __trap();  // swizzle-128B slabs need 1024-byte alignment; no static smem precedes
+    uint8_t* gen = smem_raw;
     const uint32_t fixed_s = base;
-    const uint32_t stage_s = base + kOperandBytes;
+    const uint32_t ring_s = base + kOperandBytes;
     const uint32_t bar0 = base + kBarOff;
     const uint32_t bar_fixed_full = bar0, bar_fixed_empty = bar0 + 8;
-    const uint32_t bar_full = bar0 + 16, bar_empty = bar0 + 16 + 8 * kStages;
-    const uint32_t bar_tfull = bar_empty + 8 * kStages, bar_tempty = bar_tfull + 8 * kAcc;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 120);
+    const uint32_t bar_full = bar0 + 16, bar_empty = bar0 + 16 + 8 * kRing;
+    const uint32_t bar_tfull = bar_empty + 8 * kRing, bar_tempty = bar_tfull + 8 * kAcc;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 248);
     float* lse_s = reinterpret_cast<float*>(gen + kLseOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t part_tx = p.x3 ? kOperandBytes : kPartBytes;
+    const uint32_t part_tx = p.x3 ? kOperandBytes : kPartBytes;  // bytes of the fixed operand per item
 
     if (threadIdx.x == 0) {
         mbar_init(bar_fixed_full, 1);
         mbar_init(bar_fixed_empty, 1);
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < kRing; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
         }
         for (int a = 0; a < kAcc; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
-            mbar_init(bar_tempty + 8 * a, 4);  // one arrive per epilogue warp
+            mbar_init(bar_tempty + 8 * a, 4);  // one arrive per warp of the owning epilogue group
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -198,9 +226,10 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
     const int group = p.H / p.KVH;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer: fixed operand per item, streamed operand as a ring of 16 KB slabs =====
         if (lane == 0) {
-            uint32_t stage = 0, sphase = 0, fphase = 0;
+            uint32_t ring = 0, rphase = 0, fphase = 0;
+            const int nslab = p.x3 ? 4 : 2;  // hi k0, hi k1, lo k0, lo k1
             Item it;
             for (int k = 0; item_at(p, k, it); ++k) {
                 const int b = it.bh / p.H, h = it.bh % p.H;
@@ -217,129 +246,150 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
                 }
                 fphase ^= 1;
                 for (int t = it.t0; t < it.t1; ++t) {
-                    const uint32_t dst = stage_s + stage * kOperandBytes;
-                    const uint32_t fb = bar_full + 8 * stage;
-                    mbar_wait(bar_empty + 8 * stage, sphase ^ 1);
-                    mbar_expect_tx(fb, part_tx);
-                    tma_load_3d(dst, str_hi, fb, 0, t * kTile, str_idx);
-                    tma_load_3d(dst + kSlabBytes, str_hi, fb, 32, t * kTile, str_idx);
-                    if (p.x3) {
-                        tma_load_3d(dst + kPartBytes, str_lo, fb, 0, t * kTile, str_idx);
-                        tma_load_3d(dst + kPartBytes + kSlabBytes, str_lo, fb, 32, t * kTile, str_idx);
+                    for (int sl = 0; sl < nslab; ++sl) {
+                        const uint32_t fb = bar_full + 8 * ring;
+                        mbar_wait(bar_empty + 8 * ring, rphase ^ 1);
+                        mbar_expect_tx(fb, kSlabBytes);
+                        tma_load_3d(ring_s + ring * kSlabBytes, sl < 2 ? str_hi : str_lo, fb, (sl & 1) * 32, t * kTile, str_idx);
+                        if (++ring == kRing) { ring = 0; rphase ^= 1; }
                     }
-                    if (++stage == kStages) { stage = 0; sphase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            uint32_t stage = 0, sphase = 0, fphase = 0, acc = 0, aphase = 0;
+            uint32_t ring = 0, rphase = 0, fphase = 0, acc = 0, aphase = 0;
+            const int nslab = p.x3 ? 4 : 2;
             Item it;
             for (int k = 0; item_at(p, k, it); ++k) {
                 mbar_wait(bar_fixed_full, fphase);
                 fphase ^= 1;
                 for (int t = it.t0; t < it.t1; ++t) {
-                    mbar_wait(bar_full + 8 * stage, sphase);
                     mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
-                    tc_fence_after();
                     const uint32_t d = tmem_base + acc * kTile;
-                    const uint32_t sb = stage_s + stage * kOperandBytes;
                     uint32_t first = 0;
-                    // (fixed part, streamed part): lo*hi, hi*lo, hi*hi -- small terms first
-                    const int nprod = p.x3 ? 3 : 1;
-                    for (int pr = 0; pr < nprod; ++pr) {
-                        const uint32_t fpart = (p.x3 && pr == 0) ? kPartBytes : 0u;
-                        const uint32_t spart = (p.x3 && pr == 1) ? kPartBytes : 0u;
+                    for (int sl = 0; sl < nslab; ++sl) {
+                        mbar_wait(bar_full + 8 * ring, rphase);
+                        tc_fence_after();
+                        const uint32_t sb = ring_s + ring * kSlabBytes;
+                        const uint32_t fk = (sl & 1) * kSlabBytes;  // matching 32-wide k chunk of the fixed operand
+                        // a streamed hi slab meets fixed hi (and fixed lo in 3xTF32); a streamed lo slab meets fixed hi
+                        if (!(p.dbg & 2)) {
 #pragma unroll
-                        for (int kk = 0; kk < 8; ++kk) {
-                            const uint32_t koff = (kk >> 2) * kSlabBytes + (kk & 3) * 32u;
-                            tc_mma_tf32(d, umma_desc(fixed_s + fpart + koff), umma_desc(sb + spart + koff), kIdesc, first);
+                        for (int kk = 0; kk < 4; ++kk) {
+                            tc_mma_tf32(d, umma_desc(fixed_s + fk + kk * 32u), umma_desc(sb + kk * 32u), kIdesc, first);
                             first = 1;
                         }
+                        }
+                        if (p.x3 && sl < 2 && !(p.dbg & 2)) {
+#pragma unroll
+                            for (int kk = 0; kk < 4; ++kk)
+                                tc_mma_tf32(d, umma_desc(fixed_s + kPartBytes + fk + kk * 32u), umma_desc(sb + kk * 32u), kIdesc, 1u);
+                        }
+                        tc_commit(bar_empty + 8 * ring);    // slab reusable once these MMAs retire
+                        if (++ring == kRing) { ring = 0; rphase ^= 1; }
                     }
-                    tc_commit(bar_empty + 8 * stage);   // smem stage reusable once these MMAs retire
-                    tc_commit(bar_tfull + 8 * acc);     // accumulator ready for the epilogue
-                    if (++stage == kStages) { stage = 0; sphase ^= 1; }
+                    tc_commit(bar_tfull + 8 * acc);         // accumulator ready for the epilogue
                     if (++acc == kAcc) { acc = 0; aphase ^= 1; }
                 }
-                tc_commit(bar_fixed_empty);             // fixed operand reusable
+                tc_commit(bar_fixed_empty);                 // fixed operand reusable
             }
         }
     } else {
-        // ===== epilogue: one TMEM lane (= one row of the tile) per thread =====
+        // ===== epilogue: two groups of 4 warps; group g owns TMEM accumulator g, i.e. every other
+        // tile.  A thread owns one TMEM lane (tile row).  The two warps that share a scheduler are
+        // therefore always half a tile apart: one is pulling its tile out of TMEM while the other
+        // is in the exp2 loop, so TMEM reads and MUFU work overlap.
+        const int ew = warp - 2;                    // 0..7
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
+        const int grp = ew >> 2;                    // accumulator buffer / tile parity of this group
         const int row = q4 * 32 + lane;
-        const int et = threadIdx.x - 64;            // 0..127 among epilogue threads
+        const int gt = (threadIdx.x - 64) & 127;    // thread index inside the group
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
-        uint32_t acc = 0, aphase = 0;
+        const uint32_t my_tfull = bar_tfull + 8 * grp, my_tempty = bar_tempty + 8 * grp;
+        float* lse_t = lse_s + grp * kTile;
+        uint32_t n = 0, uses = 0;                   // tiles seen by the CTA / tiles taken by this group
         Item it;
         for (int k = 0; item_at(p, k, it); ++k) {
             const int g = it.blk * kTile + row;     // global index of this thread's row
             float m = -INFINITY, l = 0.f;           // pass 1
             float colsum = 0.f, lastp = 0.f;        // pass 2
-            for (int t = it.t0; t < it.t1; ++t) {
-                float* lse_t = lse_s + acc * kTile;
+            for (int t = it.t0; t < it.t1; ++t, ++n) {
+                if ((n & 1u) != (uint32_t)grp) continue;
                 if (p.pass == 2) {
-                    const int qi = t * kTile + et;
-                    lse_t[et] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    const int qi = t * kTile + gt;
+                    lse_t[gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
+                    if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+                    else asm volatile("bar.sync 2, 128;" ::: "memory");
                 }
-                mbar_wait(bar_tfull + 8 * acc, aphase);
+                mbar_wait(my_tfull, uses & 1u);
+                ++uses;
                 tc_fence_after();
-                const uint32_t taddr = tmem_base + acc * kTile + lane_addr;
-                const int c0 = t * kTile;           // global index of tile column 0
-                const bool edge = (p.causal && t == it.blk) || (c0 + kTile > p.S);
-                if (p.pass == 1) {
-                    // columns = keys; valid iff key < S and (not causal or key <= query g)
-                    const int jmax = min(p.S - 1, p.causal ? g : p.S - 1);
+                const bool edge = (p.causal && t == it.blk) || (t * kTile + kTile > p.S);
+                const bool has_last = (p.S - 1) / kTile == t;
 #pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
-                        float v[32];
-                        tc_ld32(taddr + c * 32, v);
-                        if (edge) {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (c0 + c * 32 + i > jmax) v[i] = -INFINITY;
-                        }
-                        float cm = v[0];
-#pragma unroll
-                        for (int i = 1; i < 32; ++i) cm = fmaxf(cm, v[i]);
-                        const float mn = fmaxf(m, cm * p.cs);
-                        float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-                        for (int i = 0; i < 32; i += 2) {
-                            s0 += ex2(fmaf(v[i], p.cs, -mn));
-                            s1 += ex2(fmaf(v[i + 1], p.cs, -mn));
-                        }
-                        l = l * ex2(m - mn) + (s0 + s1);
-                        m = mn;
+                for (int half = 0; half < 2; ++half) {
+                    float v[64];
+                    tc_ld64(tmem_base + grp * kTile + lane_addr + half * 64, v);
+                    if (half == 1) {  // whole tile is in registers: hand the accumulator back to the MMA warp
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(my_tempty);
                     }
-                } else {
-                    // columns = queries; valid iff query < S (lse = +inf otherwise) and query >= key g
-                    const bool has_last = (p.S - 1) / kTile == t;
-                    const int last_col = (p.S - 1) % kTile;
-#pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
-                        float v[32];
-                        tc_ld32(taddr + c * 32, v);
+                    const int c0 = t * kTile + half * 64;  // global index of column 0 of this half
+                    if (p.dbg & 1) {
+                        colsum += v[0] + v[63];
+                        l += v[1];
+                    } else if (p.pass == 1) {
+                        // columns = keys; valid iff key < S and (not causal or key <= query g)
+                        if (edge) {
+                            const int jmax = min(p.S - 1, p.causal ? g : p.S - 1);
+#pragma unroll
+                            for (int i = 0; i < 64; ++i)
+                                if (c0 + i > jmax) v[i] = -INFINITY;
+                        }
+                        float cm0 = v[0], cm1 = v[1];
+#pragma unroll
+                        for (int i = 2; i < 64; i += 2) {
+                            cm0 = fmaxf(cm0, v[i]);
+                            cm1 = fmaxf(cm1, v[i + 1]);
+                        }
+                        const float cm = fmaxf(cm0, cm1) * p.cs;
+                        if (cm > -INFINITY) {  // at least one valid column for this row in this half
+                            const float mn = fmaxf(m, cm);
+                            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+                            for (int i = 0; i < 64; i += 4) {
+                                s0 += ex2(fmaf(v[i + 0], p.cs, -mn));
+                                s1 += ex2(fmaf(v[i + 1], p.cs, -mn));
+                                s2 += ex2(fmaf(v[i + 2], p.cs, -mn));
+                                s3 += ex2(fmaf(v[i + 3], p.cs, -mn));
+                            }
+                            l = l * ex2(m - mn) + ((s0 + s1) + (s2 + s3));
+                            m = mn;
+                        }
+                    } else {
+                        // columns = queries; valid iff query < S (lse = +inf otherwise) and query >= key g
+                        const int last_col = (p.S - 1) % kTile - half * 64;
+                        const float* ls_base = lse_t + half * 64;
                         float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-                        for (int i = 0; i < 32; i += 4) {
-                            const float4 ls = *reinterpret_cast<const float4*>(lse_t + c * 32 + i);
+                        for (int i = 0; i < 64; i += 4) {
+                            const float4 ls = *reinterpret_cast<const float4*>(ls_base + i);
                             float p0 = ex2(fmaf(v[i + 0], p.cs, -ls.x));
                             float p1 = ex2(fmaf(v[i + 1], p.cs, -ls.y));
                             float p2 = ex2(fmaf(v[i + 2], p.cs, -ls.z));
                             float p3 = ex2(fmaf(v[i + 3], p.cs, -ls.w));
                             if (edge && p.causal) {
-                                const int qi = c0 + c * 32 + i;
+                                const int qi = c0 + i;
                                 if (qi + 0 < g) p0 = 0.f;
                                 if (qi + 1 < g) p1 = 0.f;
                                 if (qi + 2 < g) p2 = 0.f;
                                 if (qi + 3 < g) p3 = 0.f;
                             }
                             if (has_last) {
-                                const int li = last_col - (c * 32 + i);
+                                const int li = last_col - i;
                                 if (li == 0) lastp = p0;
                                 if (li == 1) lastp = p1;
                                 if (li == 2) lastp = p2;
@@ -351,21 +401,26 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
                         colsum += s0 + s1;
                     }
                 }
-                // accumulator buffer drained: hand it back to the MMA warp
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
-                if (++acc == kAcc) { acc = 0; aphase ^= 1; }
             }
-            if (g < p.S) {
+            // combine the two groups' partial results of every row through shared memory
+            float2* xch = reinterpret_cast<float2*>(gen + kXchOff);
+            if (grp == 1) xch[row] = p.pass == 1 ? make_float2(m, l) : make_float2(colsum, lastp);
+            asm volatile("bar.sync 3, 256;" ::: "memory");
+            if (grp == 0 && g < p.S) {
+                const float2 o2 = xch[row];
                 const size_t o = (size_t)it.bh * p.S + g;
                 if (p.pass == 1) {
-                    p.lse2[o] = m + log2f(l);
+                    // at least one group saw a valid column (column 0 of the row block), so mm is finite
+                    const float mm = fmaxf(m, o2.x);
+                    const float la = m > -INFINITY ? l * ex2(m - mm) : 0.f;
+                    const float lb = o2.x > -INFINITY ? o2.y * ex2(o2.x - mm) : 0.f;
+                    p.lse2[o] = mm + log2f(la + lb);
                 } else {
-                    p.part_col[o] = colsum;
-                    p.part_last[o] = lastp;
+                    p.part_col[o] = colsum + o2.x;
+                    p.part_last[o] = lastp + o2.y;
                 }
             }
+            asm volatile("bar.sync 3, 256;" ::: "memory");
         }
     }
 
@@ -493,6 +548,8 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
                    "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
     SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
                    "materialised path splitq_importance_colmean", hd);
+    const int dbg = (mode >> 4) & 3;  // undocumented timing-experiment bits
+    mode &= 15;
     SPLITQ_REQUIRE(mode == SPLITQ_FUSED_TF32X3 || mode == SPLITQ_FUSED_TF32X1, SPLITQ_ERR_ARG,
                    "importance_fused: unknown mode %d", mode);
     SPLITQ_REQUIRE(scaling > 0.f, SPLITQ_ERR_ARG, "importance_fused: scaling must be positive");
@@ -529,6 +586,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = cdiv(S, kTile);
     p.causal = causal ? 1 : 0;
     p.x3 = mode == SPLITQ_FUSED_TF32X3;
+    p.dbg = dbg;
     p.cs = scaling * 1.4426950408889634f;
     p.lse2 = (float*)(w8 + wl.lse);
     p.part_col = (float*)(w8 + wl.pcol);

@@ -241,13 +241,15 @@ class BoundaryPlan:
 
     def __init__(self, B: int, H: int, S: int, D: int, ladder: Ladder, scale_mode: int = N.SCALE_GROUP,
                  method: str = "regular_importance", src_device="cuda:0", dst_device=None,
-                 causal_hint: bool = False):
+                 causal_hint: bool = False, KVH: Optional[int] = None, fused_mode: int = N.FUSED_TF32X3):
         self.B, self.H, self.S, self.D = B, H, S, D
         self.ladder, self.scale_mode, self.method, self.causal_hint = list(ladder), scale_mode, method, causal_hint
         self.src = torch.device(src_device)
         self.dst = torch.device(dst_device) if dst_device is not None else self.src
         self.nbytes = payload_bytes(S, D, self.ladder, scale_mode)
         self.transport = None
+        self.KVH = KVH or H
+        self.fused_mode = fused_mode
         f32 = dict(dtype=torch.float32, device=self.src)
         self.imp = torch.empty(B, S, **f32)
         self.bits = torch.empty(B, S, dtype=torch.uint8, device=self.src)
@@ -264,6 +266,14 @@ class BoundaryPlan:
         last = self.method == "last_row"
         importance_from_attention(A, want_col=not last, want_last=last, causal_hint=self.causal_hint,
                                   out_col=self.imp, out_last=self.imp)
+        return self.imp
+
+    def score_fused(self, q: torch.Tensor, k: torch.Tensor, scaling: Optional[float] = None) -> torch.Tensor:
+        """Importance straight from the split layer's post-RoPE Q (B,H,S,64) and K (B,KVH,S,64)."""
+        last = self.method == "last_row"
+        scaling = q.shape[-1] ** -0.5 if scaling is None else scaling
+        importance_fused(q, k, scaling, causal=True, mode=self.fused_mode, want_col=not last, want_last=last,
+                         out_col=self.imp, out_last=self.imp)
         return self.imp
 
     def send(self, h: torch.Tensor) -> torch.Tensor:
@@ -291,6 +301,29 @@ class BoundaryPlan:
         self.receive()
         return BoundaryResult(self.imp, self.bits, self.payload_dst, self.h_out)
 
+    def run_fused(self, q: torch.Tensor, k: torch.Tensor, h: torch.Tensor) -> BoundaryResult:
+        self.score_fused(q, k)
+        self.send(h)
+        self.hop()
+        self.receive()
+        return BoundaryResult(self.imp, self.bits, self.payload_dst, self.h_out)
+
+    def run_host_fused(self, q_host, k_host, h_host, out_host) -> torch.Tensor:
+        """End-to-end call with HOST buffers for the fused path: H2D of Q, K and the hidden states,
+        the whole path, D2H of the dequantised hidden states.  Blocks until `out_host` is filled."""
+        if getattr(self, "_q_dev", None) is None:
+            self._q_dev = torch.empty(q_host.shape, dtype=torch.float32, device=self.src)
+            self._k_dev = torch.empty(k_host.shape, dtype=torch.float32, device=self.src)
+            self._h_dev = torch.empty(self.B, self.S, self.D, dtype=torch.float32, device=self.src)
+        self._q_dev.copy_(q_host, non_blocking=True)
+        self._k_dev.copy_(k_host, non_blocking=True)
+        self._h_dev.copy_(h_host, non_blocking=True)
+        self.run_fused(self._q_dev, self._k_dev, self._h_dev)
+        with torch.cuda.device(self.dst):
+            out_host.copy_(self.h_out, non_blocking=True)
+            torch.cuda.current_stream(self.dst).synchronize()
+        return out_host
+
     def run_host(self, A_host: torch.Tensor, h_host: torch.Tensor, out_host: torch.Tensor) -> torch.Tensor:
         """End-to-end call with HOST buffers (pinned for full speed): H2D of this step's attention
         maps and hidden states, the whole path, D2H of the dequantised hidden states.  Blocks until
@@ -306,13 +339,15 @@ class BoundaryPlan:
             torch.cuda.current_stream(self.dst).synchronize()
         return out_host
 
-    def host_bytes_per_run(self):
-        """(h2d, d2h) bytes moved by one run_host()."""
+    def host_bytes_per_run(self, fused: bool = False):
+        """(h2d, d2h) bytes moved by one run_host() / run_host_fused()."""
+        if fused:
+            return 4 * self.B * self.S * (64 * (self.H + self.KVH) + self.D), 4 * self.B * self.S * self.D
         return 4 * self.B * (self.H * self.S * self.S + self.S * self.D), 4 * self.B * self.S * self.D
 
     #: kernels launched by one run(): colsum partial + finalize, select, [memset+class absmax,] pack, dequant
-    def launches_per_run(self) -> int:
-        n = 2 if self.method != "last_row" else 1
+    def launches_per_run(self, fused: bool = False) -> int:
+        n = 5 if fused else (2 if self.method != "last_row" else 1)  # fused: 2 splits, 2 passes, finalize
         n += 1
         n += 2 if self.scale_mode == N.SCALE_GROUP else 1
         n += 1

@@ -197,6 +197,14 @@ def reference_boundary_cpu(A: torch.Tensor, h: torch.Tensor, ladder, scale_mode:
     return imp, h
 
 
+def reference_boundary_cpu_from_qk(q, k, h, scaling, ladder, scale_mode, method="regular_importance"):
+    """Same as reference_boundary_cpu, starting where the fused GPU path starts: the split layer's
+    post-RoPE Q and K.  The reference gets its attention map from HF eager attention
+    (last_row_exp.py:92-95), which is exactly attention_probs()."""
+    A = attention_probs(q, k, scaling, causal=True)
+    return reference_boundary_cpu(A, h, ladder, scale_mode, method)
+
+
 # --------------------------------------------------------------------------------------
 # packed payload (our format; see header comment)
 # --------------------------------------------------------------------------------------
