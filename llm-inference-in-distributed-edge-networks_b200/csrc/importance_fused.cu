@@ -13,7 +13,9 @@
 // swizzle).  The reference computes QK^T in true fp32; a single TF32 product misses the 1e-5
 // importance tolerance for trained-scale logits, so operands are pre-split into tf32 hi + lo
 // parts and each tile accumulates lo*hi + hi*lo + hi*hi (3xTF32); SPLITQ_FUSED_TF32X1 keeps only
-// hi*hi.  Warp roles per CTA: 0 = TMA producer, 1 = MMA issuer (+TMEM alloc), 2..9 = epilogue.
+// hi*hi.  Four warpgroups per CTA: control (warp 0 = TMA producer of the streamed operand, warp 1 = MMA
+// issuer), two epilogue groups (one per TMEM accumulator), and loaders that put the fixed operand of
+// the next work item into tensor memory, so the MMA reads A from TMEM and only B from shared memory.
 #include <cuda.h>
 #include <math.h>
 
@@ -29,13 +31,14 @@ constexpr int kHd = 64;
 constexpr uint32_t kSlabBytes = 128 * 128;           // 128 rows x 32 fp32: one swizzle-128B slab
 constexpr uint32_t kPartBytes = 2 * kSlabBytes;      // 128 x 64 fp32 (hi or lo part)
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // hi + lo
-constexpr int kRing = 10;                            // ring of streamed 16 KB slabs (2.5 tiles in flight)
+constexpr int kRing = 13;                            // ring of streamed 16 KB slabs (3.25 tiles in flight)
 constexpr int kAcc = 2;                              // TMEM accumulator buffers
-constexpr int kThreads = 320;                         // TMA warp, MMA warp, 8 epilogue warps
-constexpr uint32_t kTmemCols = 256;
-constexpr uint32_t kBarOff = kOperandBytes + kRing * kSlabBytes;
-constexpr uint32_t kLseOff = kBarOff + 256;
-constexpr uint32_t kXchOff = kLseOff + kAcc * kTile * 4;
+constexpr int kThreads = 512;                         // 4 warpgroups: control, epilogue x2, operand loaders
+constexpr uint32_t kTmemCols = 512;                   // 2 accumulators (128 each) + 2 fixed-operand buffers (hi 64 + lo 64 each)
+constexpr uint32_t kTmemA = 256;                      // first column of the fixed-operand buffers
+constexpr uint32_t kBarOff = kRing * kSlabBytes;
+constexpr uint32_t kLseOff = kBarOff + 512;            // 36 mbarriers (288 B) + TMEM base slot
+constexpr uint32_t kXchOff = kLseOff + 2 * kAcc * kTile * 4;  // lse: 2 groups x 2 buffers x 128 floats
 constexpr uint32_t kSmemBytes = kXchOff + kTile * 8;  // dynamic smem base must be 1024-aligned (checked)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -87,6 +90,37 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uin
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
         : "memory");
 }
+// A operand (M = 128 rows on the 128 TMEM lanes, K along columns) read from tensor memory
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+// 32 consecutive columns of this thread's TMEM lane <- registers
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const float4 (&q)[8]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+        "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+        ::"r"(taddr),
+          "f"(q[0].x), "f"(q[0].y), "f"(q[0].z), "f"(q[0].w), "f"(q[1].x), "f"(q[1].y), "f"(q[1].z), "f"(q[1].w),
+          "f"(q[2].x), "f"(q[2].y), "f"(q[2].z), "f"(q[2].w), "f"(q[3].x), "f"(q[3].y), "f"(q[3].z), "f"(q[3].w),
+          "f"(q[4].x), "f"(q[4].y), "f"(q[4].z), "f"(q[4].w), "f"(q[5].x), "f"(q[5].y), "f"(q[5].z), "f"(q[5].w),
+          "f"(q[6].x), "f"(q[6].y), "f"(q[6].z), "f"(q[6].w), "f"(q[7].x), "f"(q[7].y), "f"(q[7].z), "f"(q[7].w)
+        : "memory");
+}
+// one lane of a converged warp; the surrounding code stays warp-uniform so that descriptors and
+// addresses live in uniform registers (a divergent `if (lane == 0)` costs ~6 R2UR moves per MMA)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+template <int N> __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 __device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
     uint32_t r[32];
     asm volatile(
@@ -144,6 +178,7 @@ struct Params {
     float* lse2;       // (B,H,S) log2-domain log-sum-exp
     float* part_col;   // (B,H,S) sum_i p[i][j]
     float* part_last;  // (B,H,S) p[S-1][j]
+    const float *qhi, *qlo, *khi, *klo;  // dense (n,S,64) tf32 hi / lo parts
 };
 
 // Static schedule shared by all warp roles: items ranked by cost (tiles), dealt serpentine.
@@ -175,6 +210,109 @@ __device__ __forceinline__ bool item_at(const Params& p, int k, Item& it) {
     return true;
 }
 
+// ---- epilogue building blocks -------------------------------------------------------------------
+// 64 consecutive columns of this thread's TMEM lane; asynchronous until tc_ld_wait()
+__device__ __forceinline__ void tc_ld64_issue(uint32_t taddr, float (&v)[64]) {
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+        float* q = v + 32 * hlf;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+            "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+            : "=f"(q[0]), "=f"(q[1]), "=f"(q[2]), "=f"(q[3]), "=f"(q[4]), "=f"(q[5]), "=f"(q[6]), "=f"(q[7]),
+              "=f"(q[8]), "=f"(q[9]), "=f"(q[10]), "=f"(q[11]), "=f"(q[12]), "=f"(q[13]), "=f"(q[14]), "=f"(q[15]),
+              "=f"(q[16]), "=f"(q[17]), "=f"(q[18]), "=f"(q[19]), "=f"(q[20]), "=f"(q[21]), "=f"(q[22]), "=f"(q[23]),
+              "=f"(q[24]), "=f"(q[25]), "=f"(q[26]), "=f"(q[27]), "=f"(q[28]), "=f"(q[29]), "=f"(q[30]), "=f"(q[31])
+            : "r"(taddr + 32 * hlf)
+            : "memory");
+    }
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return done != 0;
+}
+__device__ __forceinline__ void group_bar(int grp) {
+    if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+    else asm volatile("bar.sync 2, 128;" ::: "memory");
+}
+// pass 1, 64 columns (= keys c0..c0+63) of query row g: online log-sum-exp in the log2 domain
+__device__ __forceinline__ void pass1_half(float (&v)[64], int c0, bool edge, int g, const Params& p, float& m, float& l) {
+    if (edge) {  // valid iff key < S and (not causal or key <= query)
+        const int jmax = min(p.S - 1, p.causal ? g : p.S - 1);
+#pragma unroll
+        for (int i = 0; i < 64; ++i)
+            if (c0 + i > jmax) v[i] = -INFINITY;
+    }
+    float cm0 = v[0], cm1 = v[1];
+#pragma unroll
+    for (int i = 2; i < 64; i += 2) {
+        cm0 = fmaxf(cm0, v[i]);
+        cm1 = fmaxf(cm1, v[i + 1]);
+    }
+    const float cm = fmaxf(cm0, cm1) * p.cs;
+    if (cm > -INFINITY) {  // at least one valid column for this row in this half
+        const float mn = fmaxf(m, cm);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+            s0 += ex2(fmaf(v[i + 0], p.cs, -mn));
+            s1 += ex2(fmaf(v[i + 1], p.cs, -mn));
+            s2 += ex2(fmaf(v[i + 2], p.cs, -mn));
+            s3 += ex2(fmaf(v[i + 3], p.cs, -mn));
+        }
+        l = l * ex2(m - mn) + ((s0 + s1) + (s2 + s3));
+        m = mn;
+    }
+}
+// pass 2, 64 columns (= queries c0..c0+63) of key row g: sum of exp2(s*cs - lse2[query]).
+// SPECIAL = diagonal / last-row tiles (masking and the last-row pick); the common tile runs the
+// branch-free instantiation so that the 64 exp2 form one straight-line, fully scheduled block.
+template <bool SPECIAL>
+__device__ __forceinline__ void pass2_body(const float (&v)[64], const float* ls, int c0, bool mask, int g, int last_col,
+                                           float cs, float& colsum, float& lastp) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 64; i += 4) {
+        const float4 ls4 = *reinterpret_cast<const float4*>(ls + i);
+        float p0 = ex2(fmaf(v[i + 0], cs, -ls4.x));
+        float p1 = ex2(fmaf(v[i + 1], cs, -ls4.y));
+        float p2 = ex2(fmaf(v[i + 2], cs, -ls4.z));
+        float p3 = ex2(fmaf(v[i + 3], cs, -ls4.w));
+        if (SPECIAL) {
+            const int qi = c0 + i;  // valid iff query >= key (queries >= S carry lse = +inf -> 0)
+            p0 = (mask && qi + 0 < g) ? 0.f : p0;
+            p1 = (mask && qi + 1 < g) ? 0.f : p1;
+            p2 = (mask && qi + 2 < g) ? 0.f : p2;
+            p3 = (mask && qi + 3 < g) ? 0.f : p3;
+            lastp = (last_col == i + 0) ? p0 : lastp;
+            lastp = (last_col == i + 1) ? p1 : lastp;
+            lastp = (last_col == i + 2) ? p2 : lastp;
+            lastp = (last_col == i + 3) ? p3 : lastp;
+        }
+        s0 += p0;
+        s1 += p1;
+        s2 += p2;
+        s3 += p3;
+    }
+    colsum += (s0 + s1) + (s2 + s3);
+}
+__device__ __forceinline__ void pass2_half(const float (&v)[64], const float* ls, int c0, bool edge, int g, bool has_last,
+                                           int last_col, const Params& p, float& colsum, float& lastp) {
+    if (edge || has_last)
+        pass2_body<true>(v, ls, c0, edge && p.causal, g, has_last ? last_col : -1, p.cs, colsum, lastp);
+    else
+        pass2_body<false>(v, ls, c0, false, g, -1, p.cs, colsum, lastp);
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid_constant__ CUtensorMap mapQlo,
                         const __grid_constant__ CUtensorMap mapKhi, const __grid_constant__ CUtensorMap mapKlo,
@@ -183,21 +321,21 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
     const uint32_t base = smem_u32(smem_raw);
     if (base & 1023u) __trap();  // swizzle-128B slabs need 1024-byte alignment; no static smem precedes
     uint8_t* gen = smem_raw;
-    const uint32_t fixed_s = base;
-    const uint32_t ring_s = base + kOperandBytes;
+    const uint32_t ring_s = base;
     const uint32_t bar0 = base + kBarOff;
-    const uint32_t bar_fixed_full = bar0, bar_fixed_empty = bar0 + 8;
-    const uint32_t bar_full = bar0 + 16, bar_empty = bar0 + 16 + 8 * kRing;
+    const uint32_t bar_afull = bar0, bar_aempty = bar0 + 16;          // fixed operand in TMEM, 2 buffers
+    const uint32_t bar_full = bar0 + 32, bar_empty = bar_full + 8 * kRing;
     const uint32_t bar_tfull = bar_empty + 8 * kRing, bar_tempty = bar_tfull + 8 * kAcc;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 248);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 504);
     float* lse_s = reinterpret_cast<float*>(gen + kLseOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t part_tx = p.x3 ? kOperandBytes : kPartBytes;  // bytes of the fixed operand per item
 
     if (threadIdx.x == 0) {
-        mbar_init(bar_fixed_full, 1);
-        mbar_init(bar_fixed_empty, 1);
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_afull + 8 * a, 4);   // one arrive per loader warp
+            mbar_init(bar_aempty + 8 * a, 1);  // tcgen05.commit of the item's last MMA
+        }
         for (int s = 0; s < kRing; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
@@ -219,186 +357,191 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const CUtensorMap* fix_hi = p.pass == 1 ? &mapQhi : &mapKhi;
-    const CUtensorMap* fix_lo = p.pass == 1 ? &mapQlo : &mapKlo;
     const CUtensorMap* str_hi = p.pass == 1 ? &mapKhi : &mapQhi;
     const CUtensorMap* str_lo = p.pass == 1 ? &mapKlo : &mapQlo;
     const int group = p.H / p.KVH;
+    const int wg = warp >> 2;  // warpgroup: 0 control, 1-2 epilogue, 3 fixed-operand loaders
 
-    if (warp == 0) {
-        // ===== TMA producer: fixed operand per item, streamed operand as a ring of 16 KB slabs =====
-        if (lane == 0) {
-            uint32_t ring = 0, rphase = 0, fphase = 0;
-            const int nslab = p.x3 ? 4 : 2;  // hi k0, hi k1, lo k0, lo k1
-            Item it;
-            for (int k = 0; item_at(p, k, it); ++k) {
-                const int b = it.bh / p.H, h = it.bh % p.H;
-                const int q_idx = it.bh, k_idx = b * p.KVH + h / group;
-                const int fix_idx = p.pass == 1 ? q_idx : k_idx;
-                const int str_idx = p.pass == 1 ? k_idx : q_idx;
-                mbar_wait(bar_fixed_empty, fphase ^ 1);
-                mbar_expect_tx(bar_fixed_full, part_tx);
-                tma_load_3d(fixed_s, fix_hi, bar_fixed_full, 0, it.blk * kTile, fix_idx);
-                tma_load_3d(fixed_s + kSlabBytes, fix_hi, bar_fixed_full, 32, it.blk * kTile, fix_idx);
-                if (p.x3) {
-                    tma_load_3d(fixed_s + kPartBytes, fix_lo, bar_fixed_full, 0, it.blk * kTile, fix_idx);
-                    tma_load_3d(fixed_s + kPartBytes + kSlabBytes, fix_lo, bar_fixed_full, 32, it.blk * kTile, fix_idx);
-                }
-                fphase ^= 1;
-                for (int t = it.t0; t < it.t1; ++t) {
-                    for (int sl = 0; sl < nslab; ++sl) {
-                        const uint32_t fb = bar_full + 8 * ring;
-                        mbar_wait(bar_empty + 8 * ring, rphase ^ 1);
-                        mbar_expect_tx(fb, kSlabBytes);
-                        tma_load_3d(ring_s + ring * kSlabBytes, sl < 2 ? str_hi : str_lo, fb, (sl & 1) * 32, t * kTile, str_idx);
-                        if (++ring == kRing) { ring = 0; rphase ^= 1; }
+    if (wg == 0) {
+        reg_dec<56>();
+        if (warp == 0) {
+            // ===== TMA producer: streamed operand as a ring of 16 KB slabs =====
+            {
+                uint32_t ring = 0, rphase = 0;
+                const int nslab = p.x3 ? 4 : 2;  // hi k0, hi k1, lo k0, lo k1
+                Item it;
+                for (int k = 0; item_at(p, k, it); ++k) {
+                    const int b = it.bh / p.H, h = it.bh % p.H;
+                    const int str_idx = p.pass == 1 ? b * p.KVH + h / group : it.bh;
+                    for (int t = it.t0; t < it.t1; ++t) {
+                        for (int sl = 0; sl < nslab; ++sl) {
+                            const uint32_t fb = bar_full + 8 * ring;
+                            mbar_wait(bar_empty + 8 * ring, rphase ^ 1);
+                            if (elect_one()) {
+                                mbar_expect_tx(fb, kSlabBytes);
+                                tma_load_3d(ring_s + ring * kSlabBytes, sl < 2 ? str_hi : str_lo, fb, (sl & 1) * 32, t * kTile, str_idx);
+                            }
+                            __syncwarp();
+                            if (++ring == kRing) { ring = 0; rphase ^= 1; }
+                        }
                     }
+                }
+            }
+        } else if (warp == 1) {
+            // ===== MMA issuer: A (fixed operand) from TMEM, B (streamed slab) from shared memory =====
+            {
+                uint32_t ring = 0, rphase = 0, acc = 0, aphase = 0;
+                const int nslab = p.x3 ? 4 : 2;
+                Item it;
+                for (int k = 0; item_at(p, k, it); ++k) {
+                    const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
+                    const uint32_t a_hi = tmem_base + kTmemA + ab * 128u, a_lo = a_hi + 64u;
+                    mbar_wait(bar_afull + 8 * ab, abphase);
+                    tc_fence_after();
+                    for (int t = it.t0; t < it.t1; ++t) {
+                        mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
+                        const uint32_t d = tmem_base + acc * kTile;
+                        uint32_t first = 0;
+                        for (int sl = 0; sl < nslab; ++sl) {
+                            mbar_wait(bar_full + 8 * ring, rphase);
+                            tc_fence_after();
+                            const uint32_t sb = ring_s + ring * kSlabBytes;
+                            const uint32_t kc = (sl & 1) * 32u;  // first of the 32 k-columns this slab covers
+                            // a streamed hi slab meets fixed hi (and fixed lo in 3xTF32); a streamed lo slab meets fixed hi
+                            if (elect_one()) {
+                                if (!(p.dbg & 2)) {
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk) {
+                                        tc_mma_tf32_ts(d, a_hi + kc + kk * 8u, umma_desc(sb + kk * 32u), kIdesc, first | (uint32_t)kk);
+                                    }
+                                    if (p.x3 && sl < 2) {
+#pragma unroll
+                                        for (int kk = 0; kk < 4; ++kk)
+                                            tc_mma_tf32_ts(d, a_lo + kc + kk * 8u, umma_desc(sb + kk * 32u), kIdesc, 1u);
+                                    }
+                                }
+                                tc_commit(bar_empty + 8 * ring);    // slab reusable once these MMAs retire
+                            }
+                            __syncwarp();
+                            first = 1;
+                            if (++ring == kRing) { ring = 0; rphase ^= 1; }
+                        }
+                        if (elect_one()) tc_commit(bar_tfull + 8 * acc);  // accumulator ready for the epilogue
+                        __syncwarp();
+                        if (++acc == kAcc) { acc = 0; aphase ^= 1; }
+                    }
+                    if (elect_one()) tc_commit(bar_aempty + 8 * ab);      // fixed-operand buffer reusable
+                    __syncwarp();
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
-            uint32_t ring = 0, rphase = 0, fphase = 0, acc = 0, aphase = 0;
-            const int nslab = p.x3 ? 4 : 2;
-            Item it;
-            for (int k = 0; item_at(p, k, it); ++k) {
-                mbar_wait(bar_fixed_full, fphase);
-                fphase ^= 1;
-                for (int t = it.t0; t < it.t1; ++t) {
-                    mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
-                    const uint32_t d = tmem_base + acc * kTile;
-                    uint32_t first = 0;
-                    for (int sl = 0; sl < nslab; ++sl) {
-                        mbar_wait(bar_full + 8 * ring, rphase);
-                        tc_fence_after();
-                        const uint32_t sb = ring_s + ring * kSlabBytes;
-                        const uint32_t fk = (sl & 1) * kSlabBytes;  // matching 32-wide k chunk of the fixed operand
-                        // a streamed hi slab meets fixed hi (and fixed lo in 3xTF32); a streamed lo slab meets fixed hi
-                        if (!(p.dbg & 2)) {
+    } else if (wg == 3) {
+        // ===== fixed-operand loaders: one thread per row; tf32 hi/lo parts -> TMEM (A operand) =====
+        reg_dec<56>();
+        const int q4 = warp & 3;
+        const int row = q4 * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+        const float* fhi = p.pass == 1 ? p.qhi : p.khi;
+        const float* flo = p.pass == 1 ? p.qlo : p.klo;
+        Item it;
+        for (int k = 0; item_at(p, k, it); ++k) {
+            const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
+            const int b = it.bh / p.H, h = it.bh % p.H;
+            const int fix_idx = p.pass == 1 ? it.bh : b * p.KVH + h / group;
+            const int g = it.blk * kTile + row;
+            const size_t off = ((size_t)fix_idx * p.S + (g < p.S ? g : 0)) * kHd;
+            mbar_wait(bar_aempty + 8 * ab, abphase ^ 1);
+            tc_fence_after();
+            const uint32_t a0 = tmem_base + kTmemA + ab * 128u + lane_addr;
+            const int nparts = p.x3 ? 2 : 1;
+            for (int part = 0; part < nparts; ++part) {
+                const float4* src = reinterpret_cast<const float4*>((part == 0 ? fhi : flo) + off);
 #pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) {
-                            tc_mma_tf32(d, umma_desc(fixed_s + fk + kk * 32u), umma_desc(sb + kk * 32u), kIdesc, first);
-                            first = 1;
-                        }
-                        }
-                        if (p.x3 && sl < 2 && !(p.dbg & 2)) {
+                for (int c = 0; c < 2; ++c) {
+                    float4 q[8];
 #pragma unroll
-                            for (int kk = 0; kk < 4; ++kk)
-                                tc_mma_tf32(d, umma_desc(fixed_s + kPartBytes + fk + kk * 32u), umma_desc(sb + kk * 32u), kIdesc, 1u);
-                        }
-                        tc_commit(bar_empty + 8 * ring);    // slab reusable once these MMAs retire
-                        if (++ring == kRing) { ring = 0; rphase ^= 1; }
-                    }
-                    tc_commit(bar_tfull + 8 * acc);         // accumulator ready for the epilogue
-                    if (++acc == kAcc) { acc = 0; aphase ^= 1; }
+                    for (int i = 0; i < 8; ++i) q[i] = g < p.S ? __ldg(src + c * 8 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    tc_st32(a0 + part * 64u + c * 32u, q);
                 }
-                tc_commit(bar_fixed_empty);                 // fixed operand reusable
             }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_afull + 8 * ab);
         }
     } else {
+        reg_inc<200>();
         // ===== epilogue: two groups of 4 warps; group g owns TMEM accumulator g, i.e. every other
-        // tile.  A thread owns one TMEM lane (tile row).  The two warps that share a scheduler are
-        // therefore always half a tile apart: one is pulling its tile out of TMEM while the other
-        // is in the exp2 loop, so TMEM reads and MUFU work overlap.
-        const int ew = warp - 2;                    // 0..7
+        // tile; a thread owns one TMEM lane (tile row).  Each thread ping-pongs two 64-column
+        // register buffers: the tcgen05.ld of the next half tile is in flight while the exp2 loop
+        // runs on the current one, so TMEM reads (64 B/clk/SM) hide behind the MUFU work.
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
-        const int grp = ew >> 2;                    // accumulator buffer / tile parity of this group
+        const int grp = wg - 1;                     // accumulator buffer / tile parity of this group
         const int row = q4 * 32 + lane;
-        const int gt = (threadIdx.x - 64) & 127;    // thread index inside the group
-        const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+        const int gt = threadIdx.x & 127;           // thread index inside the group
         const uint32_t my_tfull = bar_tfull + 8 * grp, my_tempty = bar_tempty + 8 * grp;
-        float* lse_t = lse_s + grp * kTile;
+        const uint32_t my_tmem = tmem_base + grp * kTile + ((uint32_t)(q4 * 32) << 16);
+        float* lse_g = lse_s + grp * 2 * kTile;     // two lse buffers per group (pass 2)
         uint32_t n = 0, uses = 0;                   // tiles seen by the CTA / tiles taken by this group
         Item it;
         for (int k = 0; item_at(p, k, it); ++k) {
             const int g = it.blk * kTile + row;     // global index of this thread's row
             float m = -INFINITY, l = 0.f;           // pass 1
             float colsum = 0.f, lastp = 0.f;        // pass 2
-            for (int t = it.t0; t < it.t1; ++t, ++n) {
-                if ((n & 1u) != (uint32_t)grp) continue;
+            const int ntiles = it.t1 - it.t0;
+            int t = it.t0 + (int)((n ^ (uint32_t)grp) & 1u);  // first tile of this item that is mine
+            n += (uint32_t)ntiles;
+            if (t < it.t1) {
+                float va[64], vb[64];
+                uint32_t lb = 0;                    // lse buffer of the current tile
                 if (p.pass == 2) {
                     const int qi = t * kTile + gt;
-                    lse_t[gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
-                    if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
-                    else asm volatile("bar.sync 2, 128;" ::: "memory");
+                    lse_g[gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
                 }
                 mbar_wait(my_tfull, uses & 1u);
                 ++uses;
                 tc_fence_after();
-                const bool edge = (p.causal && t == it.blk) || (t * kTile + kTile > p.S);
-                const bool has_last = (p.S - 1) / kTile == t;
-#pragma unroll 1
-                for (int half = 0; half < 2; ++half) {
-                    float v[64];
-                    tc_ld64(tmem_base + grp * kTile + lane_addr + half * 64, v);
-                    if (half == 1) {  // whole tile is in registers: hand the accumulator back to the MMA warp
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(my_tempty);
+                tc_ld64_issue(my_tmem, va);
+                tc_ld_wait();
+                for (; t < it.t1; t += 2) {
+                    const bool edge = (p.causal && t == it.blk) || (t * kTile + kTile > p.S);
+                    const bool has_last = (p.S - 1) / kTile == t;
+                    const bool has_next = t + 2 < it.t1;
+                    const float* lse_t = lse_g + lb * kTile;
+                    if (p.pass == 2) group_bar(grp);          // this tile's lse values are in shared memory
+                    tc_ld64_issue(my_tmem + 64, vb);          // second half in flight ...
+                    if (p.dbg & 1) { colsum += va[0] + va[63]; l += va[1]; }
+                    else if (p.pass == 1) pass1_half(va, t * kTile, edge, g, p, m, l);
+                    else pass2_half(va, lse_t, t * kTile, edge, g, has_last, (p.S - 1) % kTile, p, colsum, lastp);
+                    tc_ld_wait();                             // ... now in registers: accumulator is drained
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(my_tempty);
+                    bool ready = false;
+                    if (has_next) {
+                        if (p.pass == 2) {
+                            const int qi = (t + 2) * kTile + gt;
+                            lse_g[(lb ^ 1u) * kTile + gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
+                        }
+                        ready = mbar_test(my_tfull, uses & 1u);
+                        ready = __all_sync(0xffffffffu, ready);
+                        if (ready) {
+                            tc_fence_after();
+                            tc_ld64_issue(my_tmem, va);       // next tile's first half in flight ...
+                        }
                     }
-                    const int c0 = t * kTile + half * 64;  // global index of column 0 of this half
-                    if (p.dbg & 1) {
-                        colsum += v[0] + v[63];
-                        l += v[1];
-                    } else if (p.pass == 1) {
-                        // columns = keys; valid iff key < S and (not causal or key <= query g)
-                        if (edge) {
-                            const int jmax = min(p.S - 1, p.causal ? g : p.S - 1);
-#pragma unroll
-                            for (int i = 0; i < 64; ++i)
-                                if (c0 + i > jmax) v[i] = -INFINITY;
+                    if (p.dbg & 1) { colsum += vb[0] + vb[63]; l += vb[1]; }
+                    else if (p.pass == 1) pass1_half(vb, t * kTile + 64, edge, g, p, m, l);
+                    else pass2_half(vb, lse_t + 64, t * kTile + 64, edge, g, has_last, (p.S - 1) % kTile - 64, p, colsum, lastp);
+                    if (has_next) {
+                        if (!ready) {
+                            mbar_wait(my_tfull, uses & 1u);
+                            tc_fence_after();
+                            tc_ld64_issue(my_tmem, va);
                         }
-                        float cm0 = v[0], cm1 = v[1];
-#pragma unroll
-                        for (int i = 2; i < 64; i += 2) {
-                            cm0 = fmaxf(cm0, v[i]);
-                            cm1 = fmaxf(cm1, v[i + 1]);
-                        }
-                        const float cm = fmaxf(cm0, cm1) * p.cs;
-                        if (cm > -INFINITY) {  // at least one valid column for this row in this half
-                            const float mn = fmaxf(m, cm);
-                            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-                            for (int i = 0; i < 64; i += 4) {
-                                s0 += ex2(fmaf(v[i + 0], p.cs, -mn));
-                                s1 += ex2(fmaf(v[i + 1], p.cs, -mn));
-                                s2 += ex2(fmaf(v[i + 2], p.cs, -mn));
-                                s3 += ex2(fmaf(v[i + 3], p.cs, -mn));
-                            }
-                            l = l * ex2(m - mn) + ((s0 + s1) + (s2 + s3));
-                            m = mn;
-                        }
-                    } else {
-                        // columns = queries; valid iff query < S (lse = +inf otherwise) and query >= key g
-                        const int last_col = (p.S - 1) % kTile - half * 64;
-                        const float* ls_base = lse_t + half * 64;
-                        float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-                        for (int i = 0; i < 64; i += 4) {
-                            const float4 ls = *reinterpret_cast<const float4*>(ls_base + i);
-                            float p0 = ex2(fmaf(v[i + 0], p.cs, -ls.x));
-                            float p1 = ex2(fmaf(v[i + 1], p.cs, -ls.y));
-                            float p2 = ex2(fmaf(v[i + 2], p.cs, -ls.z));
-                            float p3 = ex2(fmaf(v[i + 3], p.cs, -ls.w));
-                            if (edge && p.causal) {
-                                const int qi = c0 + i;
-                                if (qi + 0 < g) p0 = 0.f;
-                                if (qi + 1 < g) p1 = 0.f;
-                                if (qi + 2 < g) p2 = 0.f;
-                                if (qi + 3 < g) p3 = 0.f;
-                            }
-                            if (has_last) {
-                                const int li = last_col - i;
-                                if (li == 0) lastp = p0;
-                                if (li == 1) lastp = p1;
-                                if (li == 2) lastp = p2;
-                                if (li == 3) lastp = p3;
-                            }
-                            s0 += p0 + p1;
-                            s1 += p2 + p3;
-                        }
-                        colsum += s0 + s1;
+                        ++uses;
+                        tc_ld_wait();                         // ... and landed
+                        lb ^= 1u;
                     }
                 }
             }
@@ -413,8 +556,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
                     // at least one group saw a valid column (column 0 of the row block), so mm is finite
                     const float mm = fmaxf(m, o2.x);
                     const float la = m > -INFINITY ? l * ex2(m - mm) : 0.f;
-                    const float lb = o2.x > -INFINITY ? o2.y * ex2(o2.x - mm) : 0.f;
-                    p.lse2[o] = mm + log2f(la + lb);
+                    const float lb2 = o2.x > -INFINITY ? o2.y * ex2(o2.x - mm) : 0.f;
+                    p.lse2[o] = mm + log2f(la + lb2);
                 } else {
                     p.part_col[o] = colsum + o2.x;
                     p.part_last[o] = lastp + o2.y;
@@ -440,25 +583,38 @@ __device__ __forceinline__ float tf32_rn(float x) {
 }
 __global__ void __launch_bounds__(256)
 split_tf32_kernel(const float* __restrict__ x, long long sb, long long sh, long long ss, int heads, int S,
-                  long long total4, float* __restrict__ hi, float* __restrict__ lo, int vec) {
-    // one thread per 4 consecutive head-dim elements; output is dense (B,heads,S,64)
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
-         i += (long long)gridDim.x * blockDim.x) {
-        const int d4 = (int)(i % (kHd / 4));
-        const long long row = i / (kHd / 4);
-        const int s = (int)(row % S);
-        const long long bh = row / S;
-        const int h = (int)(bh % heads);
-        const long long b = bh / heads;
-        const float* src = x + b * sb + h * sh + s * ss + d4 * 4;
-        float4 v;
-        if (vec) v = __ldg(reinterpret_cast<const float4*>(src));
-        else v = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), __ldg(src + 3));
-        float4 a, r;
-        a.x = tf32_rn(v.x); a.y = tf32_rn(v.y); a.z = tf32_rn(v.z); a.w = tf32_rn(v.w);
-        r.x = tf32_rn(v.x - a.x); r.y = tf32_rn(v.y - a.y); r.z = tf32_rn(v.z - a.z); r.w = tf32_rn(v.w - a.w);
-        reinterpret_cast<float4*>(hi)[i] = a;
-        reinterpret_cast<float4*>(lo)[i] = r;
+                  float* __restrict__ hi, float* __restrict__ lo, int vec) {
+    // grid.y = b * heads + h (one division per CTA); grid.x strides over the S*16 float4 of that
+    // head, 4 per thread with 256-thread spacing so every warp access is contiguous
+    const int bh = blockIdx.y;
+    const int b = bh / heads, h = bh - b * heads;
+    const float* src0 = x + b * sb + h * sh;
+    const int n4 = S * (kHd / 4);
+    float4* hi4 = reinterpret_cast<float4*>(hi) + (size_t)bh * n4;
+    float4* lo4 = reinterpret_cast<float4*>(lo) + (size_t)bh * n4;
+    constexpr int UN = 4;
+    const int i0 = blockIdx.x * (256 * UN) + threadIdx.x;
+    float4 v[UN];
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+        const int i = i0 + u * 256;
+        if (i < n4) {
+            const float* src = src0 + (long long)(i >> 4) * ss + (i & 15) * 4;
+            if (vec) v[u] = __ldg(reinterpret_cast<const float4*>(src));
+            else v[u] = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), __ldg(src + 3));
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+        const int i = i0 + u * 256;
+        if (i < n4) {
+            float4 a, r;
+            a.x = tf32_rn(v[u].x); a.y = tf32_rn(v[u].y); a.z = tf32_rn(v[u].z); a.w = tf32_rn(v[u].w);
+            r.x = tf32_rn(v[u].x - a.x); r.y = tf32_rn(v[u].y - a.y);
+            r.z = tf32_rn(v[u].z - a.z); r.w = tf32_rn(v[u].w - a.w);
+            hi4[i] = a;
+            lo4[i] = r;
+        }
     }
 }
 
@@ -565,14 +721,15 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
           *klo = (float*)(w8 + wl.klo);
 
     {   // operand split
-        const long long tq = (long long)B * H * S * (kHd / 4), tk = (long long)B * KVH * S * (kHd / 4);
         auto vec_ok = [](const float* p, const long long* s) {
             return aligned16(p) && s[0] % 4 == 0 && s[1] % 4 == 0 && s[2] % 4 == 0;
         };
-        split_tf32_kernel<<<(unsigned)std::min<long long>((tq + 255) / 256, 148 * 16), 256, 0, st>>>(
-            Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S, tq, qhi, qlo, vec_ok(Q, q_strides_host));
-        split_tf32_kernel<<<(unsigned)std::min<long long>((tk + 255) / 256, 148 * 16), 256, 0, st>>>(
-            K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH, S, tk, khi, klo, vec_ok(K, k_strides_host));
+        SPLITQ_REQUIRE((long long)B * H <= 65535, SPLITQ_ERR_ARG, "importance_fused: B*H=%lld > 65535", (long long)B * H);
+        const unsigned gx = (unsigned)cdiv((long long)S * (kHd / 4), 256 * 4);
+        split_tf32_kernel<<<dim3(gx, B * H), 256, 0, st>>>(Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S,
+                                                        qhi, qlo, vec_ok(Q, q_strides_host));
+        split_tf32_kernel<<<dim3(gx, B * KVH), 256, 0, st>>>(K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH,
+                                                          S, khi, klo, vec_ok(K, k_strides_host));
         SPLITQ_LAUNCH_CHECK("split_tf32_kernel");
     }
 
@@ -591,6 +748,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     p.lse2 = (float*)(w8 + wl.lse);
     p.part_col = (float*)(w8 + wl.pcol);
     p.part_last = (float*)(w8 + wl.plast);
+    p.qhi = qhi; p.qlo = qlo; p.khi = khi; p.klo = klo;
 
     static bool attr_set[64] = {};
     int dev = 0, sms = 148;
