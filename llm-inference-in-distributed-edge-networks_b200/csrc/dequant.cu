@@ -28,42 +28,59 @@ struct NormArgs {
     float* normed2;
 };
 
-__device__ __forceinline__ float decode_field(uint32_t w, int i, int nb, float L, float m) {
+// q / L for the three level counts, without the general division: one multiplication by the
+// correctly rounded reciprocal plus one Newton correction through FMA gives the correctly rounded
+// quotient for every code q in [-128, 127] and L in {1, 7, 127} (checked exhaustively against
+// __fdiv_rn by tests/test_kernels_gpu.py::test_every_code_dequantises_like_ieee_division).
+__device__ __forceinline__ float div_levels(float q, float L, float rL) {
+    const float y = __fmul_rn(q, rL);
+    const float e = __fmaf_rn(-L, y, q);
+    return __fmaf_rn(e, rL, y);
+}
+__device__ __forceinline__ float decode_field(uint32_t w, int i, int nb, float L, float rL, float m) {
     const int q = (int)(w << (32 - nb * (i + 1))) >> (32 - nb);  // sign-extend field i
-    return __fmul_rn(__fdiv_rn((float)q, L), m);
+    return __fmul_rn(div_levels((float)q, L, rL), m);
 }
 
 struct RowInfo {
     int nb;
-    float m, L;
+    float m, L, rL;
     bool nan_row, bad;
     const uint8_t* src;
 };
 
 __device__ __forceinline__ RowInfo row_info(const uint8_t* P, int S, int D, int t) {
     RowInfo r;
-    const uint32_t* hdr = reinterpret_cast<const uint32_t*>(P);
-    const int mode = (int)hdr[1];
-    r.bad = hdr[0] != SPLITQ_MAGIC || hdr[2] != (uint32_t)S || hdr[3] != (uint32_t)D ||
+    // every index load below is independent of the others (section offsets depend only on S), so
+    // they are all in flight at once; only the row data depends on them
+    const uint4 h0 = __ldg(reinterpret_cast<const uint4*>(P));
+    const uint4 h1 = __ldg(reinterpret_cast<const uint4*>(P) + 1);
+    const PayloadLayout lt = payload_layout((uint32_t)S, SPLITQ_SCALE_TOKEN);
+    const int nb = P[lt.bits_off + t];
+    const uint32_t off16 = __ldg(reinterpret_cast<const uint32_t*>(P + lt.rowoff_off) + t);
+    const float4 gs = __ldg(reinterpret_cast<const float4*>(P + lt.scales_off));  // group slots (or tokens 0..3)
+    const float ts = __ldg(reinterpret_cast<const float*>(P + lt.scales_off) + t);  // token slot (inside the payload in either mode)
+    const int mode = (int)h0.y;
+    r.bad = h0.x != SPLITQ_MAGIC || h0.z != (uint32_t)S || h0.w != (uint32_t)D ||
             (mode != SPLITQ_SCALE_GROUP && mode != SPLITQ_SCALE_TOKEN);
-    const PayloadLayout lay = payload_layout((uint32_t)S, mode == SPLITQ_SCALE_TOKEN ? SPLITQ_SCALE_TOKEN : SPLITQ_SCALE_GROUP);
-    r.nb = P[lay.bits_off + t];
-    const uint32_t off16 = reinterpret_cast<const uint32_t*>(P + lay.rowoff_off)[t];
-    r.src = P + lay.codes_off + (size_t)off16 * 16u;
+    r.nb = nb;
+    r.src = P + h1.y /* codes_offset */ + (size_t)off16 * 16u;
     r.m = 0.f;
     r.L = 1.f;
+    r.rL = 1.f;
     r.nan_row = false;
-    if (r.nb != SPLITQ_BITS_RAW) {
-        if (r.nb != 2 && r.nb != 4 && r.nb != 8) {
+    if (nb != SPLITQ_BITS_RAW) {
+        if (nb != 2 && nb != 4 && nb != 8) {
             r.bad = true;
             r.nb = 8;
         }
-        const float* scales = reinterpret_cast<const float*>(P + lay.scales_off);
-        r.m = mode == SPLITQ_SCALE_GROUP ? scales[slot_of_bits(r.nb)] : scales[t];
+        r.m = mode == SPLITQ_SCALE_GROUP ? (r.nb == 8 ? gs.x : (r.nb == 4 ? gs.y : gs.z)) : ts;
         r.L = (float)((1 << (r.nb - 1)) - 1);
+        r.rL = r.nb == 8 ? 0x1.020408p-7f : (r.nb == 4 ? 0x1.24924ap-3f : 1.0f);  // fl(1/127), fl(1/7), 1
         // reference semantics: one scale for the set, all zeros -> 0/0 -> NaN rows
         r.nan_row = mode == SPLITQ_SCALE_GROUP && r.m == 0.f;
     }
+    if (r.bad) r.src = P;  // never dereference an offset taken from a corrupt header
     return r;
 }
 
@@ -106,10 +123,10 @@ dequant_kernel(const uint8_t* __restrict__ payload, size_t stride, int S, int D,
         }
 #pragma unroll
         for (int u = 0; u < MAXCH; ++u) {
-            v[u].x = decode_field(w[u], 0, r.nb, r.L, r.m);
-            v[u].y = decode_field(w[u], 1, r.nb, r.L, r.m);
-            v[u].z = decode_field(w[u], 2, r.nb, r.L, r.m);
-            v[u].w = decode_field(w[u], 3, r.nb, r.L, r.m);
+            v[u].x = decode_field(w[u], 0, r.nb, r.L, r.rL, r.m);
+            v[u].y = decode_field(w[u], 1, r.nb, r.L, r.rL, r.m);
+            v[u].z = decode_field(w[u], 2, r.nb, r.L, r.rL, r.m);
+            v[u].w = decode_field(w[u], 3, r.nb, r.L, r.rL, r.m);
             if (r.nan_row) v[u] = make_float4(qnan, qnan, qnan, qnan);
         }
     }
@@ -194,7 +211,7 @@ dequant_generic_kernel(const uint8_t* __restrict__ payload, size_t stride, int S
         if (r.nb == SPLITQ_BITS_RAW) return reinterpret_cast<const float*>(r.src)[d];
         const int per = 8 / r.nb;
         const uint32_t byte = r.src[d / per];
-        return decode_field(byte, d % per, r.nb, r.L, r.m);
+        return decode_field(byte, d % per, r.nb, r.L, r.rL, r.m);
     };
     if (h_out)
         for (int d = lane; d < D; d += 32) h_out[tok * D + d] = value(d);

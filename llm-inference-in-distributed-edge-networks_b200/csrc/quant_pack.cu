@@ -27,12 +27,25 @@ __device__ __forceinline__ int code_of(float x, float m, float L, float lo) {
     return (int)rintf(s);  // round half to even, like torch.round
 }
 
-__device__ __forceinline__ uint32_t pack4(float4 v, float m, float L, float lo, int nb) {
+// Same result as code_of() for every input, at a fraction of the instruction count: the IEEE
+// division is replaced by a multiplication with rcp = 1/m, which can differ from the exact
+// sequence by at most ~3e-7 * |s| <= 4e-5 in s; whenever s is farther than 2^-13 from a rounding
+// boundary (k + 1/2) that cannot change the rounded code, otherwise (about 1 element in 4000, and
+// always for NaN/Inf) the exact sequence decides.  Codes therefore stay bit-identical to ATen.
+__device__ __forceinline__ int code_fast(float x, float m, float rcp, float L, float lo) {
+    const float s = __fmul_rn(__fmul_rn(x, rcp), L);
+    const float r = rintf(s);
+    if (fabsf(fabsf(s - r) - 0.5f) > 1.220703125e-4f)  // false for NaN
+        return (int)fminf(fmaxf(r, lo), L);
+    return code_of(x, m, L, lo);
+}
+
+__device__ __forceinline__ uint32_t pack4(float4 v, float m, float rcp, float L, float lo, int nb) {
     const uint32_t mask = (1u << nb) - 1u;
-    const uint32_t q0 = (uint32_t)code_of(v.x, m, L, lo) & mask;
-    const uint32_t q1 = (uint32_t)code_of(v.y, m, L, lo) & mask;
-    const uint32_t q2 = (uint32_t)code_of(v.z, m, L, lo) & mask;
-    const uint32_t q3 = (uint32_t)code_of(v.w, m, L, lo) & mask;
+    const uint32_t q0 = (uint32_t)code_fast(v.x, m, rcp, L, lo) & mask;
+    const uint32_t q1 = (uint32_t)code_fast(v.y, m, rcp, L, lo) & mask;
+    const uint32_t q2 = (uint32_t)code_fast(v.z, m, rcp, L, lo) & mask;
+    const uint32_t q3 = (uint32_t)code_fast(v.w, m, rcp, L, lo) & mask;
     return q0 | (q1 << nb) | (q2 << (2 * nb)) | (q3 << (3 * nb));
 }
 
@@ -162,6 +175,7 @@ quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __re
     }
     const float L = (float)((1 << (nb - 1)) - 1);
     const float lo = -(L + 1.f);
+    const float rcp = __fdiv_rn(1.0f, m);
     const uint32_t rb = row_bytes((uint32_t)D, (uint32_t)nb);
     // chunk c (4 elements) occupies nb/2 bytes at byte c*nb/2; chunks past D pad the row with zeros
 #pragma unroll
@@ -169,7 +183,7 @@ quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __re
         const int c = lane + 32 * u;
         const uint32_t byte = (uint32_t)c * (uint32_t)nb >> 1;
         if (byte < rb) {
-            const uint32_t w = pack4(v[u], m, L, lo, nb);
+            const uint32_t w = pack4(v[u], m, rcp, L, lo, nb);
             if (nb == 8) reinterpret_cast<uint32_t*>(dst)[c] = w;
             else if (nb == 4) reinterpret_cast<uint16_t*>(dst)[c] = (uint16_t)w;
             else dst[c] = (uint8_t)w;

@@ -276,3 +276,64 @@ def test_full_size_roundtrip_properties():
     assert torch.equal(p2[:, lay[3]:], res.payload[:, lay[3]:])
     hdr = res.payload[0, :32].cpu().numpy().view(np.uint32)
     assert hdr[0] == O.MAGIC and hdr[2] == S and hdr[3] == D and hdr[6] == plan.nbytes
+
+
+@pytest.mark.parametrize("mode", [O.SCALE_GROUP, O.SCALE_TOKEN])
+def test_every_code_dequantises_like_ieee_division(mode):
+    """Hand-built payloads holding every code of every width, many scales: the kernel's
+    reciprocal + FMA-correction division must equal the oracle's q / L * m bit for bit."""
+    import struct
+    rng = np.random.default_rng(0)
+    D, S = 256, 3
+    bits = np.array([8, 4, 2], dtype=np.uint8)
+    codes = [np.arange(-128, 128), np.tile(np.arange(-8, 8), 16), np.tile(np.arange(-2, 2), 64)]
+    bits_off, rowoff_off, scales_off, codes_off = O.payload_layout(S, D, mode)
+    rb = [O.row_bytes(D, int(b)) for b in bits]
+    total = codes_off + sum(rb)
+    payloads = []
+    for trial in range(64):
+        scales = np.exp(rng.uniform(-20, 20, size=3)).astype(np.float32)
+        buf = np.zeros(total, dtype=np.uint8)
+        n_scales = O.GROUP_SLOTS if mode == O.SCALE_GROUP else S
+        buf[:32] = np.frombuffer(struct.pack("<8I", O.MAGIC, mode, S, D, n_scales, codes_off, total, 0), dtype=np.uint8)
+        buf[bits_off:bits_off + S] = bits
+        offs = (np.cumsum(rb) - rb) // 16
+        buf[rowoff_off:rowoff_off + 4 * S] = offs.astype(np.uint32).view(np.uint8)
+        sc = np.zeros(n_scales, dtype=np.float32)
+        sc[:3] = scales  # slots 8/4/2-bit in group mode, tokens 0..2 in token mode
+        buf[scales_off:scales_off + 4 * n_scales] = sc.view(np.uint8)
+        off = codes_off
+        for t in range(S):
+            packed = O._pack_row(codes[t].astype(np.int8), int(bits[t]))
+            buf[off:off + packed.size] = packed
+            off += rb[t]
+        payloads.append(buf)
+    dev = torch.from_numpy(np.stack(payloads)).to(DEV)
+    got = splitq.dequant(dev, S, D).cpu().numpy()
+    for i, buf in enumerate(payloads):
+        want = O.unpack_payload(buf).numpy()
+        assert np.array_equal(got[i].view(np.uint32), want.view(np.uint32)), i
+
+
+def test_codes_bit_exact_near_rounding_boundaries():
+    """Values engineered to sit on and next to the k + 1/2 rounding boundaries, where the fast
+    reciprocal path must defer to the exact IEEE sequence."""
+    S, D = 64, 512
+    gen = torch.Generator().manual_seed(11)
+    for bits_w in (8, 4, 2):
+        L = O.levels(bits_w)
+        m = torch.rand(S, 1, generator=gen) * 10 + 0.1
+        k = torch.randint(-L, L, (S, D), generator=gen).float() + 0.5
+        h = k / L * m                                   # lands on a boundary up to rounding
+        ulp = torch.randint(-3, 4, (S, D), generator=gen, dtype=torch.int32)
+        h = (h.view(torch.int32) + ulp).view(torch.float32)
+        h[:, 0] = m[:, 0]                               # pin the row absmax
+        h = torch.clamp(h, -m, m).unsqueeze(0)
+        imp = torch.rand(1, S, generator=gen)
+        ladder = [(S, bits_w)]
+        for mode in (O.SCALE_GROUP, O.SCALE_TOKEN):
+            nbytes = splitq.payload_bytes(S, D, ladder, mode)
+            bits, off = splitq.select_bits(imp.to(DEV), ladder, D)
+            got = splitq.quant_pack(h.to(DEV), bits, off, mode, nbytes)[0].cpu().numpy()
+            want = O.pack_payload(h[0], O.ladder_bits(imp[0], ladder), mode)
+            assert np.array_equal(got, want), (bits_w, mode)
