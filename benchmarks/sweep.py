@@ -1,0 +1,119 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[4]: importance + quantise + pack microbench sweep.
+
+  S in {512 .. 16384} x (D, H, KVH) in {(512, 8, 8) Pythia-70M, (896, 14, 2) Qwen2-0.5B},
+  importance from materialised attention (K1) vs fused Q/K recompute (K2, 3xTF32),
+  then select + quantise + pack (8/4/2-bit ladder, per-token scale).
+
+Batch B per point is chosen so the attention maps (materialised) or Q/K/h (fused) exceed the
+126 MB L2 where memory allows; CUDA-event timing, median of --iters runs after warm-up.
+Prints one JSON object per point and writes them to --out.
+
+    python benchmarks/sweep.py [--out profiles/sweep.json] [--iters 20] [--max-s 16384]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "llm-inference-in-distributed-edge-networks_b200"))
+
+import torch  # noqa: E402
+
+import splitq  # noqa: E402
+from splitq import _native as N  # noqa: E402
+
+SHAPES = [("pythia-70m", 512, 8, 8), ("qwen2-0.5b", 896, 14, 2)]
+FRACS = [(0.25, 2), (0.25, 4), (0.25, 8)]
+
+
+def timeit(fn, iters):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    times = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        times.append(a.elapsed_time(b))
+    return statistics.median(times)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=os.path.join(ROOT, "profiles", "sweep.json"))
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--max-s", type=int, default=16384)
+    ap.add_argument("--mem-gb", type=float, default=24.0, help="cap on the attention-map batch")
+    args = ap.parse_args()
+    peaks = {}
+    if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")):
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    hbm, bf16 = peaks.get("hbm_gbs", 6650.0), peaks.get("bf16_tflops", 1590.0)
+    dev = torch.device("cuda:0")
+    gen = torch.Generator(device=dev).manual_seed(0)
+    results = []
+    for name, D, H, KVH in SHAPES:
+        S = 512
+        while S <= args.max_s:
+            ladder = splitq.ladder_from_fractions(FRACS, S)
+            nbytes = splitq.payload_bytes(S, D, ladder, N.SCALE_TOKEN)
+            # ---- fused: B so that Q + K + h >= ~256 MB
+            per_win = 4 * S * (64 * (H + KVH) + D)
+            Bf = max(1, min(64, (256 << 20) // per_win))
+            q = torch.randn(Bf, H, S, 64, device=dev, generator=gen)
+            k = torch.randn(Bf, KVH, S, 64, device=dev, generator=gen)
+            h = torch.randn(Bf, S, D, device=dev, generator=gen)
+            imp = torch.empty(Bf, S, device=dev)
+            bits = torch.empty(Bf, S, dtype=torch.uint8, device=dev)
+            roff = torch.empty(Bf, S, dtype=torch.int32, device=dev)
+            payload = torch.empty(Bf, nbytes, dtype=torch.uint8, device=dev)
+            t_k2 = timeit(lambda: splitq.importance_fused(q, k, 0.125, out_col=imp), args.iters)
+            t_sel = timeit(lambda: splitq.select_bits(imp, ladder, D, bits, roff), args.iters)
+            t_qp = timeit(lambda: splitq.quant_pack(h, bits, roff, N.SCALE_TOKEN, nbytes, payload), args.iters)
+            nb = (S + 127) // 128
+            issued = Bf * H * nb * (nb + 1) * 2.0 * 128 * 128 * 64 * 3
+            qp_bytes = Bf * (4 * S * D + 5 * S + nbytes)
+            rec = {"model_shape": name, "S": S, "D": D, "H": H, "KVH": KVH,
+                   "fused": {"B": Bf, "k2_ms": t_k2, "tokens_per_s": Bf * S / (t_k2 * 1e-3),
+                             "issued_tf32_tflops": issued / (t_k2 * 1e-3) / 1e12,
+                             "frac_of_tf32_peak": issued / (t_k2 * 1e-3) / 1e12 / (bf16 / 2)},
+                   "select_ms": t_sel,
+                   "quant_pack": {"ms": t_qp, "GBps": qp_bytes / (t_qp * 1e-3) / 1e9,
+                                  "frac_of_hbm_peak": qp_bytes / (t_qp * 1e-3) / 1e9 / hbm}}
+            del q, k
+            # ---- materialised: B so that A >= ~1 GB (or 1 window when a window is larger)
+            a_win = 4 * H * S * S
+            Bm = max(1, min(Bf, int((1 << 30) // a_win) or 1))
+            if Bm * a_win <= args.mem_gb * (1 << 30):
+                A = torch.empty(Bm, H, S, S, device=dev)
+                mask = torch.full((S, S), float("-inf"), device=dev).triu(1)
+                for b in range(Bm):
+                    for hh in range(H):  # one head at a time keeps the transient small at S=16384
+                        A[b, hh] = torch.softmax(torch.randn(S, S, device=dev, generator=gen) * 2.0 + mask, dim=-1)
+                impm = torch.empty(Bm, S, device=dev)
+                t_k1 = timeit(lambda: splitq.importance_from_attention(A, out_col=impm), args.iters)
+                alg = Bm * (4 * H * S * S + 4 * S)
+                rec["materialised"] = {"B": Bm, "k1_ms": t_k1, "tokens_per_s": Bm * S / (t_k1 * 1e-3),
+                                       "GBps": alg / (t_k1 * 1e-3) / 1e9, "frac_of_hbm_peak": alg / (t_k1 * 1e-3) / 1e9 / hbm,
+                                       "attention_bytes": Bm * a_win}
+                del A
+            else:
+                rec["materialised"] = {"skipped": f"attention maps need {Bm * a_win / 2**30:.1f} GiB"}
+            torch.cuda.empty_cache()
+            print(json.dumps(rec), flush=True)
+            results.append(rec)
+            S *= 2
+    with open(args.out, "w") as f:
+        json.dump({"peaks": {"hbm_gbs": hbm, "tf32_tflops": bf16 / 2}, "points": results}, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()
