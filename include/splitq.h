@@ -152,6 +152,21 @@ int splitq_dequant_norm(const uint8_t* payload, size_t payload_stride, int B, in
                         const float* gamma2, const float* beta2, float* resid_out,
                         float* normed_out, float* normed2_out, splitq_stream_t stream);
 
+/* ---- channel-wise quantisers ----------------------------------------------------------
+ * Replaces QwenPointFiveBModel.channel_wise's per-channel Python loop
+ * (Qwen2-0.5B/qwen_layer_wise.py:122-152): per-channel statistic over all B*S rows (absmax, or
+ * mean + 1e-8 for SPLITQ_CHANNEL_1_MEAN) and the in-place quantise/dequantise of every element.
+ *   h (B,S,D) -> h_out (B,S,D) (may alias h), stats_out f32[D] (the per-channel scale used),
+ *   codes_out int8 (B,S,D) or NULL (the integer codes the reference never stores). */
+#define SPLITQ_CHANNEL_8 0
+#define SPLITQ_CHANNEL_4 1
+#define SPLITQ_CHANNEL_1_MEAN 2
+#define SPLITQ_CHANNEL_1_MAX 3
+size_t splitq_channel_workspace_bytes(int B, int S, int D);
+int splitq_channel_fake_quant(const float* h, int B, int S, int D, int method, float* stats_out,
+                              float* h_out, int8_t* codes_out, void* ws, size_t ws_bytes,
+                              splitq_stream_t stream);
+
 /* ---- transfer --------------------------------------------------------------------------
  * The device hop the reference only simulates (in-place quant->dequant,
  * pythia_model.py:176-188).  cudaMemcpyPeerAsync over NVLink; src/dst may be one device. */

@@ -1,0 +1,148 @@
+// Channel-wise quantisers of the split-layer hidden states.
+//
+// Reference: QwenPointFiveBModel.channel_wise (Experiments/Qwen2-0.5B/qwen_layer_wise.py:106-167),
+// a Python loop over the D channels with ~6 ATen launches each:
+//   channel_8 / channel_4 : m = max|x_c|,  q = round(x / m * L),             x' = q * m / L   (L = 127 / 7)
+//   channel_1_mean        : u = mean(x_c) + 1e-8, q = clamp(round(x / u), -1, 1), x' = q * u
+//   channel_1_max         : m = max|x_c|,  q = clamp(round(x / m), -1, 1),   x' = q * m
+// Here: one column reduction over the B*S rows (same stripe/partial scheme as K1) and one
+// elementwise pass with IEEE division/multiplication in the reference's order.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace splitq {
+
+constexpr int kCWarps = 8;
+
+// per-(stripe, channel) partials: absmax bit pattern or fp32 sum
+template <bool MEAN>
+__global__ void __launch_bounds__(kCWarps * 32)
+channel_partial_kernel(const float* __restrict__ h, long long R, int D, int rows_per_chunk,
+                       float* __restrict__ partial) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = blockIdx.x * 128 + lane * 4;
+    const long long r0 = (long long)blockIdx.y * rows_per_chunk;
+    const long long r1 = min(R, r0 + rows_per_chunk);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long r = r0 + warp; r < r1; r += kCWarps) {
+        float v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = (c0 + i < D) ? __ldg(h + r * D + c0 + i) : 0.f;
+        if (MEAN) {
+            acc.x += v[0]; acc.y += v[1]; acc.z += v[2]; acc.w += v[3];
+        } else {
+            acc.x = fmaxf(acc.x, fabsf(v[0])); acc.y = fmaxf(acc.y, fabsf(v[1]));
+            acc.z = fmaxf(acc.z, fabsf(v[2])); acc.w = fmaxf(acc.w, fabsf(v[3]));
+        }
+    }
+    __shared__ float4 red[kCWarps][32];
+    red[warp][lane] = acc;
+    __syncthreads();
+    if (warp == 0) {
+        float4 s = red[0][lane];
+        for (int w = 1; w < kCWarps; ++w) {
+            const float4 v = red[w][lane];
+            if (MEAN) { s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+            else { s.x = fmaxf(s.x, v.x); s.y = fmaxf(s.y, v.y); s.z = fmaxf(s.z, v.z); s.w = fmaxf(s.w, v.w); }
+        }
+        float* out = partial + (size_t)blockIdx.y * D;
+        if (c0 + 0 < D) out[c0 + 0] = s.x;
+        if (c0 + 1 < D) out[c0 + 1] = s.y;
+        if (c0 + 2 < D) out[c0 + 2] = s.z;
+        if (c0 + 3 < D) out[c0 + 3] = s.w;
+    }
+}
+
+template <bool MEAN>
+__global__ void channel_finalize_kernel(const float* __restrict__ partial, int nparts, int D, long long R,
+                                        float* __restrict__ stats) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= D) return;
+    if (MEAN) {
+        double s = 0.0;
+        for (int p = 0; p < nparts; ++p) s += (double)partial[(size_t)p * D + c];
+        stats[c] = __fadd_rn((float)(s / (double)R), 1e-8f);  // torch.mean(...) + 1e-8
+    } else {
+        float m = 0.f;
+        for (int p = 0; p < nparts; ++p) m = fmaxf(m, partial[(size_t)p * D + c]);
+        stats[c] = m;
+    }
+}
+
+__device__ __forceinline__ float channel_fake(float x, float st, int method, int8_t* code) {
+    float q, out;
+    if (method == SPLITQ_CHANNEL_8 || method == SPLITQ_CHANNEL_4) {
+        const float L = method == SPLITQ_CHANNEL_8 ? 127.f : 7.f;
+        q = rintf(__fmul_rn(__fdiv_rn(x, st), L));          // round(x / m * L)
+        out = __fdiv_rn(__fmul_rn(q, st), L);               // q * m / L
+    } else {
+        q = rintf(__fdiv_rn(x, st));                        // round(x / u)
+        q = fminf(fmaxf(q, -1.f), 1.f);                     // clamp (NaN stays NaN in ATen; see below)
+        if (!(__fdiv_rn(x, st) == __fdiv_rn(x, st))) q = __uint_as_float(0x7fc00000u);
+        out = __fmul_rn(q, st);                             // q * u
+    }
+    *code = (q == q) ? (int8_t)q : (int8_t)0;
+    return out;
+}
+
+__global__ void __launch_bounds__(256)
+channel_quant_kernel(const float* __restrict__ h, long long n, int D, int method, const float* __restrict__ stats,
+                     float* __restrict__ out, int8_t* __restrict__ codes) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % D);
+        int8_t q;
+        const float y = channel_fake(h[i], __ldg(stats + c), method, &q);
+        out[i] = y;
+        if (codes) codes[i] = q;
+    }
+}
+
+static int pick_rows(long long R, int D) {
+    const long long tiles = cdiv(D, 128);
+    int rows = 512;
+    while (rows > 32 && tiles * cdiv(R, rows) < 148LL * 4) rows >>= 1;
+    return rows;
+}
+
+}  // namespace splitq
+
+using namespace splitq;
+
+extern "C" size_t splitq_channel_workspace_bytes(int B, int S, int D) {
+    if (B <= 0 || S <= 0 || D <= 0) return 0;
+    const long long R = (long long)B * S;
+    return (size_t)cdiv(R, pick_rows(R, D)) * D * sizeof(float);
+}
+
+extern "C" int splitq_channel_fake_quant(const float* h, int B, int S, int D, int method, float* stats_out,
+                                         float* h_out, int8_t* codes_out, void* ws, size_t ws_bytes,
+                                         splitq_stream_t stream) {
+    SPLITQ_REQUIRE(h && stats_out && h_out, SPLITQ_ERR_ARG, "channel_fake_quant: NULL buffer");
+    SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0, SPLITQ_ERR_ARG, "channel_fake_quant: bad shape B=%d S=%d D=%d", B, S, D);
+    SPLITQ_REQUIRE(method >= SPLITQ_CHANNEL_8 && method <= SPLITQ_CHANNEL_1_MAX, SPLITQ_ERR_ARG,
+                   "channel_fake_quant: unknown method %d", method);
+    const long long R = (long long)B * S;
+    const int rows = pick_rows(R, D), nparts = cdiv(R, rows);
+    const size_t need = (size_t)nparts * D * sizeof(float);
+    SPLITQ_REQUIRE(ws && ws_bytes >= need, SPLITQ_ERR_WORKSPACE, "channel_fake_quant: workspace %zu < %zu bytes",
+                   ws_bytes, need);
+    SPLITQ_REQUIRE(nparts <= 65535, SPLITQ_ERR_ARG, "channel_fake_quant: too many rows");
+    if (int rc = check_arch()) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid(cdiv(D, 128), nparts);
+    const bool mean = method == SPLITQ_CHANNEL_1_MEAN;
+    if (mean) {
+        channel_partial_kernel<true><<<grid, kCWarps * 32, 0, st>>>(h, R, D, rows, (float*)ws);
+        channel_finalize_kernel<true><<<cdiv(D, 256), 256, 0, st>>>((const float*)ws, nparts, D, R, stats_out);
+    } else {
+        channel_partial_kernel<false><<<grid, kCWarps * 32, 0, st>>>(h, R, D, rows, (float*)ws);
+        channel_finalize_kernel<false><<<cdiv(D, 256), 256, 0, st>>>((const float*)ws, nparts, D, R, stats_out);
+    }
+    SPLITQ_LAUNCH_CHECK("channel stats kernels");
+    const long long n = R * D;
+    const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
+    channel_quant_kernel<<<blocks, 256, 0, st>>>(h, n, D, method, stats_out, h_out, codes_out);
+    SPLITQ_LAUNCH_CHECK("channel_quant_kernel");
+    return SPLITQ_OK;
+}

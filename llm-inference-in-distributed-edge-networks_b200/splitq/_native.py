@@ -19,6 +19,7 @@ FLAG_CAUSAL_HINT = 1
 MAX_SELECT_S = 32768
 NOALLOC_MAX_WINDOWS = 1024
 FUSED_TF32X3, FUSED_TF32X1 = 0, 1
+CHANNEL_METHODS = {"channel_8": 0, "channel_4": 1, "channel_1_mean": 2, "channel_1_max": 3}
 
 _vp, _sz, _i, _u = C.c_void_p, C.c_size_t, C.c_int, C.c_uint
 _ip = C.POINTER(C.c_int)
@@ -41,6 +42,8 @@ SIGNATURES = {
     "splitq_quant_pack_group_noalloc": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "splitq_dequant": (_i, [_vp, _sz, _i, _i, _i, _vp, _vp]),
     "splitq_dequant_norm": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, C.c_float, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "splitq_channel_workspace_bytes": (_sz, [_i, _i, _i]),
+    "splitq_channel_fake_quant": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "splitq_transfer_peer": (_i, [_vp, _i, _vp, _i, _sz, _vp]),
 }
 

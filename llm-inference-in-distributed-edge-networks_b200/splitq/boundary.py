@@ -217,6 +217,28 @@ def dequant_norm(payload: torch.Tensor, S: int, D: int, kind: int, gamma: torch.
     return resid, normed, normed2
 
 
+def channel_fake_quant(h: torch.Tensor, method: str, out: Optional[torch.Tensor] = None, want_codes: bool = False):
+    """Channel-wise quantise->dequantise of (B,S,D) hidden states; method in {"channel_8",
+    "channel_4", "channel_1_mean", "channel_1_max"} (qwen_layer_wise.py:106-152).
+    Returns (h_out, per-channel scales (D,), int8 codes or None); `out=h` works in place."""
+    if method not in N.CHANNEL_METHODS:
+        raise ValueError(f"Unknown method: {method}")
+    h = _need_cuda_f32(h, "hidden_states")
+    if h.dim() == 2:
+        h = h.unsqueeze(0)
+    B, S, D = h.shape
+    out = torch.empty_like(h) if out is None else out
+    stats = torch.empty(D, dtype=torch.float32, device=h.device)
+    codes = torch.empty(B, S, D, dtype=torch.int8, device=h.device) if want_codes else None
+    lib = N.load()
+    ws_bytes = lib.splitq_channel_workspace_bytes(B, S, D)
+    ws = _WS.get(h.device, "channel", ws_bytes)
+    with torch.cuda.device(h.device):
+        N.check(lib.splitq_channel_fake_quant(_ptr(h), B, S, D, N.CHANNEL_METHODS[method], _ptr(stats), _ptr(out),
+                                              _ptr(codes), _ptr(ws), ws_bytes, _stream(h)))
+    return out, stats, codes
+
+
 def transfer(dst: torch.Tensor, src: torch.Tensor, nbytes: Optional[int] = None) -> torch.Tensor:
     """Payload hop between the halves' devices (cudaMemcpyPeerAsync; same device = D2D copy).
     Enqueued on the current stream of the SOURCE device."""

@@ -293,6 +293,14 @@ class QwenPointFiveBModel(_LayerWiseModel):
         n = layer.input_layernorm
         return N.NORM_RMSNORM, n.weight, None, n.variance_epsilon, None, None
 
+    def channel_wise(self, batched_input_tokens, target, layer_of_interest, method):
+        """Channel-wise quantisation of the whole hidden state after `layer_of_interest`
+        (qwen_layer_wise.py:106-167); method in {"channel_8","channel_4","channel_1_mean","channel_1_max"}."""
+        with torch.no_grad():
+            hidden = self.upstream(batched_input_tokens, layer_of_interest)
+            hidden, _, _ = boundary.channel_fake_quant(hidden, method, out=hidden)
+            return self.downstream(tuple(batched_input_tokens.shape), target, layer_of_interest, hidden=hidden)
+
     def _run_prenormed_layer(self, layer, resid, normed, normed2, pos):
         # Qwen2DecoderLayer.forward with input_layernorm already applied
         attn_out, _ = layer.self_attn(hidden_states=normed, attention_mask=None, position_embeddings=pos)

@@ -183,10 +183,40 @@ def golden_degenerate():
         json.dump(facts, f, indent=1)
 
 
+def golden_channel():
+    """QwenPointFiveBModel.channel_wise (qwen_layer_wise.py:106-167) on random-init models: hidden
+    states before/after the per-channel loop and the resulting NLLs."""
+    gen = torch.Generator().manual_seed(99)
+    out, book = {}, {}
+    for name, cfg, S, loi in (("qwen_tiny", compat.QWEN2_TINY, 48, 1), ("qwen2_05b", compat.QWEN2_05B, 64, 14)):
+        model = compat.build_causal_lm("qwen2", cfg, seed=0, attn_implementation="sdpa")
+        tuple_shim(model)
+        wrapper = make_qwen_wrapper(model)
+        layers = model.base_model.layers
+        ids = torch.randint(0, cfg["vocab_size"], (1, S), generator=gen)
+        book[name] = {"S": S, "ids": ids[0].tolist(), "layer": loi, "nll": {}}
+        for method in ("channel_8", "channel_4", "channel_1_mean", "channel_1_max"):
+            grabbed = {}
+            h1 = layers[loi].register_forward_hook(
+                lambda m, i, o: grabbed.__setitem__("pre", (o[0] if isinstance(o, tuple) else o).clone()))
+            h2 = layers[loi + 1].register_forward_pre_hook(lambda m, a: grabbed.__setitem__("post", a[0].clone()))
+            nll = wrapper.channel_wise(ids, ids.clone(), loi, method)
+            h1.remove(), h2.remove()
+            book[name]["nll"][method] = nll.item()
+            if name == "qwen_tiny" or method in ("channel_4", "channel_1_mean"):
+                out[f"{name}|{method}|pre"] = grabbed["pre"][0].numpy()
+                out[f"{name}|{method}|post"] = grabbed["post"][0].numpy()
+        print(name, book[name]["nll"], flush=True)
+    np.savez_compressed(os.path.join(GOLD, "channel_quant.npz"), **out)
+    with open(os.path.join(GOLD, "channel_nll.json"), "w") as f:
+        json.dump(book, f, indent=1)
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(8)
-    golden_importance()
-    golden_degenerate()
-    golden_wrappers()
+    todo = sys.argv[1:] or ["importance", "degenerate", "wrappers", "channel"]
+    for name in todo:
+        {"importance": golden_importance, "degenerate": golden_degenerate, "wrappers": golden_wrappers,
+         "channel": golden_channel}[name]()
     print("golden fixtures written to", GOLD)

@@ -205,6 +205,29 @@ def reference_boundary_cpu_from_qk(q, k, h, scaling, ladder, scale_mode, method=
     return reference_boundary_cpu(A, h, ladder, scale_mode, method)
 
 
+def channel_fake_quant_reference(h: torch.Tensor, method: str) -> torch.Tensor:
+    """Channel-wise quantise->dequantise of (B,S,D), the arithmetic of qwen_layer_wise.py:125-152.
+    absmax variants are vectorised over channels (max is order independent); the mean variant
+    keeps the reference's per-channel torch.mean over the strided column so the scale is bit-equal."""
+    h = h.clone()
+    if method in ("channel_8", "channel_4"):
+        L = 127 if method == "channel_8" else 7
+        m = h.abs().amax(dim=(0, 1))
+        q = torch.round(h / m * L)
+        return q * m / L
+    if method == "channel_1_max":
+        m = h.abs().amax(dim=(0, 1))
+        q = torch.clamp(torch.round(h / m), -1, 1)
+        return q * m
+    if method == "channel_1_mean":
+        for c in range(h.shape[2]):
+            col = h[:, :, c]
+            u = torch.mean(col) + 1e-8
+            h[:, :, c] = torch.clamp(torch.round(col / u), -1, 1) * u
+        return h
+    raise ValueError(f"Unknown method: {method}")
+
+
 # --------------------------------------------------------------------------------------
 # packed payload (our format; see header comment)
 # --------------------------------------------------------------------------------------
