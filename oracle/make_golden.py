@@ -212,11 +212,23 @@ def golden_channel():
         json.dump(book, f, indent=1)
 
 
+def golden_initial():
+    """extract_attentions of the reference's first experiment (initial_exp.py:27-72) on the 3-layer
+    synthetic attention maps already stored in importance.npz (tag "a")."""
+    import initial_exp  # reference
+    g = np.load(os.path.join(GOLD, "importance.npz"))
+    A = torch.from_numpy(g["a_A"])
+    maps = [A[l] for l in range(A.shape[0])]
+    keys = ["aggregate upto 2", "maximum aggregation", "upto ratio", 0, 2]
+    res = initial_exp.extract_attentions(maps, keys)
+    np.savez_compressed(os.path.join(GOLD, "initial_orderings.npz"), **{str(k): np.asarray(v) for k, v in res.items()})
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(8)
-    todo = sys.argv[1:] or ["importance", "degenerate", "wrappers", "channel"]
+    todo = sys.argv[1:] or ["importance", "degenerate", "wrappers", "channel", "initial"]
     for name in todo:
         {"importance": golden_importance, "degenerate": golden_degenerate, "wrappers": golden_wrappers,
-         "channel": golden_channel}[name]()
+         "channel": golden_channel, "initial": golden_initial}[name]()
     print("golden fixtures written to", GOLD)

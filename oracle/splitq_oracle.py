@@ -378,6 +378,44 @@ def rms_norm(x: torch.Tensor, gamma: torch.Tensor, eps: float) -> torch.Tensor:
 
 
 # --------------------------------------------------------------------------------------
+# (8f-4) layer-distance analytics, numpy like the notebook
+# --------------------------------------------------------------------------------------
+def kl_divergence_np(p: np.ndarray, q: np.ndarray) -> float:
+    """Notebooks/distributions_distance_across_layers.ipynb cell 12."""
+    with np.errstate(divide="ignore", invalid="ignore"):
+        return float(np.sum(np.where(p != 0, p * np.log2(p / q), 0)))
+
+
+def jensen_shannon_np(p: np.ndarray, q: np.ndarray) -> float:
+    """Same notebook, cell 13 (`jenson_shannon_distance`)."""
+    m = 0.5 * (p + q)
+    return 0.5 * (kl_divergence_np(p, m) + kl_divergence_np(q, m))
+
+
+def layer_distance_matrix_np(dist: np.ndarray) -> np.ndarray:
+    """Same notebook, cell 16: upper triangle of sample-averaged JS divergences."""
+    L, N = dist.shape[0], dist.shape[1]
+    out = np.full((L, L), np.nan)
+    for i in range(L):
+        for j in range(i + 1, L):
+            out[i, j] = sum(jensen_shannon_np(dist[i][s], dist[j][s]) for s in range(N)) / N
+    return out
+
+
+def top_rho_keep_count(distribution: np.ndarray, ratio: float) -> int:
+    """pythia_model.py:93-106: iterate the descending distribution until the running total reaches
+    1 - 0.1*ratio; returns how many tokens were taken."""
+    threshold = 1 - 0.1 * ratio
+    total, n = 0, 0
+    for value in sorted(distribution.tolist(), reverse=True):
+        if total >= threshold:
+            break
+        total += value
+        n += 1
+    return n
+
+
+# --------------------------------------------------------------------------------------
 # (a12) sliding-window schedule and accounting
 # --------------------------------------------------------------------------------------
 def window_schedule(n_tokens: int, max_length: int, stride: int):
