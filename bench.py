@@ -210,7 +210,7 @@ def main() -> None:
                          "materialised: scores from attention probabilities already in HBM (K1)")
     ap.add_argument("--fused-mode", default="tf32x3", choices=["tf32x3", "tf32x1"])
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -253,22 +253,22 @@ def main() -> None:
     else:
         A, h = synth_inputs(cfg, B, device, seed=1234 + rank)
 
+    def make_plan():
+        pl = splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=cfg["scale_mode"], method=cfg["method"],
+                                 src_device=device, KVH=KVH, fused_mode=plan.fused_mode)
+        pl.transport = plan.transport
+        return pl
+
+    # software pipeline over steps: hop + dequantise of step i on a side stream under the scoring of i+1
+    ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused)
+    dev_inputs = (q, k, h) if fused else (A, h)
+
     def step(timed_events=None):
-        if timed_events is not None:
-            timed_events[0].record()
-        if fused:
-            plan.score_fused(q, k)
-        else:
-            plan.score(A)
-        if timed_events is not None:
-            timed_events[1].record()
-        plan.send(h)
-        plan.hop()
-        plan.receive()
+        ob.step(*dev_inputs, score_events=timed_events)
 
     for _ in range(args.warmup):
         step()
-    torch.cuda.synchronize()
+    ob.drain()
     if dist is not None:
         dist.barrier()
         torch.cuda.synchronize()
@@ -280,6 +280,7 @@ def main() -> None:
     t0.record()
     for i in range(args.steps):
         step(k_events[i])
+    ob.main.wait_stream(ob.side)  # the clock stops when the last step's dequantise has finished
     t1.record()
     torch.cuda.synchronize()
     if dist is not None:
@@ -288,22 +289,24 @@ def main() -> None:
     elapsed_ms = t0.elapsed_time(t1)
     score_ms = sum(a.elapsed_time(b) for a, b in k_events) / args.steps
 
-    # ---- end to end through the public host-buffer API: H2D of the step's inputs, the path, D2H
+    # ---- end to end through the public host-buffer API (splitq.HostPipeline): every step uploads its
+    # inputs from pinned host memory, runs the path, and downloads the dequantised hidden states;
+    # consecutive steps overlap on three streams, the clock stops when the last result is on the host
     pin = lambda t: torch.empty(t.shape, dtype=torch.float32, pin_memory=True).copy_(t)  # noqa: E731
     h_host, out_host = pin(h), torch.empty(h.shape, dtype=torch.float32, pin_memory=True)
-    if fused:
-        q_host, k_host = pin(q), pin(k)
-        run_e2e = lambda: plan.run_host_fused(q_host, k_host, h_host, out_host)  # noqa: E731
-    else:
-        A_host = pin(A)
-        run_e2e = lambda: plan.run_host(A_host, h_host, out_host)  # noqa: E731
+    inputs_host = [pin(q), pin(k), h_host] if fused else [pin(A), h_host]
+
+    pipe = splitq.HostPipeline(make_plan, depth=2, fused=fused)
     torch.cuda.synchronize()
-    run_e2e()
+    for _ in range(2):
+        pipe.submit(inputs_host, out_host)
+    pipe.drain()
     if dist is not None:
         dist.barrier()
     e0 = time.perf_counter()
     for _ in range(args.e2e_steps):
-        run_e2e()
+        pipe.submit(inputs_host, out_host)
+    pipe.drain()
     e2e_s = time.perf_counter() - e0
     clocks = sampler.finish()
 
@@ -357,10 +360,12 @@ def main() -> None:
                        "ladder": ladder, "scale_mode": "token" if cfg["scale_mode"] else "group",
                        "importance_impl": args.importance + (f" ({args.fused_mode})" if fused else ""),
                        "payload_bytes_per_window": plan.nbytes,
-                       "transfer": "nccl pair exchange" if world > 1 else "device-to-device copy", "l2": l2_note},
+                       "transfer": "nccl pair exchange" if world > 1 else "device-to-device copy", "l2": l2_note,
+                       "pipelining": "hop + dequantise of step i on a side stream, overlapping the scoring of step i+1"},
             "roofline": roofline,
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": args.e2e_steps},
+                    "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
+                    "api": "splitq.HostPipeline.submit/drain (pinned host buffers, 3 streams, depth 2)"},
             "gpu_launches": plan.launches_per_run(fused) * args.steps,
             "clocks": clocks,
         }

@@ -374,3 +374,101 @@ class BoundaryPlan:
         n += 2 if self.scale_mode == N.SCALE_GROUP else 1
         n += 1
         return n
+
+
+class HostPipeline:
+    """Host-buffer front end that keeps PCIe and the GPU busy at the same time.
+
+    `submit()` takes one step's inputs in (pinned) HOST memory, enqueues their host->device copy
+    on a copy stream, the whole boundary path on the compute stream and the device->host read of
+    the dequantised hidden states on a second copy stream, and returns without waiting; successive
+    steps alternate between `depth` buffer sets, so the upload of step i+1 and the download of step
+    i-1 overlap the kernels of step i.  `drain()` blocks until every submitted result is on the
+    host.  Works for the fused (q, k, h) and the materialised (A, h) inputs."""
+
+    def __init__(self, make_plan, depth: int = 2, fused: bool = True):
+        self.plans = [make_plan() for _ in range(depth)]
+        self.fused = fused
+        dev = self.plans[0].src
+        self.compute = torch.cuda.current_stream(dev)
+        self.h2d = torch.cuda.Stream(dev)
+        self.d2h = torch.cuda.Stream(self.plans[0].dst)
+        self.slot = 0
+        for p in self.plans:
+            p._in = None
+            p._compute_done = None
+            p._d2h_done = None
+
+    def submit(self, inputs_host: Sequence[torch.Tensor], out_host: torch.Tensor) -> None:
+        p = self.plans[self.slot]
+        self.slot = (self.slot + 1) % len(self.plans)
+        if p._in is None:
+            p._in = [torch.empty(t.shape, dtype=t.dtype, device=p.src) for t in inputs_host]
+        with torch.cuda.stream(self.h2d):
+            if p._compute_done is not None:  # the step that last used this buffer set has consumed its inputs
+                self.h2d.wait_event(p._compute_done)
+            for d, h in zip(p._in, inputs_host):
+                d.copy_(h, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(self.h2d)
+        self.compute.wait_event(ready)
+        if p._d2h_done is not None:  # ... and its result has left the device
+            self.compute.wait_event(p._d2h_done)
+        if self.fused:
+            p.run_fused(*p._in)
+        else:
+            p.run(*p._in)
+        p._compute_done = torch.cuda.Event()
+        p._compute_done.record(torch.cuda.current_stream(p.dst))
+        with torch.cuda.stream(self.d2h):
+            self.d2h.wait_event(p._compute_done)
+            out_host.copy_(p.h_out, non_blocking=True)
+            p._d2h_done = torch.cuda.Event()
+            p._d2h_done.record(self.d2h)
+
+    def drain(self) -> None:
+        self.d2h.synchronize()
+        self.compute.synchronize()
+
+
+class OverlappedBoundary:
+    """Device-resident variant of the same software pipeline: scoring + select + quantise/pack of
+    step i+1 run on the main stream while the payload hop (peer copy or NCCL pair exchange) and the
+    dequantise of step i run on a side stream; `depth` payload/output buffer sets alternate."""
+
+    def __init__(self, make_plan, depth: int = 2, fused: bool = True):
+        self.plans = [make_plan() for _ in range(depth)]
+        self.fused = fused
+        self.main = torch.cuda.current_stream(self.plans[0].src)
+        self.side = torch.cuda.Stream(self.plans[0].src)
+        self.slot = 0
+        for p in self.plans:
+            p._xfer_done = None
+
+    def step(self, *inputs: torch.Tensor, score_events=None) -> "BoundaryPlan":
+        p = self.plans[self.slot]
+        self.slot = (self.slot + 1) % len(self.plans)
+        if p._xfer_done is not None:  # this slot's payload and output buffers are free again
+            self.main.wait_event(p._xfer_done)
+        if score_events is not None:
+            score_events[0].record(self.main)
+        if self.fused:
+            p.score_fused(inputs[0], inputs[1])
+        else:
+            p.score(inputs[0])
+        if score_events is not None:
+            score_events[1].record(self.main)
+        p.send(inputs[-1])
+        packed = torch.cuda.Event()
+        packed.record(self.main)
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(packed)
+            p.hop()
+            p.receive()
+            p._xfer_done = torch.cuda.Event()
+            p._xfer_done.record(self.side)
+        return p
+
+    def drain(self) -> None:
+        self.side.synchronize()
+        self.main.synchronize()
