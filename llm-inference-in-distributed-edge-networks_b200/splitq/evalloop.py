@@ -67,7 +67,7 @@ class _Dist:
 
 def evaluate(params: dict, wrapper, input_ids: torch.Tensor, importance_fn: Callable, max_length: int,
              out_prefix: Optional[str] = None, checkpoint_every: int = 1000, reduce_device=None, group=None,
-             log: Callable = print) -> EvalResult:
+             log: Callable = print, batch_methods: bool = False) -> EvalResult:
     """Run the (method, layer, ratio) sweep over this rank's share of the windows.
 
     params         the reference's params.json dict: ratios, layers_of_interest, methods, stride
@@ -75,6 +75,8 @@ def evaluate(params: dict, wrapper, input_ids: torch.Tensor, importance_fn: Call
     wrapper        a splitq.models wrapper (needs upstream/boundary_send/boundary_hop/downstream)
     input_ids      (1, N) token stream (encodings.input_ids)
     importance_fn  (window_ids (1,S)) -> {method: [importance (S,) per layer]}
+    batch_methods  push the M methods of one (layer, ratio) through the downstream half as one batch
+                   (same arithmetic per row; cuBLAS may pick other kernels, so NLLs agree to ~1e-6)
     out_prefix     if set, rank 0 writes <prefix>total_nll*.pkl / n_tokens*.pkl / avg_ppl_results*.pkl
     """
     ratios, lois, methods = params["ratios"], params["layers_of_interest"], params["methods"]
@@ -99,6 +101,19 @@ def evaluate(params: dict, wrapper, input_ids: torch.Tensor, importance_fn: Call
                 hidden = wrapper.upstream(ids, loi)  # once per split layer
                 shape = tuple(ids.shape)
                 base = None
+                if batch_methods and M > 1 and hidden.shape[0] == 1:
+                    # one downstream pass per ratio with the M methods as the batch
+                    hid_m = hidden.expand(M, -1, -1).contiguous()
+                    tgt_m = target.expand(M, -1)
+                    imp_m = torch.stack([imp[method][loi] for method in methods])
+                    for r, ratio in enumerate(ratios):
+                        if ratio > 0:
+                            payload = wrapper.boundary_hop(wrapper.boundary_send(hid_m, imp_m, ratio))
+                            nll_dev[:, l, r] = wrapper.downstream((M, shape[1]), tgt_m, loi, payload=payload,
+                                                                  per_sequence=True)
+                        else:
+                            nll_dev[:, l, r] = wrapper.downstream(shape, target, loi, hidden=hidden)
+                    continue
                 for m, method in enumerate(methods):
                     for r, ratio in enumerate(ratios):
                         if ratio > 0:

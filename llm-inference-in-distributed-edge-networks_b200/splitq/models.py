@@ -115,14 +115,21 @@ class _LayerWiseModel:
             ids.size(0), -1)
         return model.base_model.rotary_emb(hidden, position_ids)
 
-    def last_portion(self, post_norm, target, model=None):
-        """LM head + shifted cross entropy (qwen_layer_wise.py:28-40, pythia_model.py:193-203)."""
+    def last_portion(self, post_norm, target, model=None, per_sequence=False):
+        """LM head + shifted cross entropy (qwen_layer_wise.py:28-40, pythia_model.py:193-203).
+        per_sequence=True returns one mean NLL per batch row (used when several (method, ratio)
+        variants of the same window are pushed through the downstream half as one batch)."""
         model = model or self._down
         logits = self._lm_head(model)(post_norm)
         target = target[:, 1:].to(logits.device)
         logits = logits[:, :-1, :]
-        return torch.nn.functional.cross_entropy(logits.reshape(-1, logits.size(-1)), target.reshape(-1),
-                                                 ignore_index=-100)
+        if not per_sequence:
+            return torch.nn.functional.cross_entropy(logits.reshape(-1, logits.size(-1)), target.reshape(-1),
+                                                     ignore_index=-100)
+        tok = torch.nn.functional.cross_entropy(logits.reshape(-1, logits.size(-1)), target.reshape(-1),
+                                                ignore_index=-100, reduction="none").view(target.shape)
+        valid = (target != -100).sum(dim=1).clamp_min(1)
+        return tok.sum(dim=1) / valid
 
     def ladder(self, ratio: float, S: int):
         if self.ladder_fracs is not None:  # extension: fixed multi-width ladder scaled by ratio
@@ -162,7 +169,7 @@ class _LayerWiseModel:
         torch.cuda.current_stream(self.down_device).wait_event(ev)
         return dst
 
-    def downstream(self, ids_shape, target, layer_of_interest, payload=None, hidden=None):
+    def downstream(self, ids_shape, target, layer_of_interest, payload=None, hidden=None, per_sequence=False):
         """Layers layer_of_interest+1.. + final norm + loss on the downstream device, starting
         either from a payload (dequantise fused into the first norm) or from raw hidden states."""
         model = self._down
@@ -185,7 +192,7 @@ class _LayerWiseModel:
                 eps = fn.eps if kind == N.NORM_LAYERNORM else fn.variance_epsilon
                 _, post_norm, _ = boundary.dequant_norm(payload, S, D, kind, fn.weight, getattr(fn, "bias", None),
                                                         eps, want_resid=False)
-                return self.last_portion(post_norm, target, model)
+                return self.last_portion(post_norm, target, model, per_sequence)
         elif payload is not None:
             hidden = boundary.dequant(payload, S, D)
         else:
@@ -195,7 +202,7 @@ class _LayerWiseModel:
             for i in range(nxt, self.num_layers):
                 hidden = compat.layer_output(layers[i](hidden, position_embeddings=pos))
         post_norm = self._final_norm(model)(hidden)
-        return self.last_portion(post_norm, target, model)
+        return self.last_portion(post_norm, target, model, per_sequence)
 
     # ---- reference API ------------------------------------------------------------------------
     def activation_quantization(self, batched_input_tokens, target, importance_values, ratio, layer_of_interest):

@@ -449,3 +449,36 @@ def shifted_nll(logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
 def perplexity(total_nll: float, n_tokens: int) -> float:
     """last_row_exp.py:138."""
     return math.exp(total_nll / n_tokens)
+
+
+# --------------------------------------------------------------------------------------
+# whole-window reference sweep on the CPU (timed baseline for the eval driver)
+# --------------------------------------------------------------------------------------
+def reference_window_sweep_cpu(model, eager_model, ids, target, methods, layers_of_interest, ratios):
+    """What one iteration of the reference loop does for one window (last_row_exp.py:92-111):
+    an eager forward for the attention maps, get_importance_order per method, then a FULL
+    layer-by-layer forward with the in-place int4 block for every (method, layer, ratio)
+    (pythia_model.py:153-206 / qwen_layer_wise.py:42-76).  HF modules on the CPU; returns the
+    (M, L, R) NLL tensor."""
+    base = model.base_model
+    embed = getattr(base, "embed_in", None) or base.embed_tokens
+    final_norm = getattr(base, "final_layer_norm", None) or base.norm
+    head = getattr(model, "embed_out", None) or model.lm_head
+    num_layers = len(base.layers)
+    out = torch.zeros(len(methods), len(layers_of_interest), len(ratios))
+    with torch.no_grad():
+        att = eager_model(input_ids=ids, output_attentions=True).attentions
+        imps = {m: get_importance_order(m, att, num_layers) for m in methods}
+        for mi, m in enumerate(methods):
+            for li, loi in enumerate(layers_of_interest):
+                for ri, ratio in enumerate(ratios):
+                    h = embed(ids)
+                    pos_ids = torch.arange(ids.size(1)).unsqueeze(0)
+                    pos = base.rotary_emb(h, pos_ids)
+                    for i in range(num_layers):
+                        o = base.layers[i](h, position_embeddings=pos)
+                        h = o[0] if isinstance(o, (tuple, list)) else o
+                        if i == loi and ratio > 0:
+                            h = fake_quant_reference(h, imps[m][loi], ratio)
+                    out[mi, li, ri] = shifted_nll(head(final_norm(h)), target)
+    return out

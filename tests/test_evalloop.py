@@ -130,3 +130,19 @@ def _pair_worker(rank, world, port, out):
 def test_pair_exchange_over_gloo(tmp_path, world):
     """rank r swaps payloads with r^1; an unpaired last rank keeps its own (local copy)."""
     mp.spawn(_pair_worker, args=(world, 29620 + world, str(tmp_path)), nprocs=world, join=True)
+
+
+@pytest.mark.gpu
+def test_batching_methods_through_downstream_changes_nothing():
+    from splitq import compat
+    from splitq.models import QwenPointFiveBModel
+    cfg = dict(compat.QWEN2_TINY, hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=256)
+    w = QwenPointFiveBModel.from_config("cuda:0", cfg=cfg, seed=0)
+    params = {"ratios": [0, 0.5, 1], "layers_of_interest": [0, 2], "methods": ["regular_importance", "last_row", "aggregate_till"],
+              "stride": 32}
+    ids = torch.randint(0, 512, (1, 200), generator=torch.Generator().manual_seed(5))
+    fn = evalloop.make_importance_fn(w, params["methods"], "fused")
+    a = evalloop.evaluate(params, w, ids, fn, 128, log=lambda *x: None)
+    b = evalloop.evaluate(params, w, ids, fn, 128, log=lambda *x: None, batch_methods=True)
+    assert a.n_tokens == b.n_tokens
+    assert torch.allclose(torch.tensor(a.total_nll), torch.tensor(b.total_nll), rtol=1e-5)
