@@ -322,7 +322,17 @@ def main() -> None:
             peaks = json.load(open(path))
         tokens_per_step = world * B * S
         value = tokens_per_step * args.steps / (elapsed_ms * 1e-3)
-        if fused:
+        if fused and cfg["method"] == "last_row":
+            # last-row importance from Q,K is one GEMV per head: HBM-bound, no tensor-core work
+            peak, peak_src = load_peaks()
+            alg_bytes = 4 * B * (KVH * S * 64 + H * 64 + S)
+            achieved = alg_bytes / (score_ms * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "kernel": "last_row_logits_kernel + last_row_softmax_kernel", "achieved": achieved,
+                        "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                        "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": score_ms,
+                        "note": "tiny, latency-bound reduction; the step is dominated by quantise/pack + dequantise"}
+            l2_note = f"inputs per step ({4 * B * S * (64 * (H + KVH) + D) / 1e6:.0f} MB) exceed the 126 MB L2; no flush"
+        elif fused:
             nb = (S + 127) // 128
             tiles = B * H * nb * (nb + 1)  # causal tiles, two passes
             products = 3 if args.fused_mode == "tf32x3" else 1
@@ -366,7 +376,7 @@ def main() -> None:
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
                     "api": "splitq.HostPipeline.submit/drain (pinned host buffers, 3 streams, depth 2)"},
-            "gpu_launches": plan.launches_per_run(fused) * args.steps,
+            "gpu_launches": (plan.launches_per_run(fused) - (3 if fused and cfg["method"] == "last_row" else 0)) * args.steps,
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -637,6 +637,65 @@ fused_finalize_kernel(const float* __restrict__ part_col, const float* __restric
     if (out_last) out_last[(size_t)b * S + j] = l;
 }
 
+// ---- last-row importance only: a single-query GEMV per head, no S x S work at all ---------------
+// logit2[b][h][j] = (q[b,h,S-1,:] . k[b,kvh,j,:]) * scaling * log2(e), exact fp32 FMAs on CUDA cores
+__global__ void __launch_bounds__(256)
+last_row_logits_kernel(const float* __restrict__ Q, long long qsb, long long qsh, long long qss,
+                       const float* __restrict__ K, long long ksb, long long ksh, long long kss, int H, int KVH,
+                       int S, float cs, float* __restrict__ logit2) {
+    __shared__ float qs[kHd];
+    const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
+    const float* q = Q + b * qsb + h * qsh + (long long)(S - 1) * qss;
+    if (threadIdx.x < kHd) qs[threadIdx.x] = q[threadIdx.x];
+    __syncthreads();
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= S) return;
+    const float* kr = K + b * ksb + (h / (H / KVH)) * ksh + (long long)j * kss;
+    float acc = 0.f;
+#pragma unroll
+    for (int d = 0; d < kHd; ++d) acc = fmaf(qs[d], __ldg(kr + d), acc);
+    logit2[(size_t)bh * S + j] = acc * cs;
+}
+// out_last[b][j] = sum_h w_h * softmax_j(logits of head h); one CTA per window
+__global__ void __launch_bounds__(1024)
+last_row_softmax_kernel(const float* __restrict__ logit2, int H, int S, HeadW hw, float* __restrict__ out_last) {
+    __shared__ float red[32];
+    __shared__ float s_m, s_l;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int j = tid; j < S; j += blockDim.x) out_last[(size_t)b * S + j] = 0.f;
+    for (int h = 0; h < H; ++h) {
+        const float* x = logit2 + ((size_t)b * H + h) * S;
+        float m = -INFINITY;
+        for (int j = tid; j < S; j += blockDim.x) m = fmaxf(m, x[j]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) red[warp] = m;
+        __syncthreads();
+        if (warp == 0) {
+            float v = lane < (blockDim.x >> 5) ? red[lane] : -INFINITY;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+            if (lane == 0) s_m = v;
+        }
+        __syncthreads();
+        m = s_m;
+        float l = 0.f;
+        for (int j = tid; j < S; j += blockDim.x) l += exp2f(x[j] - m);
+        l = warp_sum(l);
+        if (lane == 0) red[warp] = l;
+        __syncthreads();
+        if (warp == 0) {
+            float v = lane < (blockDim.x >> 5) ? red[lane] : 0.f;
+            v = warp_sum(v);
+            if (lane == 0) s_l = v;
+        }
+        __syncthreads();
+        const float scale = hw.w[h] / s_l;
+        for (int j = tid; j < S; j += blockDim.x) out_last[(size_t)b * S + j] += scale * exp2f(x[j] - m);
+        __syncthreads();
+    }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -717,6 +776,19 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     if (int rc = check_arch()) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t* w8 = (uint8_t*)ws;
+    if (!out_col && causal) {
+        // "last_row" alone needs one query row per head: GEMV + softmax, exact fp32, no tensor cores
+        HeadW hw1;
+        for (int h = 0; h < H; ++h) hw1.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
+        float* logit2 = (float*)(w8 + wl.lse);
+        SPLITQ_REQUIRE((long long)B * H <= 65535, SPLITQ_ERR_ARG, "importance_fused: B*H=%lld > 65535", (long long)B * H);
+        last_row_logits_kernel<<<dim3(cdiv(S, 256), B * H), 256, 0, st>>>(
+            Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], K, k_strides_host[0], k_strides_host[1],
+            k_strides_host[2], H, KVH, S, scaling * 1.4426950408889634f, logit2);
+        last_row_softmax_kernel<<<B, 1024, 0, st>>>(logit2, H, S, hw1, out_last);
+        SPLITQ_LAUNCH_CHECK("last_row kernels");
+        return SPLITQ_OK;
+    }
     float *qhi = (float*)(w8 + wl.qhi), *qlo = (float*)(w8 + wl.qlo), *khi = (float*)(w8 + wl.khi),
           *klo = (float*)(w8 + wl.klo);
 

@@ -86,3 +86,16 @@ def test_fused_rejects_other_head_dims():
     q = torch.zeros(1, 1, 8, 32, device=DEV)
     with pytest.raises(N.SplitqError):
         splitq.importance_fused(q, q, 0.1)
+
+
+@pytest.mark.parametrize("B,H,KVH,S", [(1, 8, 8, 2048), (2, 14, 2, 333), (1, 2, 1, 1)])
+def test_last_row_only_uses_the_gemv_path_and_matches(B, H, KVH, S):
+    """want_col=False: one query row per head (north star: "single-query GEMV against K")."""
+    gen = torch.Generator().manual_seed(S)
+    q, k = make_qk(gen, B, H, KVH, S, 1.0, hf_layout=True)
+    col, last = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_col=False, want_last=True)
+    assert col is None
+    _, want_last = oracle_scores(q, k, True)
+    assert max_rel(last.cpu(), want_last) <= 1e-5
+    both_col, both_last = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_col=True, want_last=True)
+    assert max_rel(both_last.cpu(), want_last) <= 1e-5

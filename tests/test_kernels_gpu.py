@@ -337,3 +337,35 @@ def test_codes_bit_exact_near_rounding_boundaries():
             got = splitq.quant_pack(h.to(DEV), bits, off, mode, nbytes)[0].cpu().numpy()
             want = O.pack_payload(h[0], O.ladder_bits(imp[0], ladder), mode)
             assert np.array_equal(got, want), (bits_w, mode)
+
+
+def test_pipelined_front_ends_give_the_same_bytes_as_the_plain_plan():
+    """OverlappedBoundary (side-stream hop + dequantise) and HostPipeline (H2D / kernels / D2H on
+    three streams) are schedules, not arithmetic: outputs must equal BoundaryPlan.run bit for bit."""
+    B, H, KVH, S, D = 2, 4, 2, 256, 128
+    gen = torch.Generator(device=DEV).manual_seed(21)
+    ladder = splitq.ladder_from_fractions([(0.25, 2), (0.25, 4), (0.25, 8)], S)
+    mk = lambda: splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=O.SCALE_TOKEN, KVH=KVH)  # noqa: E731
+    steps = [(torch.randn(B, H, S, 64, device=DEV, generator=gen), torch.randn(B, KVH, S, 64, device=DEV, generator=gen),
+              torch.randn(B, S, D, device=DEV, generator=gen)) for _ in range(5)]
+    ref_plan = mk()
+    want = []
+    for q, k, h in steps:
+        r = ref_plan.run_fused(q, k, h)
+        want.append((r.payload.clone(), r.hidden.clone()))
+    ob = splitq.OverlappedBoundary(mk, depth=2, fused=True)
+    got = []
+    for q, k, h in steps:
+        p = ob.step(q, k, h)
+        ob.side.synchronize()
+        got.append((p.payload_dst.clone(), p.h_out.clone()))
+    ob.drain()
+    for (wp, wh), (gp, gh) in zip(want, got):
+        assert torch.equal(wp, gp) and torch.equal(wh, gh)
+    pipe = splitq.HostPipeline(mk, depth=2, fused=True)
+    outs = [torch.empty(B, S, D, pin_memory=True) for _ in steps]
+    for (q, k, h), o in zip(steps, outs):
+        pipe.submit([t.cpu().pin_memory() for t in (q, k, h)], o)
+    pipe.drain()
+    for (wp, wh), o in zip(want, outs):
+        assert torch.equal(wh.cpu(), o)
