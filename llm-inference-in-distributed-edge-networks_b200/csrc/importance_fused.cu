@@ -31,13 +31,13 @@ constexpr int kHd = 64;
 constexpr uint32_t kSlabBytes = 128 * 128;           // 128 rows x 32 fp32: one swizzle-128B slab
 constexpr uint32_t kPartBytes = 2 * kSlabBytes;      // 128 x 64 fp32 (hi or lo part)
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // hi + lo
-constexpr int kRing = 13;                            // ring of streamed 16 KB slabs (3.25 tiles in flight)
+constexpr int kStages = 3;                           // streamed tiles in flight; one barrier pair and two TMA issues per tile
 constexpr int kAcc = 2;                              // TMEM accumulator buffers
 constexpr int kThreads = 512;                         // 4 warpgroups: control, epilogue x2, operand loaders
 constexpr uint32_t kTmemCols = 512;                   // 2 accumulators (128 each) + 2 fixed-operand buffers (hi 64 + lo 64 each)
 constexpr uint32_t kTmemA = 256;                      // first column of the fixed-operand buffers
-constexpr uint32_t kBarOff = kRing * kSlabBytes;
-constexpr uint32_t kLseOff = kBarOff + 512;            // 36 mbarriers (288 B) + TMEM base slot
+constexpr uint32_t kBarOff = kStages * kOperandBytes;
+constexpr uint32_t kLseOff = kBarOff + 512;            // 14 mbarriers + TMEM base slot
 constexpr uint32_t kXchOff = kLseOff + 2 * kAcc * kTile * 4;  // lse: 2 groups x 2 buffers x 128 floats
 constexpr uint32_t kSmemBytes = kXchOff + kTile * 8;  // dynamic smem base must be 1024-aligned (checked)
 
@@ -75,6 +75,15 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+// 5-D box {32 fp32, 128 rows, 2 k-chunks, 1, parts}: a whole streamed tile (both 32-wide k chunks, hi and
+// lo parts) in ONE transaction, landing as [part][k chunk][128 rows][128 B] = four swizzle-128B slabs
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3,
+                                            int c4) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+        ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
         : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -314,8 +323,7 @@ __device__ __forceinline__ void pass2_half(const float (&v)[64], const float* ls
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid_constant__ CUtensorMap mapQlo,
-                        const __grid_constant__ CUtensorMap mapKhi, const __grid_constant__ CUtensorMap mapKlo,
+fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
                         const Params p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -324,8 +332,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
     const uint32_t ring_s = base;
     const uint32_t bar0 = base + kBarOff;
     const uint32_t bar_afull = bar0, bar_aempty = bar0 + 16;          // fixed operand in TMEM, 2 buffers
-    const uint32_t bar_full = bar0 + 32, bar_empty = bar_full + 8 * kRing;
-    const uint32_t bar_tfull = bar_empty + 8 * kRing, bar_tempty = bar_tfull + 8 * kAcc;
+    const uint32_t bar_full = bar0 + 32, bar_empty = bar_full + 8 * kStages;
+    const uint32_t bar_tfull = bar_empty + 8 * kStages, bar_tempty = bar_tfull + 8 * kAcc;
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 504);
     float* lse_s = reinterpret_cast<float*>(gen + kLseOff);
 
@@ -336,7 +344,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
             mbar_init(bar_afull + 8 * a, 4);   // one arrive per loader warp
             mbar_init(bar_aempty + 8 * a, 1);  // tcgen05.commit of the item's last MMA
         }
-        for (int s = 0; s < kRing; ++s) {
+        for (int s = 0; s < kStages; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
         }
@@ -357,41 +365,41 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const CUtensorMap* str_hi = p.pass == 1 ? &mapKhi : &mapQhi;
-    const CUtensorMap* str_lo = p.pass == 1 ? &mapKlo : &mapQlo;
+    const CUtensorMap* str_map = p.pass == 1 ? &mapK : &mapQ;  // streamed operand, hi and lo parts in dim 3
     const int group = p.H / p.KVH;
     const int wg = warp >> 2;  // warpgroup: 0 control, 1-2 epilogue, 3 fixed-operand loaders
 
     if (wg == 0) {
         reg_dec<56>();
         if (warp == 0) {
-            // ===== TMA producer: streamed operand as a ring of 16 KB slabs =====
+            // ===== TMA producer: one stage = one streamed 128-row tile (hi + lo parts); per tile ONE
+            // barrier wait, one expect_tx and ONE 5-D TMA issue.  The per-transaction round trip
+            // (try_wait + expect_tx + issue, ~300 cycles) was the limiter of a finer 16 KB-slab ring,
+            // not bytes =====
             {
-                uint32_t ring = 0, rphase = 0;
-                const int nslab = p.x3 ? 4 : 2;  // hi k0, hi k1, lo k0, lo k1
+                uint32_t stage = 0, sphase = 0;
+                const uint32_t tile_tx = p.x3 ? kOperandBytes : kPartBytes;
                 Item it;
                 for (int k = 0; item_at(p, k, it); ++k) {
                     const int b = it.bh / p.H, h = it.bh % p.H;
                     const int str_idx = p.pass == 1 ? b * p.KVH + h / group : it.bh;
                     for (int t = it.t0; t < it.t1; ++t) {
-                        for (int sl = 0; sl < nslab; ++sl) {
-                            const uint32_t fb = bar_full + 8 * ring;
-                            mbar_wait(bar_empty + 8 * ring, rphase ^ 1);
-                            if (elect_one()) {
-                                mbar_expect_tx(fb, kSlabBytes);
-                                tma_load_3d(ring_s + ring * kSlabBytes, sl < 2 ? str_hi : str_lo, fb, (sl & 1) * 32, t * kTile, str_idx);
-                            }
-                            __syncwarp();
-                            if (++ring == kRing) { ring = 0; rphase ^= 1; }
+                        const uint32_t fb = bar_full + 8 * stage;
+                        const uint32_t dst = ring_s + stage * kOperandBytes;
+                        mbar_wait(bar_empty + 8 * stage, sphase ^ 1);
+                        if (elect_one()) {
+                            mbar_expect_tx(fb, tile_tx);
+                            tma_load_5d(dst, str_map, fb, 0, t * kTile, 0, str_idx, 0);
                         }
+                        __syncwarp();
+                        if (++stage == kStages) { stage = 0; sphase ^= 1; }
                     }
                 }
             }
         } else if (warp == 1) {
             // ===== MMA issuer: A (fixed operand) from TMEM, B (streamed slab) from shared memory =====
             {
-                uint32_t ring = 0, rphase = 0, acc = 0, aphase = 0;
-                const int nslab = p.x3 ? 4 : 2;
+                uint32_t stage = 0, sphase = 0, acc = 0, aphase = 0;
                 Item it;
                 for (int k = 0; item_at(p, k, it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
@@ -400,34 +408,35 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQhi, const __grid
                     tc_fence_after();
                     for (int t = it.t0; t < it.t1; ++t) {
                         mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
+                        mbar_wait(bar_full + 8 * stage, sphase);
+                        tc_fence_after();
                         const uint32_t d = tmem_base + acc * kTile;
-                        uint32_t first = 0;
-                        for (int sl = 0; sl < nslab; ++sl) {
-                            mbar_wait(bar_full + 8 * ring, rphase);
-                            tc_fence_after();
-                            const uint32_t sb = ring_s + ring * kSlabBytes;
-                            const uint32_t kc = (sl & 1) * 32u;  // first of the 32 k-columns this slab covers
-                            // a streamed hi slab meets fixed hi (and fixed lo in 3xTF32); a streamed lo slab meets fixed hi
-                            if (elect_one()) {
-                                if (!(p.dbg & 2)) {
+                        const uint32_t st0 = ring_s + stage * kOperandBytes;
+                        if (elect_one()) {
+                            if (!(p.dbg & 2)) {
 #pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk) {
-                                        tc_mma_tf32_ts(d, a_hi + kc + kk * 8u, umma_desc(sb + kk * 32u), kIdesc, first | (uint32_t)kk);
-                                    }
-                                    if (p.x3 && sl < 2) {
+                                for (int kc = 0; kc < 2; ++kc) {
+                                    const uint32_t s_hi = st0 + kc * kSlabBytes, s_lo = s_hi + kPartBytes;  // [part][k chunk] slabs
+                                    const uint32_t ac = kc * 32u;  // first of the 32 k-columns of this chunk in the A operand
+                                    // streamed hi meets fixed hi (and fixed lo in 3xTF32); streamed lo meets fixed hi
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk)
+                                        tc_mma_tf32_ts(d, a_hi + ac + kk * 8u, umma_desc(s_hi + kk * 32u), kIdesc, (uint32_t)(kc | kk));
+                                    if (p.x3) {
 #pragma unroll
                                         for (int kk = 0; kk < 4; ++kk)
-                                            tc_mma_tf32_ts(d, a_lo + kc + kk * 8u, umma_desc(sb + kk * 32u), kIdesc, 1u);
+                                            tc_mma_tf32_ts(d, a_lo + ac + kk * 8u, umma_desc(s_hi + kk * 32u), kIdesc, 1u);
+#pragma unroll
+                                        for (int kk = 0; kk < 4; ++kk)
+                                            tc_mma_tf32_ts(d, a_hi + ac + kk * 8u, umma_desc(s_lo + kk * 32u), kIdesc, 1u);
                                     }
                                 }
-                                tc_commit(bar_empty + 8 * ring);    // slab reusable once these MMAs retire
                             }
-                            __syncwarp();
-                            first = 1;
-                            if (++ring == kRing) { ring = 0; rphase ^= 1; }
+                            tc_commit(bar_empty + 8 * stage);   // stage reusable once these MMAs retire
+                            tc_commit(bar_tfull + 8 * acc);     // accumulator ready for the epilogue
                         }
-                        if (elect_one()) tc_commit(bar_tfull + 8 * acc);  // accumulator ready for the epilogue
                         __syncwarp();
+                        if (++stage == kStages) { stage = 0; sphase ^= 1; }
                         if (++acc == kAcc) { acc = 0; aphase ^= 1; }
                     }
                     if (elect_one()) tc_commit(bar_aempty + 8 * ab);      // fixed-operand buffer reusable
@@ -712,15 +721,17 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// (64, S, n) fp32 tensor, box = 32 x 128 x 1, 128-byte swizzle, rows past S read as zero
-static int make_map(CUtensorMap* map, float* base, int S, long long n) {
+// the (n, S, 64) hi array and the lo array behind it, viewed as a 5-D fp32 tensor
+// (32 in-chunk, S rows, 2 k-chunks, n, 2 parts); box = 32 x 128 x 2 x 1 x parts, 128-byte swizzle, rows past S
+// read as zero
+static int make_map(CUtensorMap* map, float* base, int S, long long n, size_t part_stride_bytes, int parts) {
     EncodeTiledFn enc = encode_fn();
     SPLITQ_REQUIRE(enc != nullptr, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled is unavailable");
-    cuuint64_t dims[3] = {(cuuint64_t)kHd, (cuuint64_t)S, (cuuint64_t)n};
-    cuuint64_t strides[2] = {(cuuint64_t)kHd * 4, (cuuint64_t)S * kHd * 4};
-    cuuint32_t box[3] = {32, (cuuint32_t)kTile, 1};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr,
+    cuuint64_t dims[5] = {32, (cuuint64_t)S, 2, (cuuint64_t)n, 2};
+    cuuint64_t strides[4] = {(cuuint64_t)kHd * 4, 128, (cuuint64_t)S * kHd * 4, (cuuint64_t)part_stride_bytes};
+    cuuint32_t box[5] = {32, (cuuint32_t)kTile, 2, 1, (cuuint32_t)parts};
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 5, base, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     SPLITQ_REQUIRE(r == CUDA_SUCCESS, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -805,11 +816,10 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
         SPLITQ_LAUNCH_CHECK("split_tf32_kernel");
     }
 
-    CUtensorMap mqh, mql, mkh, mkl;
-    if (int rc = make_map(&mqh, qhi, S, (long long)B * H)) return rc;
-    if (int rc = make_map(&mql, qlo, S, (long long)B * H)) return rc;
-    if (int rc = make_map(&mkh, khi, S, (long long)B * KVH)) return rc;
-    if (int rc = make_map(&mkl, klo, S, (long long)B * KVH)) return rc;
+    const int parts = mode == SPLITQ_FUSED_TF32X3 ? 2 : 1;
+    CUtensorMap mq, mk;
+    if (int rc = make_map(&mq, qhi, S, (long long)B * H, wl.qlo - wl.qhi, parts)) return rc;
+    if (int rc = make_map(&mk, khi, S, (long long)B * KVH, wl.klo - wl.khi, parts)) return rc;
 
     Params p;
     p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = cdiv(S, kTile);
@@ -834,7 +844,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     const int grid = (int)std::min<long long>(items, sms);
     for (int pass = 1; pass <= 2; ++pass) {
         p.pass = pass;
-        fused_importance_kernel<<<grid, kThreads, kSmemBytes, st>>>(mqh, mql, mkh, mkl, p);
+        fused_importance_kernel<<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
         SPLITQ_LAUNCH_CHECK("fused_importance_kernel");
     }
     HeadW hw;
