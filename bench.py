@@ -335,19 +335,25 @@ def main() -> None:
         elif fused:
             nb = (S + 127) // 128
             tiles = B * H * nb * (nb + 1)  # causal tiles, two passes
-            products = 3 if args.fused_mode == "tf32x3" else 1
-            issued = tiles * 2.0 * 128 * 128 * 64 * products
-            dense_equiv = 4.0 * B * H * S * S * 64
+            tile_flops = 2.0 * 128 * 128 * 64
             bf16 = peaks.get("bf16_tflops", 1590.0)
+            x3 = args.fused_mode == "tf32x3"
+            tf32_flops = tiles * tile_flops                       # hi*hi on kind::tf32 (half the bf16 rate)
+            f16_flops = tiles * tile_flops * 2 if x3 else 0.0     # lo*x and x*lo on kind::f16 (bf16 rate)
+            issued = tf32_flops + f16_flops
+            # speed of light of this instruction mix = flops / (time on the pipe at the measured cuBLAS rates)
+            peak_mix = issued / (tf32_flops / (bf16 / 2) + f16_flops / bf16)
+            dense_equiv = 4.0 * B * H * S * S * 64
             achieved = issued / (score_ms * 1e-3) / 1e12
+            mufu_ms = tiles * 128 * 128 / (16.0 * 148 * 1.965e9) * 1e3   # 16 ex2/clk/SM at the max SM clock
             roofline = {
-                "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + tf32 split + finalize",
-                "achieved": achieved, "peak": bf16 / 2, "unit": "TFLOP/s", "frac": achieved / (bf16 / 2), "traffic": None,
-                "peak_source": ("MEASURED_PEAKS.json bf16_tflops / 2" if peaks else "fallback 1590 / 2") +
-                               " (kind::tf32 issues at half the bf16 rate)",
-                "flops_counted": "issued tcgen05 tf32 MMA flops: causal tiles x 2 passes x products",
+                "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + operand split + finalize",
+                "achieved": achieved, "peak": peak_mix, "unit": "TFLOP/s", "frac": achieved / peak_mix, "traffic": None,
+                "peak_source": ("MEASURED_PEAKS.json bf16_tflops" if peaks else "fallback 1590") +
+                               ": kind::tf32 flops at half of it, kind::f16 flops at it, harmonic mix",
+                "flops_counted": "issued tcgen05 MMA flops: causal tiles x 2 passes x (1 tf32 + 2 fp16 products)",
                 "issued_flops_per_launch": issued, "dense_equivalent_tflops": dense_equiv / (score_ms * 1e-3) / 1e12,
-                "kernel_ms": score_ms,
+                "kernel_ms": score_ms, "co_bound_mufu_frac": mufu_ms / score_ms,
                 "attention_matrix_bytes_avoided": 4 * B * H * S * S}
             l2_note = f"inputs per step ({4 * B * S * (64 * (H + KVH) + D) / 1e6:.0f} MB) exceed the 126 MB L2; no flush"
         else:

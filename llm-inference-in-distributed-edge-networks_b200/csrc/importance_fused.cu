@@ -11,12 +11,16 @@
 //           summed over queries per key (one TMEM lane = one key: no cross-thread reduction)
 // QK^T runs on tcgen05 (kind::tf32, accumulators in TMEM, operands staged by TMA with 128-byte
 // swizzle).  The reference computes QK^T in true fp32; a single TF32 product misses the 1e-5
-// importance tolerance for trained-scale logits, so operands are pre-split into tf32 hi + lo
-// parts and each tile accumulates lo*hi + hi*lo + hi*hi (3xTF32); SPLITQ_FUSED_TF32X1 keeps only
-// hi*hi.  Four warpgroups per CTA: control (warp 0 = TMA producer of the streamed operand, warp 1 = MMA
+// importance tolerance for trained-scale logits, so every operand x is pre-split into hi = tf32(x)
+// and lo = x - hi, and each tile accumulates hi*hi (kind::tf32) plus the two correction terms
+// lo*x and x*lo, which only need ~12 bits of each factor and therefore run as kind::f16 on
+// fp16(x) / fp16(lo) at twice the tf32 rate ("3xTF32" accuracy for 2/3 of the tensor time; valid
+// for |x| < 65504, beyond which fp16 overflows and the scores come out NaN).  SPLITQ_FUSED_TF32X1
+// keeps only hi*hi.  Four warpgroups per CTA: control (warp 0 = TMA producer of the streamed operand, warp 1 = MMA
 // issuer), two epilogue groups (one per TMEM accumulator), and loaders that put the fixed operand of
 // the next work item into tensor memory, so the MMA reads A from TMEM and only B from shared memory.
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <math.h>
 
 #include <algorithm>
@@ -108,6 +112,15 @@ __device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem,
         ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
         : "memory");
 }
+// same with fp16 operands (K = 16 per instruction; A packs two halfs per TMEM column)
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
 // 32 consecutive columns of this thread's TMEM lane <- registers
 __device__ __forceinline__ void tc_st32(uint32_t taddr, const float4 (&q)[8]) {
     asm volatile(
@@ -165,11 +178,15 @@ __device__ __forceinline__ void tc_ld64(uint32_t taddr, float (&v)[64]) {
 #pragma unroll
     for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(r[i]);
 }
+#ifdef SPLITQ_K2_NO_MUFU  // timing experiment only: how much of the epilogue is the MUFU pipe?
+__device__ __forceinline__ float ex2(float x) { return x * 0.5f; }
+#else
 __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+#endif
 
 // K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {32 fp32, 128 rows} TMA box writes)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
@@ -177,6 +194,8 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
 }
 // kind::tf32, fp32 accumulate, A and B K-major, M = N = 128
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+// kind::f16 with fp16 A and B (format 0), fp32 accumulate, K-major, M = N = 128
+constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
 
 struct Params {
     int pass;          // 1 = row LSE, 2 = column sums
@@ -414,22 +433,26 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         const uint32_t st0 = ring_s + stage * kOperandBytes;
                         if (elect_one()) {
                             if (!(p.dbg & 2)) {
+                                // main term: tf32(F) * tf32(S), K = 8 per instruction
 #pragma unroll
                                 for (int kc = 0; kc < 2; ++kc) {
-                                    const uint32_t s_hi = st0 + kc * kSlabBytes, s_lo = s_hi + kPartBytes;  // [part][k chunk] slabs
-                                    const uint32_t ac = kc * 32u;  // first of the 32 k-columns of this chunk in the A operand
-                                    // streamed hi meets fixed hi (and fixed lo in 3xTF32); streamed lo meets fixed hi
 #pragma unroll
                                     for (int kk = 0; kk < 4; ++kk)
-                                        tc_mma_tf32_ts(d, a_hi + ac + kk * 8u, umma_desc(s_hi + kk * 32u), kIdesc, (uint32_t)(kc | kk));
-                                    if (p.x3) {
+                                        tc_mma_tf32_ts(d, a_hi + kc * 32u + kk * 8u, umma_desc(st0 + kc * kSlabBytes + kk * 32u), kIdesc,
+                                                       (uint32_t)(kc | kk));
+                                }
+                                if (p.x3) {
+                                    // the two correction terms need ~12 bits of each factor: fp16 operands, K = 16 per
+                                    // instruction -> half the tensor time of a tf32 product.
+                                    // (F - tf32(F)) * S: A = packed fp16 lo part (TMEM cols a_lo+32..), B = fp16(S) slab
+                                    // F * (S - tf32(S)): A = packed fp16(F)      (TMEM cols a_lo+0..),  B = fp16 lo slab
+                                    const uint32_t s_h16 = st0 + kPartBytes, s_l16 = s_h16 + kSlabBytes;
 #pragma unroll
-                                        for (int kk = 0; kk < 4; ++kk)
-                                            tc_mma_tf32_ts(d, a_lo + ac + kk * 8u, umma_desc(s_hi + kk * 32u), kIdesc, 1u);
+                                    for (int kk = 0; kk < 4; ++kk)
+                                        tc_mma_f16_ts(d, a_lo + 32u + kk * 8u, umma_desc(s_h16 + kk * 32u), kIdescF16, 1u);
 #pragma unroll
-                                        for (int kk = 0; kk < 4; ++kk)
-                                            tc_mma_tf32_ts(d, a_hi + ac + kk * 8u, umma_desc(s_lo + kk * 32u), kIdesc, 1u);
-                                    }
+                                    for (int kk = 0; kk < 4; ++kk)
+                                        tc_mma_f16_ts(d, a_lo + kk * 8u, umma_desc(s_l16 + kk * 32u), kIdescF16, 1u);
                                 }
                             }
                             tc_commit(bar_empty + 8 * stage);   // stage reusable once these MMAs retire
@@ -600,7 +623,6 @@ split_tf32_kernel(const float* __restrict__ x, long long sb, long long sh, long 
     const float* src0 = x + b * sb + h * sh;
     const int n4 = S * (kHd / 4);
     float4* hi4 = reinterpret_cast<float4*>(hi) + (size_t)bh * n4;
-    float4* lo4 = reinterpret_cast<float4*>(lo) + (size_t)bh * n4;
     constexpr int UN = 4;
     const int i0 = blockIdx.x * (256 * UN) + threadIdx.x;
     float4 v[UN];
@@ -617,12 +639,16 @@ split_tf32_kernel(const float* __restrict__ x, long long sb, long long sh, long 
     for (int u = 0; u < UN; ++u) {
         const int i = i0 + u * 256;
         if (i < n4) {
-            float4 a, r;
+            float4 a;
             a.x = tf32_rn(v[u].x); a.y = tf32_rn(v[u].y); a.z = tf32_rn(v[u].z); a.w = tf32_rn(v[u].w);
-            r.x = tf32_rn(v[u].x - a.x); r.y = tf32_rn(v[u].y - a.y);
-            r.z = tf32_rn(v[u].z - a.z); r.w = tf32_rn(v[u].w - a.w);
             hi4[i] = a;
-            lo4[i] = r;
+            // second array, per row of 64 words: words 0..31 = fp16(x) (64 halfs), words 32..63 = fp16(x - hi)
+            const __half2 h01 = __floats2half2_rn(v[u].x, v[u].y), h23 = __floats2half2_rn(v[u].z, v[u].w);
+            const __half2 l01 = __floats2half2_rn(v[u].x - a.x, v[u].y - a.y), l23 = __floats2half2_rn(v[u].z - a.z, v[u].w - a.w);
+            uint2* row = reinterpret_cast<uint2*>(lo) + ((size_t)bh * S + (i >> 4)) * 32;  // 64 words = 32 uint2
+            const int d4 = i & 15;                                                    // 4 elements -> 2 words
+            row[d4] = make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
+            row[16 + d4] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
         }
     }
 }
