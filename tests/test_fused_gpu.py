@@ -99,3 +99,15 @@ def test_last_row_only_uses_the_gemv_path_and_matches(B, H, KVH, S):
     assert max_rel(last.cpu(), want_last) <= 1e-5
     both_col, both_last = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_col=True, want_last=True)
     assert max_rel(both_last.cpu(), want_last) <= 1e-5
+
+
+def test_fused_out_of_fp16_range_fails_loudly_and_tf32x1_does_not():
+    """The correction terms run on fp16 operands: |q|,|k| >= 65504 overflow there.  The documented
+    behaviour is NaN scores (loud), while the single-tf32 mode has no such limit."""
+    gen = torch.Generator().manual_seed(1)
+    q, k = make_qk(gen, 1, 2, 2, 256, 1.0)
+    q[0, 0, 5, 3] = 1.0e5
+    col, _ = splitq.importance_fused(q.to(DEV), k.to(DEV), 1e-6)
+    assert torch.isnan(col).any()
+    col1, _ = splitq.importance_fused(q.to(DEV), k.to(DEV), 1e-6, mode=N.FUSED_TF32X1)
+    assert torch.isfinite(col1).all()
