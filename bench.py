@@ -184,6 +184,44 @@ def cpu_inputs(cfg, fused, seed=1234):
     return A, h
 
 
+EVAL_SWEEPS = {
+    "qwen": dict(family="qwen2", ratios=[0, 0.25, 0.5, 0.75, 1], layers_of_interest=[3, 11, 18, 22, 23],
+                 methods=["regular_importance", "last_row", "aggregate_till"], max_length=512, stride=32),
+    "pythia": dict(family="gpt_neox", ratios=[0, 0.25, 0.5, 0.75, 1], layers_of_interest=[1, 2, 4, 5],
+                   methods=["regular_importance", "last_row", "aggregate_till"], max_length=2048, stride=32),
+}
+
+
+def run_reference_eval(args):
+    """--impl reference --eval-family F: the reference's whole per-window sweep (eager forward for the
+    attention maps, get_importance_order, one full layer-by-layer forward per (method, layer, ratio))
+    as restated in oracle/, on the host CPU; the CPU leg of benchmarks/eval_throughput.py."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import splitq_oracle as O
+    from splitq import compat
+
+    sw = EVAL_SWEEPS[args.eval_family]
+    cfg = compat.QWEN2_05B if args.eval_family == "qwen" else compat.PYTHIA_70M
+    S, stride = sw["max_length"], sw["stride"]
+    model = compat.build_causal_lm(sw["family"], cfg, seed=0)
+    eager = compat.clone_with_attention(model, "eager")
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    ids = torch.randint(0, cfg["vocab_size"], (1, S + args.steps * stride), generator=torch.Generator().manual_seed(1234))
+    t0 = time.perf_counter()
+    for w in range(args.steps):
+        win = ids[:, w * stride:w * stride + S]
+        O.reference_window_sweep_cpu(model, eager, win, win.clone(), sw["methods"], sw["layers_of_interest"], sw["ratios"])
+    dt = time.perf_counter() - t0
+    combos = len(sw["methods"]) * len(sw["layers_of_interest"]) * len(sw["ratios"])
+    print(json.dumps({"impl": "reference", "metric": "eval window tokens/sec", "eval_family": args.eval_family,
+                      "cores": threads, "windows": args.steps, "S": S, "combos_per_window": combos, "seconds": dt,
+                      "window_tokens_per_s": args.steps * S / dt,
+                      "split_forward_tokens_per_s": args.steps * S * combos / dt}))
+
+
 def run_reference(args, cfg, name):
     """--impl reference: the reference's CPU implementation of the same path, all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -233,8 +271,13 @@ def main() -> None:
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--eval-family", default=None, choices=["qwen", "pythia"],
+                    help="with --impl reference: time the CPU port of the eval-loop sweep over --steps windows instead")
     args = ap.parse_args()
     cfg = WORKLOADS[args.workload]
+    if args.impl == "reference" and args.eval_family:
+        run_reference_eval(args)
+        return
     if args.impl == "reference":
         run_reference(args, cfg, args.workload)
         return

@@ -9,7 +9,8 @@ Per window the sweep is the notebook's: M methods x L split layers x R ratios (d
 75 split forwards, Qwen2-0.5B, S=512, stride 32; Pythia-70M uses S=2048 and 4 layers like its
 params.json).  Reported: window tokens/s (windows*S / time), split-forward token throughput
 (x M*L*R; comparable to the reference notebook's ~3.2 k token-forwards/s on a T4), and the same
-two figures for the CPU port on --cpu-windows windows (rank 0 only).
+two figures for the CPU port on --cpu-windows windows (rank 0 only; run through
+`bench.py --impl reference --eval-family ...`, the one place that executes oracle/).
 """
 from __future__ import annotations
 
@@ -20,7 +21,7 @@ import sys
 import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path[:0] = [os.path.join(ROOT, "llm-inference-in-distributed-edge-networks_b200"), os.path.join(ROOT, "oracle")]
+sys.path.insert(0, os.path.join(ROOT, "llm-inference-in-distributed-edge-networks_b200"))
 
 import torch  # noqa: E402
 
@@ -77,19 +78,14 @@ def main():
            "importance_impl": args.importance, "batch_methods": args.batch_methods, "seconds": dt, "window_tokens_per_s": res.windows * S / dt,
            "split_forward_tokens_per_s": res.windows * S * combos / dt, "ppl_no_quant": res.ppl[0][0][0]}
     if rank == 0 and not args.no_cpu:
-        import splitq_oracle as O
-        cpu = compat.build_causal_lm("qwen2" if args.family == "qwen" else "gpt_neox", cfg, seed=0)
-        eager = compat.clone_with_attention(cpu, "eager")
-        torch.set_num_threads(os.cpu_count() or 1)
-        t0 = time.perf_counter()
-        for w in range(args.cpu_windows):
-            win = ids[:, w * stride:w * stride + S]
-            O.reference_window_sweep_cpu(cpu, eager, win, win.clone(), params["methods"], params["layers_of_interest"],
-                                         params["ratios"])
-        cdt = time.perf_counter() - t0
-        out["cpu_port"] = {"cores": os.cpu_count(), "windows": args.cpu_windows, "seconds": cdt,
-                           "window_tokens_per_s": args.cpu_windows * S / cdt,
-                           "split_forward_tokens_per_s": args.cpu_windows * S * combos / cdt}
+        # the CPU port of the reference loop lives in oracle/ and is only ever executed by bench.py
+        import subprocess
+        line = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--eval-family",
+                               args.family, "--steps", str(args.cpu_windows)], capture_output=True, text=True,
+                              check=True).stdout.strip().splitlines()[-1]
+        cpu = json.loads(line)
+        out["cpu_port"] = {k: cpu[k] for k in ("cores", "windows", "seconds", "window_tokens_per_s",
+                                                "split_forward_tokens_per_s")}
     if rank == 0:
         print(json.dumps(out))
     if world > 1:
