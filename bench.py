@@ -266,7 +266,7 @@ def main() -> None:
     ap.add_argument("--importance", default="fused", choices=["fused", "materialised"],
                     help="fused: scores from the split layer's Q,K (K2, no attention matrix); "
                          "materialised: scores from attention probabilities already in HBM (K1)")
-    ap.add_argument("--fused-mode", default="tf32x3", choices=["tf32x3", "tf32x1"])
+    ap.add_argument("--fused-mode", default="f16x3", choices=["f16x3", "f16x1"])
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
@@ -305,7 +305,7 @@ def main() -> None:
     ladder = splitq.ladder_from_fractions(cfg["fracs"], S)
     plan = splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=cfg["scale_mode"], method=cfg["method"],
                                src_device=device, KVH=KVH,
-                               fused_mode=N.FUSED_TF32X3 if args.fused_mode == "tf32x3" else N.FUSED_TF32X1)
+                               fused_mode=N.FUSED_F16X3 if args.fused_mode == "f16x3" else N.FUSED_F16X1)
     plan.transport = PairExchange(rank, world) if world > 1 else None
     if fused:
         q, k = synth_qk(cfg, B, device, seed=1234 + rank)
@@ -400,24 +400,21 @@ def main() -> None:
             tiles = B * H * nb * (nb + 1)  # causal tiles, two passes
             tile_flops = 2.0 * 128 * 128 * 64
             bf16 = peaks.get("bf16_tflops", 1590.0)
-            x3 = args.fused_mode == "tf32x3"
-            tf32_flops = tiles * tile_flops                       # hi*hi on kind::tf32 (half the bf16 rate)
-            f16_flops = tiles * tile_flops * 2 if x3 else 0.0     # lo*x and x*lo on kind::f16 (bf16 rate)
-            issued = tf32_flops + f16_flops
-            # speed of light of this instruction mix = flops / (time on the pipe at the measured cuBLAS rates)
-            peak_mix = issued / (tf32_flops / (bf16 / 2) + f16_flops / bf16)
+            x3 = args.fused_mode == "f16x3"
+            issued = tiles * tile_flops * (3 if x3 else 1)        # h0*h0 (+ h1*h0 + h0*h1), all kind::f16
+            peak_mix = bf16                                       # kind::f16 runs at the measured cuBLAS bf16 rate
             dense_equiv = 4.0 * B * H * S * S * 64
             achieved = issued / (score_ms * 1e-3) / 1e12
             mufu_ms = tiles * 128 * 128 / (16.0 * 148 * 1.965e9) * 1e3   # 16 ex2/clk/SM at the max SM clock
             roofline = {
                 "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + operand split + finalize",
                 "achieved": achieved, "peak": peak_mix, "unit": "TFLOP/s", "frac": achieved / peak_mix,
-                "traffic": (captured_traffic("r1_g_ncu_full_k2_summary.csv", "fused_importance_kernel")
+                "traffic": (captured_traffic("r1_h_ncu_full_k2_summary.csv", "fused_importance_kernel")
                             if args.workload == DEFAULT_WORKLOAD and B == cfg["B_fused"] and x3 else None),
                 "traffic_note": "DRAM bytes of the two tensor-core passes (ncu); operands are re-read from L2, not HBM",
                 "peak_source": ("MEASURED_PEAKS.json bf16_tflops" if peaks else "fallback 1590") +
-                               ": kind::tf32 flops at half of it, kind::f16 flops at it, harmonic mix",
-                "flops_counted": "issued tcgen05 MMA flops: causal tiles x 2 passes x (1 tf32 + 2 fp16 products)",
+                               " (kind::f16 rate)",
+                "flops_counted": "issued tcgen05 MMA flops: causal tiles x 2 passes x 3 fp16 products (split operands)",
                 "issued_flops_per_launch": issued, "dense_equivalent_tflops": dense_equiv / (score_ms * 1e-3) / 1e12,
                 "kernel_ms": score_ms, "co_bound_mufu_frac": mufu_ms / score_ms,
                 "attention_matrix_bytes_avoided": 4 * B * H * S * S}

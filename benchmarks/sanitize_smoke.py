@@ -21,7 +21,7 @@ for (B, H, KVH, S, D) in [(1, 4, 2, 200, 896), (2, 2, 2, 77, 20), (1, 1, 1, 1, 5
     q = torch.randn(B, H, S, 64, device=dev, generator=g)
     k = torch.randn(B, KVH, S, 64, device=dev, generator=g)
     fc, fl = splitq.importance_fused(q, k, 0.125, want_last=True)
-    splitq.importance_fused(q, k, 0.125, causal=False, mode=N.FUSED_TF32X1)
+    splitq.importance_fused(q, k, 0.125, causal=False, mode=N.FUSED_F16X1)
     ladder = [(S // 4, 2), (S // 4, 4), (S // 4, 8)]
     for mode in (N.SCALE_GROUP, N.SCALE_TOKEN):
         nbytes = splitq.payload_bytes(S, D, ladder, mode)

@@ -2,7 +2,7 @@
 """BASELINE.json configs[4]: importance + quantise + pack microbench sweep.
 
   S in {512 .. 16384} x (D, H, KVH) in {(512, 8, 8) Pythia-70M, (896, 14, 2) Qwen2-0.5B},
-  importance from materialised attention (K1) vs fused Q/K recompute (K2, 3xTF32),
+  importance from materialised attention (K1) vs fused Q/K recompute (K2, three fp16 products),
   then select + quantise + pack (8/4/2-bit ladder, per-token scale).
 
 Batch B per point is chosen so the attention maps (materialised) or Q/K/h (fused) exceed the
@@ -83,8 +83,8 @@ def main():
             qp_bytes = Bf * (4 * S * D + 5 * S + nbytes)
             rec = {"model_shape": name, "S": S, "D": D, "H": H, "KVH": KVH,
                    "fused": {"B": Bf, "k2_ms": t_k2, "tokens_per_s": Bf * S / (t_k2 * 1e-3),
-                             "issued_tf32_tflops": issued / (t_k2 * 1e-3) / 1e12,
-                             "frac_of_tf32_peak": issued / (t_k2 * 1e-3) / 1e12 / (bf16 / 2)},
+                             "issued_f16_tflops": issued / (t_k2 * 1e-3) / 1e12,
+                             "frac_of_f16_peak": issued / (t_k2 * 1e-3) / 1e12 / bf16},
                    "select_ms": t_sel,
                    "quant_pack": {"ms": t_qp, "GBps": qp_bytes / (t_qp * 1e-3) / 1e9,
                                   "frac_of_hbm_peak": qp_bytes / (t_qp * 1e-3) / 1e9 / hbm}}
@@ -112,7 +112,7 @@ def main():
             results.append(rec)
             S *= 2
     with open(args.out, "w") as f:
-        json.dump({"peaks": {"hbm_gbs": hbm, "tf32_tflops": bf16 / 2}, "points": results}, f, indent=1)
+        json.dump({"peaks": {"hbm_gbs": hbm, "f16_tflops": bf16}, "points": results}, f, indent=1)
 
 
 if __name__ == "__main__":

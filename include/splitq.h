@@ -83,11 +83,13 @@ int splitq_importance_colmean(const float* A, int B, int H, int Sq, int Sk, cons
  *   Q (B,H,S,hd), K (B,KVH,S,hd): fp32, head_dim contiguous, element strides of (b, head, s) in
  *   q_strides_host[3] / k_strides_host[3] (so HF's transposed views need no copy); hd must be 64.
  *   scaling = head_dim^-0.5; causal != 0 applies the lower-triangular mask.
- *   mode: SPLITQ_FUSED_TF32X3 (tf32 main product + two fp16 correction products from a hi/lo split:
- *   ~fp32 accuracy, meets 1e-5; needs |q|,|k| < 65504) or SPLITQ_FUSED_TF32X1 (tf32 product only).
+ *   mode: SPLITQ_FUSED_F16X3 (operands split into h0 = fp16(x), h1 = fp16(x - h0); three fp16
+ *   products h0*h0 + h1*h0 + h0*h1 accumulated in fp32: ~fp32 accuracy, meets 1e-5) or
+ *   SPLITQ_FUSED_F16X1 (h0*h0 only, 11-bit mantissas).  Both need |q|,|k| < 65504 (fp16 range);
+ *   beyond it the scores come out NaN.
  *   ws: 256-byte aligned scratch of splitq_importance_fused_workspace_bytes(). */
-#define SPLITQ_FUSED_TF32X3 0
-#define SPLITQ_FUSED_TF32X1 1
+#define SPLITQ_FUSED_F16X3 0
+#define SPLITQ_FUSED_F16X1 1
 size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd);
 int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
                             const long long* k_strides_host, int B, int H, int KVH, int S, int hd,

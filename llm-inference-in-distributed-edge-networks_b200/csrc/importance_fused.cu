@@ -9,16 +9,18 @@
 //   pass 1  row block I (128 queries) x key blocks J<=I : S = Q_I K_J^T  -> per-row log-sum-exp
 //   pass 2  key block J (128 keys) x query blocks I>=J  : S^T = K_J Q_I^T -> p = exp(s - lse_i),
 //           summed over queries per key (one TMEM lane = one key: no cross-thread reduction)
-// QK^T runs on tcgen05 (kind::tf32, accumulators in TMEM, operands staged by TMA with 128-byte
-// swizzle).  The reference computes QK^T in true fp32; a single TF32 product misses the 1e-5
-// importance tolerance for trained-scale logits, so every operand x is pre-split into hi = tf32(x)
-// and lo = x - hi, and each tile accumulates hi*hi (kind::tf32) plus the two correction terms
-// lo*x and x*lo, which only need ~12 bits of each factor and therefore run as kind::f16 on
-// fp16(x) / fp16(lo) at twice the tf32 rate ("3xTF32" accuracy for 2/3 of the tensor time; valid
-// for |x| < 65504, beyond which fp16 overflows and the scores come out NaN).  SPLITQ_FUSED_TF32X1
-// keeps only hi*hi.  Four warpgroups per CTA: control (warp 0 = TMA producer of the streamed operand, warp 1 = MMA
-// issuer), two epilogue groups (one per TMEM accumulator), and loaders that put the fixed operand of
-// the next work item into tensor memory, so the MMA reads A from TMEM and only B from shared memory.
+// QK^T runs on tcgen05 (accumulators in TMEM, the streamed operand staged by TMA with 128-byte
+// swizzle).  The reference computes QK^T in true fp32; one 11-bit-mantissa product misses the 1e-5
+// importance tolerance for trained-scale logits, so every operand x is pre-split into
+// h0 = fp16(x) and h1 = fp16(x - h0) (22 mantissa bits together) and each tile accumulates
+// h0*h0 + h1*h0 + h0*h1 in fp32 -- three kind::f16 products, K = 16 per instruction.  The error is
+// that of the classic 3xTF32 scheme (same mantissa widths; the dropped h1*h1 term is ~2^-22) at 3/4
+// of the tensor time of one tf32 product plus two fp16 corrections, and with half the operand bytes.
+// Valid for |x| < 65504; beyond that fp16 overflows and the scores come out NaN (loudly wrong).
+// SPLITQ_FUSED_F16X1 keeps only h0*h0.  Four warpgroups per CTA: control (warp 0 = TMA producer of
+// the streamed operand, warp 1 = MMA issuer), two epilogue groups (alternate tiles, three TMEM
+// accumulators in rotation), and loaders that put the fixed operand of the next work item into
+// tensor memory, so the MMA reads A from TMEM and only B from shared memory.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <math.h>
@@ -32,17 +34,17 @@ namespace k2 {
 
 constexpr int kTile = 128;
 constexpr int kHd = 64;
-constexpr uint32_t kSlabBytes = 128 * 128;           // 128 rows x 32 fp32: one swizzle-128B slab
-constexpr uint32_t kPartBytes = 2 * kSlabBytes;      // 128 x 64 fp32 (hi or lo part)
-constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // hi + lo
-constexpr int kStages = 3;                           // streamed tiles in flight; one barrier pair and two TMA issues per tile
-constexpr int kAcc = 2;                              // TMEM accumulator buffers
+constexpr uint32_t kPartBytes = 128 * 128;           // 128 rows x 64 fp16: one swizzle-128B slab (h0 or h1 part)
+constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // h0 + h1
+constexpr int kStages = 4;                           // streamed tiles in flight; one barrier pair and one TMA issue per tile
+constexpr int kAcc = 3;                              // TMEM accumulator buffers, used in rotation
 constexpr int kThreads = 512;                         // 4 warpgroups: control, epilogue x2, operand loaders
-constexpr uint32_t kTmemCols = 512;                   // 2 accumulators (128 each) + 2 fixed-operand buffers (hi 64 + lo 64 each)
-constexpr uint32_t kTmemA = 256;                      // first column of the fixed-operand buffers
+constexpr uint32_t kTmemCols = 512;                   // 3 accumulators (128 each) + 2 fixed-operand buffers (h0 32 + h1 32 each)
+constexpr uint32_t kTmemA = kAcc * 128;               // first column of the fixed-operand buffers
+constexpr uint32_t kTmemABuf = 64;                    // columns per fixed-operand buffer (two halfs per column)
 constexpr uint32_t kBarOff = kStages * kOperandBytes;
-constexpr uint32_t kLseOff = kBarOff + 512;            // 14 mbarriers + TMEM base slot
-constexpr uint32_t kXchOff = kLseOff + 2 * kAcc * kTile * 4;  // lse: 2 groups x 2 buffers x 128 floats
+constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
+constexpr uint32_t kXchOff = kLseOff + 2 * 2 * kTile * 4;     // lse: 2 groups x 2 buffers x 128 floats
 constexpr uint32_t kSmemBytes = kXchOff + kTile * 8;  // dynamic smem base must be 1024-aligned (checked)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -75,19 +77,29 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         }
     }
 }
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
-        : "memory");
+// 4-D box {64 fp16, 128 rows, 1, parts}: a whole streamed tile (h0 and h1 parts) in ONE transaction,
+// landing as [part][128 rows][128 B] = two swizzle-128B slabs
+// same protocol guard without the printf: a call in the wait loop would force every register that is
+// live across it (the loaders' prefetched operand row) through local memory
+__device__ __forceinline__ void mbar_wait_quiet(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        if (clock64() - t0 > 4000000000LL) __trap();
+    }
 }
-// 5-D box {32 fp32, 128 rows, 2 k-chunks, 1, parts}: a whole streamed tile (both 32-wide k chunks, hi and
-// lo parts) in ONE transaction, landing as [part][k chunk][128 rows][128 B] = four swizzle-128B slabs
-__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3,
-                                            int c4) {
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
     asm volatile(
-        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-        ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -95,24 +107,8 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-        : "memory");
-}
-// A operand (M = 128 rows on the 128 TMEM lanes, K along columns) read from tensor memory
-__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
-        : "memory");
-}
-// same with fp16 operands (K = 16 per instruction; A packs two halfs per TMEM column)
+// A operand (M = 128 rows on the 128 TMEM lanes, K along columns, two halfs per column) read from
+// tensor memory; fp16 operands, K = 16 per instruction
 __device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -122,16 +118,16 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, 
         : "memory");
 }
 // 32 consecutive columns of this thread's TMEM lane <- registers
-__device__ __forceinline__ void tc_st32(uint32_t taddr, const float4 (&q)[8]) {
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint4 (&q)[8]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
         "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
         "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
         ::"r"(taddr),
-          "f"(q[0].x), "f"(q[0].y), "f"(q[0].z), "f"(q[0].w), "f"(q[1].x), "f"(q[1].y), "f"(q[1].z), "f"(q[1].w),
-          "f"(q[2].x), "f"(q[2].y), "f"(q[2].z), "f"(q[2].w), "f"(q[3].x), "f"(q[3].y), "f"(q[3].z), "f"(q[3].w),
-          "f"(q[4].x), "f"(q[4].y), "f"(q[4].z), "f"(q[4].w), "f"(q[5].x), "f"(q[5].y), "f"(q[5].z), "f"(q[5].w),
-          "f"(q[6].x), "f"(q[6].y), "f"(q[6].z), "f"(q[6].w), "f"(q[7].x), "f"(q[7].y), "f"(q[7].z), "f"(q[7].w)
+          "r"(q[0].x), "r"(q[0].y), "r"(q[0].z), "r"(q[0].w), "r"(q[1].x), "r"(q[1].y), "r"(q[1].z), "r"(q[1].w),
+          "r"(q[2].x), "r"(q[2].y), "r"(q[2].z), "r"(q[2].w), "r"(q[3].x), "r"(q[3].y), "r"(q[3].z), "r"(q[3].w),
+          "r"(q[4].x), "r"(q[4].y), "r"(q[4].z), "r"(q[4].w), "r"(q[5].x), "r"(q[5].y), "r"(q[5].z), "r"(q[5].w),
+          "r"(q[6].x), "r"(q[6].y), "r"(q[6].z), "r"(q[6].w), "r"(q[7].x), "r"(q[7].y), "r"(q[7].z), "r"(q[7].w)
         : "memory");
 }
 // one lane of a converged warp; the surrounding code stays warp-uniform so that descriptors and
@@ -143,41 +139,6 @@ __device__ __forceinline__ bool elect_one() {
 }
 template <int N> __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
-__device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
-    uint32_t r[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-// 64 consecutive columns of this thread's TMEM lane: two 32-column loads in flight, one wait
-__device__ __forceinline__ void tc_ld64(uint32_t taddr, float (&v)[64]) {
-    uint32_t r[64];
-#pragma unroll
-    for (int hlf = 0; hlf < 2; ++hlf) {
-        uint32_t* q = r + 32 * hlf;
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-            "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-            : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7]),
-              "=r"(q[8]), "=r"(q[9]), "=r"(q[10]), "=r"(q[11]), "=r"(q[12]), "=r"(q[13]), "=r"(q[14]), "=r"(q[15]),
-              "=r"(q[16]), "=r"(q[17]), "=r"(q[18]), "=r"(q[19]), "=r"(q[20]), "=r"(q[21]), "=r"(q[22]), "=r"(q[23]),
-              "=r"(q[24]), "=r"(q[25]), "=r"(q[26]), "=r"(q[27]), "=r"(q[28]), "=r"(q[29]), "=r"(q[30]), "=r"(q[31])
-            : "r"(taddr + 32 * hlf));
-    }
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(r[i]);
-}
 #ifdef SPLITQ_K2_NO_MUFU  // timing experiment only: how much of the epilogue is the MUFU pipe?
 __device__ __forceinline__ float ex2(float x) { return x * 0.5f; }
 #else
@@ -188,25 +149,24 @@ __device__ __forceinline__ float ex2(float x) {
 }
 #endif
 
-// K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {32 fp32, 128 rows} TMA box writes)
+// K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {64 fp16, 128 rows} TMA box writes)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
-// kind::tf32, fp32 accumulate, A and B K-major, M = N = 128
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
 // kind::f16 with fp16 A and B (format 0), fp32 accumulate, K-major, M = N = 128
 constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
 
 struct Params {
     int pass;          // 1 = row LSE, 2 = column sums
     int B, H, KVH, S, nb;
-    int causal, x3;
-    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue (timing experiments only)
+    int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
+    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads (timing experiments only)
     float cs;          // scaling * log2(e)
     float* lse2;       // (B,H,S) log2-domain log-sum-exp
     float* part_col;   // (B,H,S) sum_i p[i][j]
     float* part_last;  // (B,H,S) p[S-1][j]
-    const float *qhi, *qlo, *khi, *klo;  // dense (n,S,64) tf32 hi / lo parts
+    const uint4 *q16, *k16;  // dense (n,S,64) fp16 h0 part; the h1 part follows at +q_part / +k_part uint4
+    size_t q_part, k_part;
 };
 
 // Static schedule shared by all warp roles: items ranked by cost (tiles), dealt serpentine.
@@ -353,6 +313,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     const uint32_t bar_afull = bar0, bar_aempty = bar0 + 16;          // fixed operand in TMEM, 2 buffers
     const uint32_t bar_full = bar0 + 32, bar_empty = bar_full + 8 * kStages;
     const uint32_t bar_tfull = bar_empty + 8 * kStages, bar_tempty = bar_tfull + 8 * kAcc;
+    static_assert(32 + 16 * kStages + 16 * kAcc <= 504, "barrier region overflow");
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 504);
     float* lse_s = reinterpret_cast<float*>(gen + kLseOff);
 
@@ -369,7 +330,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
         for (int a = 0; a < kAcc; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
-            mbar_init(bar_tempty + 8 * a, 4);  // one arrive per warp of the owning epilogue group
+            mbar_init(bar_tempty + 8 * a, 4);  // one arrive per warp of the epilogue group that drained it
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -384,15 +345,15 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const CUtensorMap* str_map = p.pass == 1 ? &mapK : &mapQ;  // streamed operand, hi and lo parts in dim 3
+    const CUtensorMap* str_map = p.pass == 1 ? &mapK : &mapQ;  // streamed operand, h0 and h1 parts in dim 3
     const int group = p.H / p.KVH;
     const int wg = warp >> 2;  // warpgroup: 0 control, 1-2 epilogue, 3 fixed-operand loaders
 
     if (wg == 0) {
         reg_dec<56>();
         if (warp == 0) {
-            // ===== TMA producer: one stage = one streamed 128-row tile (hi + lo parts); per tile ONE
-            // barrier wait, one expect_tx and ONE 5-D TMA issue.  The per-transaction round trip
+            // ===== TMA producer: one stage = one streamed 128-row tile (h0 + h1 parts); per tile ONE
+            // barrier wait, one expect_tx and ONE 4-D TMA issue.  The per-transaction round trip
             // (try_wait + expect_tx + issue, ~300 cycles) was the limiter of a finer 16 KB-slab ring,
             // not bytes =====
             {
@@ -408,7 +369,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         mbar_wait(bar_empty + 8 * stage, sphase ^ 1);
                         if (elect_one()) {
                             mbar_expect_tx(fb, tile_tx);
-                            tma_load_5d(dst, str_map, fb, 0, t * kTile, 0, str_idx, 0);
+                            tma_load_4d(dst, str_map, fb, 0, t * kTile, str_idx, 0);
                         }
                         __syncwarp();
                         if (++stage == kStages) { stage = 0; sphase ^= 1; }
@@ -422,7 +383,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 Item it;
                 for (int k = 0; item_at(p, k, it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
-                    const uint32_t a_hi = tmem_base + kTmemA + ab * 128u, a_lo = a_hi + 64u;
+                    const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;
                     mbar_wait(bar_afull + 8 * ab, abphase);
                     tc_fence_after();
                     for (int t = it.t0; t < it.t1; ++t) {
@@ -433,26 +394,19 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         const uint32_t st0 = ring_s + stage * kOperandBytes;
                         if (elect_one()) {
                             if (!(p.dbg & 2)) {
-                                // main term: tf32(F) * tf32(S), K = 8 per instruction
+                                // F = fixed operand (A, TMEM), T = streamed operand (B, shared memory); K = 16 per
+                                // instruction, 8 TMEM columns / 32 smem bytes per step
+                                const uint32_t s_h0 = st0, s_h1 = st0 + kPartBytes;
 #pragma unroll
-                                for (int kc = 0; kc < 2; ++kc) {
-#pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk)
-                                        tc_mma_tf32_ts(d, a_hi + kc * 32u + kk * 8u, umma_desc(st0 + kc * kSlabBytes + kk * 32u), kIdesc,
-                                                       (uint32_t)(kc | kk));
-                                }
+                                for (int kk = 0; kk < 4; ++kk)   // h0(F) * h0(T)
+                                    tc_mma_f16_ts(d, a_h0 + kk * 8u, umma_desc(s_h0 + kk * 32u), kIdescF16, (uint32_t)kk);
                                 if (p.x3) {
-                                    // the two correction terms need ~12 bits of each factor: fp16 operands, K = 16 per
-                                    // instruction -> half the tensor time of a tf32 product.
-                                    // (F - tf32(F)) * S: A = packed fp16 lo part (TMEM cols a_lo+32..), B = fp16(S) slab
-                                    // F * (S - tf32(S)): A = packed fp16(F)      (TMEM cols a_lo+0..),  B = fp16 lo slab
-                                    const uint32_t s_h16 = st0 + kPartBytes, s_l16 = s_h16 + kSlabBytes;
 #pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk)
-                                        tc_mma_f16_ts(d, a_lo + 32u + kk * 8u, umma_desc(s_h16 + kk * 32u), kIdescF16, 1u);
+                                    for (int kk = 0; kk < 4; ++kk)  // h1(F) * h0(T)
+                                        tc_mma_f16_ts(d, a_h1 + kk * 8u, umma_desc(s_h0 + kk * 32u), kIdescF16, 1u);
 #pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk)
-                                        tc_mma_f16_ts(d, a_lo + kk * 8u, umma_desc(s_l16 + kk * 32u), kIdescF16, 1u);
+                                    for (int kk = 0; kk < 4; ++kk)  // h0(F) * h1(T)
+                                        tc_mma_f16_ts(d, a_h0 + kk * 8u, umma_desc(s_h1 + kk * 32u), kIdescF16, 1u);
                                 }
                             }
                             tc_commit(bar_empty + 8 * stage);   // stage reusable once these MMAs retire
@@ -468,33 +422,31 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             }
         }
     } else if (wg == 3) {
-        // ===== fixed-operand loaders: one thread per row; tf32 hi/lo parts -> TMEM (A operand) =====
+        // ===== fixed-operand loaders: one thread per row; fp16 h0 / h1 parts -> TMEM (A operand) =====
         reg_dec<56>();
         const int q4 = warp & 3;
         const int row = q4 * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
-        const float* fhi = p.pass == 1 ? p.qhi : p.khi;
-        const float* flo = p.pass == 1 ? p.qlo : p.klo;
+        const uint4* f16 = p.pass == 1 ? p.q16 : p.k16;
+        const size_t fpart = p.pass == 1 ? p.q_part : p.k_part;
         Item it;
         for (int k = 0; item_at(p, k, it); ++k) {
             const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
             const int b = it.bh / p.H, h = it.bh % p.H;
             const int fix_idx = p.pass == 1 ? it.bh : b * p.KVH + h / group;
             const int g = it.blk * kTile + row;
-            const size_t off = ((size_t)fix_idx * p.S + (g < p.S ? g : 0)) * kHd;
-            mbar_wait(bar_aempty + 8 * ab, abphase ^ 1);
+            const uint4* src = f16 + ((size_t)fix_idx * p.S + (g < p.S ? g : 0)) * (kHd * 2 / 16);
+            uint4 q[8];  // this row: 64 halfs = 128 B = 32 TMEM columns per part; h0 is fetched ahead of the wait
+#pragma unroll
+            for (int i = 0; i < 8; ++i) q[i] = g < p.S ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
+            mbar_wait_quiet(bar_aempty + 8 * ab, abphase ^ 1);
             tc_fence_after();
-            const uint32_t a0 = tmem_base + kTmemA + ab * 128u + lane_addr;
-            const int nparts = p.x3 ? 2 : 1;
-            for (int part = 0; part < nparts; ++part) {
-                const float4* src = reinterpret_cast<const float4*>((part == 0 ? fhi : flo) + off);
+            const uint32_t a0 = tmem_base + kTmemA + ab * kTmemABuf + lane_addr;
+            tc_st32(a0, q);
+            if (p.x3) {
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    float4 q[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) q[i] = g < p.S ? __ldg(src + c * 8 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    tc_st32(a0 + part * 64u + c * 32u, q);
-                }
+                for (int i = 0; i < 8; ++i) q[i] = g < p.S ? __ldg(src + fpart + i) : make_uint4(0u, 0u, 0u, 0u);
+                tc_st32(a0 + 32u, q);
             }
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             tc_fence_before();
@@ -503,18 +455,19 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
     } else {
         reg_inc<200>();
-        // ===== epilogue: two groups of 4 warps; group g owns TMEM accumulator g, i.e. every other
-        // tile; a thread owns one TMEM lane (tile row).  Each thread ping-pongs two 64-column
-        // register buffers: the tcgen05.ld of the next half tile is in flight while the exp2 loop
-        // runs on the current one, so TMEM reads (64 B/clk/SM) hide behind the MUFU work.
+        // ===== epilogue: two groups of 4 warps; group g takes the tiles of parity g (counted over the
+        // whole CTA), tile n lives in TMEM accumulator n % 3; a thread owns one TMEM lane (tile
+        // row).  Each thread ping-pongs two 64-column register buffers: the tcgen05.ld of the next
+        // half tile is in flight while the exp2 loop runs on the current one, so TMEM reads
+        // (64 B/clk/SM) hide behind the MUFU work, and the third accumulator lets the MMA of tile
+        // n + 2 start before tile n has been read out.
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
-        const int grp = wg - 1;                     // accumulator buffer / tile parity of this group
+        const int grp = wg - 1;                     // tile parity of this group
         const int row = q4 * 32 + lane;
         const int gt = threadIdx.x & 127;           // thread index inside the group
-        const uint32_t my_tfull = bar_tfull + 8 * grp, my_tempty = bar_tempty + 8 * grp;
-        const uint32_t my_tmem = tmem_base + grp * kTile + ((uint32_t)(q4 * 32) << 16);
+        const uint32_t tmem_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         float* lse_g = lse_s + grp * 2 * kTile;     // two lse buffers per group (pass 2)
-        uint32_t n = 0, uses = 0;                   // tiles seen by the CTA / tiles taken by this group
+        uint32_t n = 0;                             // tiles seen by the CTA so far
         Item it;
         for (int k = 0; item_at(p, k, it); ++k) {
             const int g = it.blk * kTile + row;     // global index of this thread's row
@@ -522,44 +475,52 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             float colsum = 0.f, lastp = 0.f;        // pass 2
             const int ntiles = it.t1 - it.t0;
             int t = it.t0 + (int)((n ^ (uint32_t)grp) & 1u);  // first tile of this item that is mine
+            uint32_t gn = n + (uint32_t)(t - it.t0);          // its index in the CTA's tile sequence
             n += (uint32_t)ntiles;
             if (t < it.t1) {
                 float va[64], vb[64];
+                if (p.dbg & 4) {
+#pragma unroll
+                    for (int i = 0; i < 64; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
+                }
                 uint32_t lb = 0;                    // lse buffer of the current tile
                 if (p.pass == 2) {
                     const int qi = t * kTile + gt;
                     lse_g[gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
                 }
-                mbar_wait(my_tfull, uses & 1u);
-                ++uses;
+                uint32_t a = gn % (uint32_t)kAcc;   // accumulator of the current tile
+                uint32_t cur_tmem = tmem_lane + a * kTile;
+                mbar_wait(bar_tfull + 8 * a, (gn / (uint32_t)kAcc) & 1u);
                 tc_fence_after();
-                tc_ld64_issue(my_tmem, va);
+                if (!(p.dbg & 4)) tc_ld64_issue(cur_tmem, va);
                 tc_ld_wait();
-                for (; t < it.t1; t += 2) {
+                for (; t < it.t1; t += 2, gn += 2) {
                     const bool edge = (p.causal && t == it.blk) || (t * kTile + kTile > p.S);
                     const bool has_last = (p.S - 1) / kTile == t;
                     const bool has_next = t + 2 < it.t1;
                     const float* lse_t = lse_g + lb * kTile;
                     if (p.pass == 2) group_bar(grp);          // this tile's lse values are in shared memory
-                    tc_ld64_issue(my_tmem + 64, vb);          // second half in flight ...
+                    if (!(p.dbg & 4)) tc_ld64_issue(cur_tmem + 64, vb);  // second half in flight ...
                     if (p.dbg & 1) { colsum += va[0] + va[63]; l += va[1]; }
                     else if (p.pass == 1) pass1_half(va, t * kTile, edge, g, p, m, l);
                     else pass2_half(va, lse_t, t * kTile, edge, g, has_last, (p.S - 1) % kTile, p, colsum, lastp);
                     tc_ld_wait();                             // ... now in registers: accumulator is drained
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(my_tempty);
+                    if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
+                    const uint32_t na = (gn + 2u) % (uint32_t)kAcc, nph = ((gn + 2u) / (uint32_t)kAcc) & 1u;
+                    const uint32_t nxt_tmem = tmem_lane + na * kTile;
                     bool ready = false;
                     if (has_next) {
                         if (p.pass == 2) {
                             const int qi = (t + 2) * kTile + gt;
                             lse_g[(lb ^ 1u) * kTile + gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
                         }
-                        ready = mbar_test(my_tfull, uses & 1u);
+                        ready = mbar_test(bar_tfull + 8 * na, nph);
                         ready = __all_sync(0xffffffffu, ready);
                         if (ready) {
                             tc_fence_after();
-                            tc_ld64_issue(my_tmem, va);       // next tile's first half in flight ...
+                            if (!(p.dbg & 4)) tc_ld64_issue(nxt_tmem, va);  // next tile's first half in flight ...
                         }
                     }
                     if (p.dbg & 1) { colsum += vb[0] + vb[63]; l += vb[1]; }
@@ -567,13 +528,14 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     else pass2_half(vb, lse_t + 64, t * kTile + 64, edge, g, has_last, (p.S - 1) % kTile - 64, p, colsum, lastp);
                     if (has_next) {
                         if (!ready) {
-                            mbar_wait(my_tfull, uses & 1u);
+                            mbar_wait(bar_tfull + 8 * na, nph);
                             tc_fence_after();
-                            tc_ld64_issue(my_tmem, va);
+                            if (!(p.dbg & 4)) tc_ld64_issue(nxt_tmem, va);
                         }
-                        ++uses;
                         tc_ld_wait();                         // ... and landed
                         lb ^= 1u;
+                        a = na;
+                        cur_tmem = nxt_tmem;
                     }
                 }
             }
@@ -607,22 +569,19 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     }
 }
 
-// ---- operand preparation: fp32 -> tf32 hi + tf32 lo, gathered from arbitrary (b,h,s) strides ----
-__device__ __forceinline__ float tf32_rn(float x) {
-    uint32_t u;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
-    return __uint_as_float(u);
-}
+// ---- operand preparation: fp32 -> fp16 h0 = fp16(x) and h1 = fp16(x - h0), gathered from arbitrary
+// (b,h,s) strides into dense (n, S, 64) fp16 arrays (one 128-byte row per token) ----
 __global__ void __launch_bounds__(256)
-split_tf32_kernel(const float* __restrict__ x, long long sb, long long sh, long long ss, int heads, int S,
-                  float* __restrict__ hi, float* __restrict__ lo, int vec) {
+split_f16_kernel(const float* __restrict__ x, long long sb, long long sh, long long ss, int heads, int S,
+                 uint2* __restrict__ h0, uint2* __restrict__ h1, int vec) {
     // grid.y = b * heads + h (one division per CTA); grid.x strides over the S*16 float4 of that
     // head, 4 per thread with 256-thread spacing so every warp access is contiguous
     const int bh = blockIdx.y;
     const int b = bh / heads, h = bh - b * heads;
     const float* src0 = x + b * sb + h * sh;
     const int n4 = S * (kHd / 4);
-    float4* hi4 = reinterpret_cast<float4*>(hi) + (size_t)bh * n4;
+    uint2* o0 = h0 + (size_t)bh * n4;
+    uint2* o1 = h1 + (size_t)bh * n4;
     constexpr int UN = 4;
     const int i0 = blockIdx.x * (256 * UN) + threadIdx.x;
     float4 v[UN];
@@ -639,16 +598,12 @@ split_tf32_kernel(const float* __restrict__ x, long long sb, long long sh, long 
     for (int u = 0; u < UN; ++u) {
         const int i = i0 + u * 256;
         if (i < n4) {
-            float4 a;
-            a.x = tf32_rn(v[u].x); a.y = tf32_rn(v[u].y); a.z = tf32_rn(v[u].z); a.w = tf32_rn(v[u].w);
-            hi4[i] = a;
-            // second array, per row of 64 words: words 0..31 = fp16(x) (64 halfs), words 32..63 = fp16(x - hi)
-            const __half2 h01 = __floats2half2_rn(v[u].x, v[u].y), h23 = __floats2half2_rn(v[u].z, v[u].w);
-            const __half2 l01 = __floats2half2_rn(v[u].x - a.x, v[u].y - a.y), l23 = __floats2half2_rn(v[u].z - a.z, v[u].w - a.w);
-            uint2* row = reinterpret_cast<uint2*>(lo) + ((size_t)bh * S + (i >> 4)) * 32;  // 64 words = 32 uint2
-            const int d4 = i & 15;                                                    // 4 elements -> 2 words
-            row[d4] = make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
-            row[16 + d4] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
+            const __half2 a01 = __floats2half2_rn(v[u].x, v[u].y), a23 = __floats2half2_rn(v[u].z, v[u].w);
+            const float2 f01 = __half22float2(a01), f23 = __half22float2(a23);
+            const __half2 l01 = __floats2half2_rn(v[u].x - f01.x, v[u].y - f01.y);
+            const __half2 l23 = __floats2half2_rn(v[u].z - f23.x, v[u].w - f23.y);
+            o0[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a01), *reinterpret_cast<const uint32_t*>(&a23));
+            o1[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
         }
     }
 }
@@ -747,17 +702,16 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// the (n, S, 64) hi array and the lo array behind it, viewed as a 5-D fp32 tensor
-// (32 in-chunk, S rows, 2 k-chunks, n, 2 parts); box = 32 x 128 x 2 x 1 x parts, 128-byte swizzle, rows past S
-// read as zero
-static int make_map(CUtensorMap* map, float* base, int S, long long n, size_t part_stride_bytes, int parts) {
+// the (n, S, 64) fp16 h0 array and the h1 array behind it, viewed as a 4-D tensor
+// (64 halfs, S rows, n, 2 parts); box = 64 x 128 x 1 x parts, 128-byte swizzle, rows past S read as zero
+static int make_map(CUtensorMap* map, void* base, int S, long long n, size_t part_stride_bytes, int parts) {
     EncodeTiledFn enc = encode_fn();
     SPLITQ_REQUIRE(enc != nullptr, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled is unavailable");
-    cuuint64_t dims[5] = {32, (cuuint64_t)S, 2, (cuuint64_t)n, 2};
-    cuuint64_t strides[4] = {(cuuint64_t)kHd * 4, 128, (cuuint64_t)S * kHd * 4, (cuuint64_t)part_stride_bytes};
-    cuuint32_t box[5] = {32, (cuuint32_t)kTile, 2, 1, (cuuint32_t)parts};
-    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 5, base, dims, strides, box, estr,
+    cuuint64_t dims[4] = {(cuuint64_t)kHd, (cuuint64_t)S, (cuuint64_t)n, 2};
+    cuuint64_t strides[3] = {(cuuint64_t)kHd * 2, (cuuint64_t)S * kHd * 2, (cuuint64_t)part_stride_bytes};
+    cuuint32_t box[4] = {(cuuint32_t)kHd, (cuuint32_t)kTile, 1, (cuuint32_t)parts};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, base, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     SPLITQ_REQUIRE(r == CUDA_SUCCESS, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -767,13 +721,13 @@ static int make_map(CUtensorMap* map, float* base, int S, long long n, size_t pa
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
 
 struct WsLayout {
-    size_t qhi, qlo, khi, klo, lse, pcol, plast, total;
+    size_t q0, q1, k0, k1, lse, pcol, plast, total;  // fp16 h0 / h1 parts of Q and K, then per-(b,h,s) floats
 };
 static WsLayout ws_layout(int B, int H, int KVH, int S) {
     WsLayout w;
-    const size_t q = align256((size_t)B * H * S * kHd * 4), k = align256((size_t)B * KVH * S * kHd * 4);
+    const size_t q = align256((size_t)B * H * S * kHd * 2), k = align256((size_t)B * KVH * S * kHd * 2);
     const size_t v = align256((size_t)B * H * S * 4);
-    w.qhi = 0; w.qlo = q; w.khi = 2 * q; w.klo = 2 * q + k;
+    w.q0 = 0; w.q1 = q; w.k0 = 2 * q; w.k1 = 2 * q + k;
     w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + v; w.total = w.plast + v;
     return w;
 }
@@ -800,9 +754,9 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
                    "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
     SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
                    "materialised path splitq_importance_colmean", hd);
-    const int dbg = (mode >> 4) & 3;  // undocumented timing-experiment bits
+    const int dbg = (mode >> 4) & 7;  // undocumented timing-experiment bits
     mode &= 15;
-    SPLITQ_REQUIRE(mode == SPLITQ_FUSED_TF32X3 || mode == SPLITQ_FUSED_TF32X1, SPLITQ_ERR_ARG,
+    SPLITQ_REQUIRE(mode == SPLITQ_FUSED_F16X3 || mode == SPLITQ_FUSED_F16X1, SPLITQ_ERR_ARG,
                    "importance_fused: unknown mode %d", mode);
     SPLITQ_REQUIRE(scaling > 0.f, SPLITQ_ERR_ARG, "importance_fused: scaling must be positive");
     const WsLayout wl = ws_layout(B, H, KVH, S);
@@ -826,8 +780,6 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
         SPLITQ_LAUNCH_CHECK("last_row kernels");
         return SPLITQ_OK;
     }
-    float *qhi = (float*)(w8 + wl.qhi), *qlo = (float*)(w8 + wl.qlo), *khi = (float*)(w8 + wl.khi),
-          *klo = (float*)(w8 + wl.klo);
 
     {   // operand split
         auto vec_ok = [](const float* p, const long long* s) {
@@ -835,28 +787,29 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
         };
         SPLITQ_REQUIRE((long long)B * H <= 65535, SPLITQ_ERR_ARG, "importance_fused: B*H=%lld > 65535", (long long)B * H);
         const unsigned gx = (unsigned)cdiv((long long)S * (kHd / 4), 256 * 4);
-        split_tf32_kernel<<<dim3(gx, B * H), 256, 0, st>>>(Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S,
-                                                        qhi, qlo, vec_ok(Q, q_strides_host));
-        split_tf32_kernel<<<dim3(gx, B * KVH), 256, 0, st>>>(K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH,
-                                                          S, khi, klo, vec_ok(K, k_strides_host));
-        SPLITQ_LAUNCH_CHECK("split_tf32_kernel");
+        split_f16_kernel<<<dim3(gx, B * H), 256, 0, st>>>(Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S,
+                                                       (uint2*)(w8 + wl.q0), (uint2*)(w8 + wl.q1), vec_ok(Q, q_strides_host));
+        split_f16_kernel<<<dim3(gx, B * KVH), 256, 0, st>>>(K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH, S,
+                                                         (uint2*)(w8 + wl.k0), (uint2*)(w8 + wl.k1), vec_ok(K, k_strides_host));
+        SPLITQ_LAUNCH_CHECK("split_f16_kernel");
     }
 
-    const int parts = mode == SPLITQ_FUSED_TF32X3 ? 2 : 1;
+    const int parts = mode == SPLITQ_FUSED_F16X3 ? 2 : 1;
     CUtensorMap mq, mk;
-    if (int rc = make_map(&mq, qhi, S, (long long)B * H, wl.qlo - wl.qhi, parts)) return rc;
-    if (int rc = make_map(&mk, khi, S, (long long)B * KVH, wl.klo - wl.khi, parts)) return rc;
+    if (int rc = make_map(&mq, w8 + wl.q0, S, (long long)B * H, wl.q1 - wl.q0, parts)) return rc;
+    if (int rc = make_map(&mk, w8 + wl.k0, S, (long long)B * KVH, wl.k1 - wl.k0, parts)) return rc;
 
     Params p;
     p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = cdiv(S, kTile);
     p.causal = causal ? 1 : 0;
-    p.x3 = mode == SPLITQ_FUSED_TF32X3;
+    p.x3 = mode == SPLITQ_FUSED_F16X3;
     p.dbg = dbg;
     p.cs = scaling * 1.4426950408889634f;
     p.lse2 = (float*)(w8 + wl.lse);
     p.part_col = (float*)(w8 + wl.pcol);
     p.part_last = (float*)(w8 + wl.plast);
-    p.qhi = qhi; p.qlo = qlo; p.khi = khi; p.klo = klo;
+    p.q16 = (const uint4*)(w8 + wl.q0); p.k16 = (const uint4*)(w8 + wl.k0);
+    p.q_part = (wl.q1 - wl.q0) / 16; p.k_part = (wl.k1 - wl.k0) / 16;
 
     static bool attr_set[64] = {};
     int dev = 0, sms = 148;

@@ -18,7 +18,7 @@ NORM_LAYERNORM, NORM_RMSNORM = 0, 1
 FLAG_CAUSAL_HINT = 1
 MAX_SELECT_S = 32768
 NOALLOC_MAX_WINDOWS = 1024
-FUSED_TF32X3, FUSED_TF32X1 = 0, 1
+FUSED_F16X3, FUSED_F16X1 = 0, 1
 CHANNEL_METHODS = {"channel_8": 0, "channel_4": 1, "channel_1_mean": 2, "channel_1_max": 3}
 
 _vp, _sz, _i, _u = C.c_void_p, C.c_size_t, C.c_int, C.c_uint

@@ -107,7 +107,7 @@ def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]]
 
 
 def importance_fused(q: torch.Tensor, k: torch.Tensor, scaling: float, causal: bool = True,
-                     mode: int = N.FUSED_TF32X3, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
+                     mode: int = N.FUSED_F16X3, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
                      want_last: bool = False, out_col: Optional[torch.Tensor] = None,
                      out_last: Optional[torch.Tensor] = None):
     """q: (B,H,S,64), k: (B,KVH,S,64) post-RoPE fp32 CUDA tensors (any batch/head/seq strides, e.g.
@@ -263,7 +263,7 @@ class BoundaryPlan:
 
     def __init__(self, B: int, H: int, S: int, D: int, ladder: Ladder, scale_mode: int = N.SCALE_GROUP,
                  method: str = "regular_importance", src_device="cuda:0", dst_device=None,
-                 causal_hint: bool = False, KVH: Optional[int] = None, fused_mode: int = N.FUSED_TF32X3):
+                 causal_hint: bool = False, KVH: Optional[int] = None, fused_mode: int = N.FUSED_F16X3):
         self.B, self.H, self.S, self.D = B, H, S, D
         self.ladder, self.scale_mode, self.method, self.causal_hint = list(ladder), scale_mode, method, causal_hint
         self.src = torch.device(src_device)

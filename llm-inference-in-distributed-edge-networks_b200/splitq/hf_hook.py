@@ -55,7 +55,7 @@ class ImportanceCapture:
     last-row importance of its (B,H,S,S) attention without materialising it."""
 
     def __init__(self, model, layers: Optional[Sequence[int]] = None, want_col: bool = True,
-                 want_last: bool = True, head_weights=None, mode: int = boundary.N.FUSED_TF32X3):
+                 want_last: bool = True, head_weights=None, mode: int = boundary.N.FUSED_F16X3):
         self.model = model
         self.layers = None if layers is None else set(layers)
         self.want_col, self.want_last, self.head_weights, self.mode = want_col, want_last, head_weights, mode
