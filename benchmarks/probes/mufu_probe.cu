@@ -22,7 +22,22 @@ __global__ void probe(float* out, long long* clk, int iters, float cs, float off
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
         for (int i = 0; i < 64; i += 4) {
-            if (MIX) {
+            if (MIX >= 2) {
+                // batched form: MIX exp2 results land in temporaries before any of them is consumed
+                constexpr int BM = MIX >= 2 ? MIX : 4;
+                if (i % BM == 0) {
+                    float t[BM];
+#pragma unroll
+                    for (int j = 0; j < BM; ++j) t[j] = ex2(fmaf(v[i + j], cs, -off));
+#pragma unroll
+                    for (int j = 0; j < BM; j += 4) {
+                        s0 += t[j + 0];
+                        s1 += t[j + 1];
+                        s2 += t[j + 2];
+                        s3 += t[j + 3];
+                    }
+                }
+            } else if (MIX) {
                 s0 += ex2(fmaf(v[i + 0], cs, -off));
                 s1 += ex2(fmaf(v[i + 1], cs, -off));
                 s2 += ex2(fmaf(v[i + 2], cs, -off));
@@ -50,11 +65,14 @@ int main() {
     cudaMalloc(&out, 148 * 1024 * sizeof(float));
     cudaMalloc(&clk, 148 * sizeof(long long));
     const int iters = 2000;
-    for (int mix = 0; mix < 2; ++mix)
+    for (int mix = 0; mix < 5; ++mix)
         for (int warps_per_smsp = 1; warps_per_smsp <= 4; warps_per_smsp *= 2) {
             const int threads = 128 * warps_per_smsp;
             for (int rep = 0; rep < 2; ++rep) {
-                if (mix) probe<1><<<148, threads>>>(out, clk, iters, 0.18f, 3.f);
+                if (mix == 1) probe<1><<<148, threads>>>(out, clk, iters, 0.18f, 3.f);
+                else if (mix == 2) probe<8><<<148, threads>>>(out, clk, iters, 0.18f, 3.f);
+                else if (mix == 3) probe<16><<<148, threads>>>(out, clk, iters, 0.18f, 3.f);
+                else if (mix == 4) probe<32><<<148, threads>>>(out, clk, iters, 0.18f, 3.f);
                 else probe<0><<<148, threads>>>(out, clk, iters, 0.18f, 3.f);
             }
             cudaDeviceSynchronize();
@@ -65,7 +83,7 @@ int main() {
             c /= 148;
             const double warp_instr_per_smsp = (double)iters * 64 * warps_per_smsp;
             printf("%s warps/SMSP=%d: %.2f clk per warp-level EX2 per sub-partition (%.1f ex2/clk/SM)\n",
-                   mix ? "ffma+ex2+fadd" : "ex2 only     ", warps_per_smsp, c / warp_instr_per_smsp,
+                   mix == 0 ? "ex2 only        " : mix == 1 ? "ffma+ex2+fadd   " : mix == 2 ? "batched by 8    " : mix == 3 ? "batched by 16   " : "batched by 32   ", warps_per_smsp, c / warp_instr_per_smsp,
                    32.0 * 4 * warp_instr_per_smsp / c);
         }
     printf("%s\n", cudaGetErrorString(cudaGetLastError()));

@@ -44,8 +44,8 @@ constexpr uint32_t kTmemA = kAcc * 128;               // first column of the fix
 constexpr uint32_t kTmemABuf = 64;                    // columns per fixed-operand buffer (two halfs per column)
 constexpr uint32_t kBarOff = kStages * kOperandBytes;
 constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
-constexpr uint32_t kXchOff = kLseOff + 2 * 2 * kTile * 4;     // lse: 2 groups x 2 buffers x 128 floats
-constexpr uint32_t kSmemBytes = kXchOff + kTile * 8;  // dynamic smem base must be 1024-aligned (checked)
+constexpr uint32_t kSmemBytes = kLseOff + 8 * 2 * kTile * 4;  // lse: 8 epilogue warps x 2 buffers x 128 floats
+// (the dynamic smem base must be 1024-aligned; checked in the kernel)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -141,13 +141,24 @@ template <int N> __device__ __forceinline__ void reg_dec() { asm volatile("setma
 template <int N> __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 #ifdef SPLITQ_K2_NO_MUFU  // timing experiment only: how much of the epilogue is the MUFU pipe?
 __device__ __forceinline__ float ex2(float x) { return x * 0.5f; }
+__device__ __forceinline__ float ex2_ordered(float x) { return x * 0.5f; }
 #else
 __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// volatile: the compiler keeps these in program order, which is how the epilogue loops force
+// kExpBatch exp2 in flight before the first result is consumed.  Measured (benchmarks/probes/
+// mufu_probe.cu): ptxas' own schedule consumes each result three MUFUs later, which caps a lone warp at
+// 13.9 clk per warp-level EX2; batches of 16 reach 9.8 (the pipe's floor is 8).
+__device__ __forceinline__ float ex2_ordered(float x) {
+    float y;
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 #endif
+constexpr int kExpBatch = 16;
 
 // K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {64 fp16, 128 rows} TMA box writes)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
@@ -157,12 +168,12 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
 constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
 
 struct Params {
-    int pass;          // 1 = row LSE, 2 = column sums
     int B, H, KVH, S, nb;
     int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
     int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads (timing experiments only)
     float cs;          // scaling * log2(e)
-    float* lse2;       // (B,H,S) log2-domain log-sum-exp
+    float2* ml;        // (2 groups,B,H,S) pass-1 partial (max, sum) of each epilogue group
+    float* lse2;       // (B,H,S) log2-domain log-sum-exp (lse_combine_kernel)
     float* part_col;   // (B,H,S) sum_i p[i][j]
     float* part_last;  // (B,H,S) p[S-1][j]
     const uint4 *q16, *k16;  // dense (n,S,64) fp16 h0 part; the h1 part follows at +q_part / +k_part uint4
@@ -173,25 +184,26 @@ struct Params {
 struct Item {
     int bh, blk, t0, t1;  // streamed block range [t0, t1)
 };
+template <int PASS>
 __device__ __forceinline__ bool item_at(const Params& p, int k, Item& it) {
     // Rank r of the k-th item of this CTA.  Items are ordered window by window (so that the CTAs
     // running at any moment stream one window's operands and those stay in L2), inside a window by
     // cost (number of streamed tiles, largest first), and dealt to CTAs in serpentine order.
-    const int G = gridDim.x, c = blockIdx.x;
-    const long long total = (long long)p.B * p.H * p.nb;
-    const long long r = (long long)k * G + ((k & 1) ? (G - 1 - c) : c);
+    const uint32_t G = gridDim.x, c = blockIdx.x;
+    const uint32_t total = (uint32_t)p.B * p.H * p.nb;  // < 2^31, checked on the host
+    const uint32_t r = (uint32_t)k * G + ((k & 1) ? (G - 1 - c) : c);
     if (r >= total) return false;
-    const int per_window = p.H * p.nb;
-    const int b = (int)(r / per_window);
-    const int q = (int)(r % per_window);
-    const int rank = q / p.H;
-    it.bh = b * p.H + q % p.H;
-    if (p.pass == 1) {
-        it.blk = p.nb - 1 - rank;  // most key blocks first
+    const uint32_t per_window = (uint32_t)p.H * p.nb;
+    const uint32_t b = r / per_window;
+    const uint32_t q = r - b * per_window;
+    const uint32_t rank = q / (uint32_t)p.H;
+    it.bh = (int)(b * p.H + (q - rank * p.H));
+    if (PASS == 1) {
+        it.blk = p.nb - 1 - (int)rank;  // most key blocks first
         it.t0 = 0;
         it.t1 = p.causal ? it.blk + 1 : p.nb;
     } else {
-        it.blk = rank;             // most query blocks first
+        it.blk = (int)rank;        // most query blocks first
         it.t0 = p.causal ? it.blk : 0;
         it.t1 = p.nb;
     }
@@ -228,14 +240,29 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
         : "memory");
     return done != 0;
 }
-__device__ __forceinline__ void group_bar(int grp) {
-    if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
-    else asm volatile("bar.sync 2, 128;" ::: "memory");
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// log2-domain lse of queries q0..q0+3 of one (b,h) row block; queries past S read +inf (-> p = 0)
+__device__ __forceinline__ float4 load_lse4(const float* __restrict__ row0, int q0, int S, bool vec) {
+    if (vec && q0 + 3 < S) return __ldg(reinterpret_cast<const float4*>(row0 + q0));
+    float4 r;
+    r.x = q0 + 0 < S ? __ldg(row0 + q0 + 0) : INFINITY;
+    r.y = q0 + 1 < S ? __ldg(row0 + q0 + 1) : INFINITY;
+    r.z = q0 + 2 < S ? __ldg(row0 + q0 + 2) : INFINITY;
+    r.w = q0 + 3 < S ? __ldg(row0 + q0 + 3) : INFINITY;
+    return r;
 }
 // pass 1, 64 columns (= keys c0..c0+63) of query row g: online log-sum-exp in the log2 domain
-__device__ __forceinline__ void pass1_half(float (&v)[64], int c0, bool edge, int g, const Params& p, float& m, float& l) {
+__device__ __forceinline__ void pass1_half(float (&v)[64], int c0, bool edge, int g, int S, bool causal, float cs, float& m,
+                                           float& l) {
     if (edge) {  // valid iff key < S and (not causal or key <= query)
-        const int jmax = min(p.S - 1, p.causal ? g : p.S - 1);
+        const int jmax = min(S - 1, causal ? g : S - 1);
 #pragma unroll
         for (int i = 0; i < 64; ++i)
             if (c0 + i > jmax) v[i] = -INFINITY;
@@ -246,61 +273,91 @@ __device__ __forceinline__ void pass1_half(float (&v)[64], int c0, bool edge, in
         cm0 = fmaxf(cm0, v[i]);
         cm1 = fmaxf(cm1, v[i + 1]);
     }
-    const float cm = fmaxf(cm0, cm1) * p.cs;
+    const float cm = fmaxf(cm0, cm1) * cs;
     if (cm > -INFINITY) {  // at least one valid column for this row in this half
         const float mn = fmaxf(m, cm);
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-        for (int i = 0; i < 64; i += 4) {
-            s0 += ex2(fmaf(v[i + 0], p.cs, -mn));
-            s1 += ex2(fmaf(v[i + 1], p.cs, -mn));
-            s2 += ex2(fmaf(v[i + 2], p.cs, -mn));
-            s3 += ex2(fmaf(v[i + 3], p.cs, -mn));
+        for (int i0 = 0; i0 < 64; i0 += kExpBatch) {
+            float e[kExpBatch];
+#pragma unroll
+            for (int j = 0; j < kExpBatch; ++j) e[j] = ex2_ordered(fmaf(v[i0 + j], cs, -mn));
+#pragma unroll
+            for (int j = 0; j < kExpBatch; j += 4) {
+                s0 += e[j + 0];
+                s1 += e[j + 1];
+                s2 += e[j + 2];
+                s3 += e[j + 3];
+            }
         }
         l = l * ex2(m - mn) + ((s0 + s1) + (s2 + s3));
         m = mn;
     }
 }
-// pass 2, 64 columns (= queries c0..c0+63) of key row g: sum of exp2(s*cs - lse2[query]).
-// SPECIAL = diagonal / last-row tiles (masking and the last-row pick); the common tile runs the
-// branch-free instantiation so that the 64 exp2 form one straight-line, fully scheduled block.
+// pass 2, 64 columns (= queries c0..c0+63) of key row g: sum of exp2(s*cs - lse2[query]); ls = shared
+// address of the 64 lse values.  SPECIAL = diagonal / last-row tiles (masking and the last-row
+// pick); the common tile runs the branch-free instantiation so that the 64 exp2 form one
+// straight-line, fully scheduled block.
 template <bool SPECIAL>
-__device__ __forceinline__ void pass2_body(const float (&v)[64], const float* ls, int c0, bool mask, int g, int last_col,
+__device__ __forceinline__ void pass2_body(const float (&v)[64], uint32_t ls, int c0, bool mask, int g, int last_col,
                                            float cs, float& colsum, float& lastp) {
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 64; i += 4) {
-        const float4 ls4 = *reinterpret_cast<const float4*>(ls + i);
-        float p0 = ex2(fmaf(v[i + 0], cs, -ls4.x));
-        float p1 = ex2(fmaf(v[i + 1], cs, -ls4.y));
-        float p2 = ex2(fmaf(v[i + 2], cs, -ls4.z));
-        float p3 = ex2(fmaf(v[i + 3], cs, -ls4.w));
-        if (SPECIAL) {
-            const int qi = c0 + i;  // valid iff query >= key (queries >= S carry lse = +inf -> 0)
-            p0 = (mask && qi + 0 < g) ? 0.f : p0;
-            p1 = (mask && qi + 1 < g) ? 0.f : p1;
-            p2 = (mask && qi + 2 < g) ? 0.f : p2;
-            p3 = (mask && qi + 3 < g) ? 0.f : p3;
-            lastp = (last_col == i + 0) ? p0 : lastp;
-            lastp = (last_col == i + 1) ? p1 : lastp;
-            lastp = (last_col == i + 2) ? p2 : lastp;
-            lastp = (last_col == i + 3) ? p3 : lastp;
+    for (int i0 = 0; i0 < 64; i0 += kExpBatch) {
+        float e[kExpBatch];
+#pragma unroll
+        for (int j = 0; j < kExpBatch; j += 4) {
+            const float4 ls4 = lds128(ls + 4u * (i0 + j));
+            e[j + 0] = ex2_ordered(fmaf(v[i0 + j + 0], cs, -ls4.x));
+            e[j + 1] = ex2_ordered(fmaf(v[i0 + j + 1], cs, -ls4.y));
+            e[j + 2] = ex2_ordered(fmaf(v[i0 + j + 2], cs, -ls4.z));
+            e[j + 3] = ex2_ordered(fmaf(v[i0 + j + 3], cs, -ls4.w));
         }
-        s0 += p0;
-        s1 += p1;
-        s2 += p2;
-        s3 += p3;
+#pragma unroll
+        for (int j = 0; j < kExpBatch; ++j) {
+            if (SPECIAL) {
+                const int i = i0 + j;  // valid iff query >= key (queries >= S carry lse = +inf -> 0)
+                e[j] = (mask && c0 + i < g) ? 0.f : e[j];
+                lastp = (last_col == i) ? e[j] : lastp;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kExpBatch; j += 4) {
+            s0 += e[j + 0];
+            s1 += e[j + 1];
+            s2 += e[j + 2];
+            s3 += e[j + 3];
+        }
     }
     colsum += (s0 + s1) + (s2 + s3);
 }
-__device__ __forceinline__ void pass2_half(const float (&v)[64], const float* ls, int c0, bool edge, int g, bool has_last,
-                                           int last_col, const Params& p, float& colsum, float& lastp) {
+__device__ __forceinline__ void pass2_half(const float (&v)[64], uint32_t ls, int c0, bool edge, int g, bool has_last,
+                                           int last_col, bool causal, float cs, float& colsum, float& lastp) {
     if (edge || has_last)
-        pass2_body<true>(v, ls, c0, edge && p.causal, g, has_last ? last_col : -1, p.cs, colsum, lastp);
+        pass2_body<true>(v, ls, c0, edge && causal, g, has_last ? last_col : -1, cs, colsum, lastp);
     else
-        pass2_body<false>(v, ls, c0, false, g, -1, p.cs, colsum, lastp);
+        pass2_body<false>(v, ls, c0, false, g, -1, cs, colsum, lastp);
 }
 
+// Position in a CTA's tile sequence (items in schedule order, each item's streamed tiles in order).
+template <int PASS>
+struct TileCursor {
+    int k;         // item index of this CTA
+    uint32_t n0;   // sequence number of the item's first tile
+    Item it;
+    __device__ __forceinline__ bool start(const Params& p) { k = 0; n0 = 0; return item_at<PASS>(p, 0, it); }
+    // move to the item that holds tile number gn (>= n0); false when the sequence ends before it
+    __device__ __forceinline__ bool seek(const Params& p, uint32_t gn) {
+        while (gn >= n0 + (uint32_t)(it.t1 - it.t0)) {
+            n0 += (uint32_t)(it.t1 - it.t0);
+            if (!item_at<PASS>(p, ++k, it)) return false;
+        }
+        return true;
+    }
+};
+
+// PASS 1 = row log-sum-exp, 2 = column sums; DBG compiles the timing-experiment switches of Params::dbg in
+template <int PASS, bool DBG>
 __global__ void __launch_bounds__(kThreads, 1)
 fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
                         const Params p) {
@@ -315,7 +372,6 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     const uint32_t bar_tfull = bar_empty + 8 * kStages, bar_tempty = bar_tfull + 8 * kAcc;
     static_assert(32 + 16 * kStages + 16 * kAcc <= 504, "barrier region overflow");
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 504);
-    float* lse_s = reinterpret_cast<float*>(gen + kLseOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -345,7 +401,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const CUtensorMap* str_map = p.pass == 1 ? &mapK : &mapQ;  // streamed operand, h0 and h1 parts in dim 3
+    const CUtensorMap* str_map = PASS == 1 ? &mapK : &mapQ;  // streamed operand, h0 and h1 parts in dim 3
     const int group = p.H / p.KVH;
     const int wg = warp >> 2;  // warpgroup: 0 control, 1-2 epilogue, 3 fixed-operand loaders
 
@@ -360,9 +416,9 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 uint32_t stage = 0, sphase = 0;
                 const uint32_t tile_tx = p.x3 ? kOperandBytes : kPartBytes;
                 Item it;
-                for (int k = 0; item_at(p, k, it); ++k) {
+                for (int k = 0; item_at<PASS>(p, k, it); ++k) {
                     const int b = it.bh / p.H, h = it.bh % p.H;
-                    const int str_idx = p.pass == 1 ? b * p.KVH + h / group : it.bh;
+                    const int str_idx = PASS == 1 ? b * p.KVH + h / group : it.bh;
                     for (int t = it.t0; t < it.t1; ++t) {
                         const uint32_t fb = bar_full + 8 * stage;
                         const uint32_t dst = ring_s + stage * kOperandBytes;
@@ -381,7 +437,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             {
                 uint32_t stage = 0, sphase = 0, acc = 0, aphase = 0;
                 Item it;
-                for (int k = 0; item_at(p, k, it); ++k) {
+                for (int k = 0; item_at<PASS>(p, k, it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
                     const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;
                     mbar_wait(bar_afull + 8 * ab, abphase);
@@ -393,7 +449,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         const uint32_t d = tmem_base + acc * kTile;
                         const uint32_t st0 = ring_s + stage * kOperandBytes;
                         if (elect_one()) {
-                            if (!(p.dbg & 2)) {
+                            if (!(DBG && (p.dbg & 2))) {
                                 // F = fixed operand (A, TMEM), T = streamed operand (B, shared memory); K = 16 per
                                 // instruction, 8 TMEM columns / 32 smem bytes per step
                                 const uint32_t s_h0 = st0, s_h1 = st0 + kPartBytes;
@@ -427,13 +483,13 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const int q4 = warp & 3;
         const int row = q4 * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
-        const uint4* f16 = p.pass == 1 ? p.q16 : p.k16;
-        const size_t fpart = p.pass == 1 ? p.q_part : p.k_part;
+        const uint4* f16 = PASS == 1 ? p.q16 : p.k16;
+        const size_t fpart = PASS == 1 ? p.q_part : p.k_part;
         Item it;
-        for (int k = 0; item_at(p, k, it); ++k) {
+        for (int k = 0; item_at<PASS>(p, k, it); ++k) {
             const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
             const int b = it.bh / p.H, h = it.bh % p.H;
-            const int fix_idx = p.pass == 1 ? it.bh : b * p.KVH + h / group;
+            const int fix_idx = PASS == 1 ? it.bh : b * p.KVH + h / group;
             const int g = it.blk * kTile + row;
             const uint4* src = f16 + ((size_t)fix_idx * p.S + (g < p.S ? g : 0)) * (kHd * 2 / 16);
             uint4 q[8];  // this row: 64 halfs = 128 B = 32 TMEM columns per part; h0 is fetched ahead of the wait
@@ -455,109 +511,139 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
     } else {
         reg_inc<200>();
-        // ===== epilogue: two groups of 4 warps; group g takes the tiles of parity g (counted over the
-        // whole CTA), tile n lives in TMEM accumulator n % 3; a thread owns one TMEM lane (tile
-        // row).  Each thread ping-pongs two 64-column register buffers: the tcgen05.ld of the next
-        // half tile is in flight while the exp2 loop runs on the current one, so TMEM reads
-        // (64 B/clk/SM) hide behind the MUFU work, and the third accumulator lets the MMA of tile
-        // n + 2 start before tile n has been read out.
+        // ===== epilogue: two groups of 4 warps; group g takes the tiles of parity g, counted over the
+        // CTA's whole tile sequence (item after item); tile n lives in TMEM accumulator n % 3; a
+        // thread owns one TMEM lane (tile row).  Every warp runs on its own: no block or group
+        // barrier anywhere, only the accumulator mbarriers.  The loop is software-pipelined across
+        // tiles AND items: while the exp2 loop runs on one 64-column half, the tcgen05.ld of the
+        // next half (or of the next tile's first half) is in flight, and the next tile's lse values
+        // (pass 2; each warp stages all 128 of them for itself) are on their way from L2.  When the
+        // sequence moves to another item the per-row partial results are flushed: pass 1 stores
+        // this group's (max, sum) pair, merged with the other group's by lse_combine_kernel; pass 2
+        // adds its column sum with one atomicAdd (two addends on a zeroed array: order-independent).
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
         const int grp = wg - 1;                     // tile parity of this group
         const int row = q4 * 32 + lane;
-        const int gt = threadIdx.x & 127;           // thread index inside the group
         const uint32_t tmem_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
-        float* lse_g = lse_s + grp * 2 * kTile;     // two lse buffers per group (pass 2)
-        uint32_t n = 0;                             // tiles seen by the CTA so far
-        Item it;
-        for (int k = 0; item_at(p, k, it); ++k) {
-            const int g = it.blk * kTile + row;     // global index of this thread's row
-            float m = -INFINITY, l = 0.f;           // pass 1
-            float colsum = 0.f, lastp = 0.f;        // pass 2
-            const int ntiles = it.t1 - it.t0;
-            int t = it.t0 + (int)((n ^ (uint32_t)grp) & 1u);  // first tile of this item that is mine
-            uint32_t gn = n + (uint32_t)(t - it.t0);          // its index in the CTA's tile sequence
-            n += (uint32_t)ntiles;
-            if (t < it.t1) {
-                float va[64], vb[64];
-                if (p.dbg & 4) {
+        const uint32_t lse_w = base + kLseOff + (uint32_t)(warp - 4) * (2u * kTile * 4u);  // two 128-float buffers per warp
+        const int S = p.S, dbg = DBG ? p.dbg : 0;
+        const bool causal = p.causal != 0;
+        const float cs = p.cs;
+        const float* __restrict__ lse2 = p.lse2;
+        const bool lse_vec = (S & 3) == 0;
+        const int last_tile = (S - 1) / kTile, last_col = (S - 1) % kTile;
+        float2* __restrict__ ml_g = p.ml + (size_t)grp * p.B * p.H * S;
+
+        auto flush = [&](const Item& fi, float m, float l, float colsum, float lastp, bool saw_last) {
+            const int g = fi.blk * kTile + row;
+            if (g >= S) return;
+            const size_t o = (size_t)fi.bh * S + g;
+            if (PASS == 1) {
+                ml_g[o] = make_float2(m, l);
+            } else {
+                if (colsum != 0.f) atomicAdd(p.part_col + o, colsum);
+                if (saw_last) p.part_last[o] = lastp;
+            }
+        };
+
+        TileCursor<PASS> nx;                              // runs one tile ahead of the tile being processed
+        uint32_t gn = (uint32_t)grp;
+        bool have = nx.start(p) && nx.seek(p, gn);
+        Item st_it;                                 // item whose partial results are in registers
+        int st_k = 0;
+        item_at<PASS>(p, 0, st_it);
+        float m = -INFINITY, l = 0.f;               // pass 1
+        float colsum = 0.f, lastp = 0.f;            // pass 2
+        bool saw_last = false;
+        float va[64], vb[64];
+        if (dbg & 4) {
 #pragma unroll
-                    for (int i = 0; i < 64; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
+            for (int i = 0; i < 64; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
+        }
+        uint32_t lb = 0;                            // lse buffer of the current tile
+        if (have) {
+            const int t = nx.it.t0 + (int)(gn - nx.n0);
+            if (PASS == 2) {
+                sts128(lse_w + 16u * lane, load_lse4(lse2 + (size_t)nx.it.bh * S, t * kTile + lane * 4, S, lse_vec));
+                __syncwarp();
+            }
+            const uint32_t a = gn % (uint32_t)kAcc;
+            mbar_wait(bar_tfull + 8 * a, (gn / (uint32_t)kAcc) & 1u);
+            tc_fence_after();
+            if (!(dbg & 4)) tc_ld64_issue(tmem_lane + a * kTile, va);
+            tc_ld_wait();
+        }
+        while (have) {
+            // ---- the tile being processed: number gn, described by nx (before it moves on)
+            const Item ci = nx.it;
+            const int ck = nx.k;
+            const int t = ci.t0 + (int)(gn - nx.n0);
+            const uint32_t a = gn % (uint32_t)kAcc;
+            const uint32_t cur_tmem = tmem_lane + a * kTile;
+            // ---- look one tile ahead and start fetching its lse values
+            const bool has_next = nx.seek(p, gn + 2u);
+            const int tn = has_next ? nx.it.t0 + (int)(gn + 2u - nx.n0) : 0;
+            float4 lse_nx = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (has_next && PASS == 2) lse_nx = load_lse4(lse2 + (size_t)nx.it.bh * S, tn * kTile + lane * 4, S, lse_vec);
+            // ---- entering a new item: flush what the registers hold (and empty results for items
+            // in which this group had no tile at all)
+            if (ck != st_k) {
+                flush(st_it, m, l, colsum, lastp, saw_last);
+                for (int kk = st_k + 1; kk < ck; ++kk) {
+                    Item e;
+                    item_at<PASS>(p, kk, e);
+                    flush(e, -INFINITY, 0.f, 0.f, 0.f, false);
                 }
-                uint32_t lb = 0;                    // lse buffer of the current tile
-                if (p.pass == 2) {
-                    const int qi = t * kTile + gt;
-                    lse_g[gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
-                }
-                uint32_t a = gn % (uint32_t)kAcc;   // accumulator of the current tile
-                uint32_t cur_tmem = tmem_lane + a * kTile;
-                mbar_wait(bar_tfull + 8 * a, (gn / (uint32_t)kAcc) & 1u);
-                tc_fence_after();
-                if (!(p.dbg & 4)) tc_ld64_issue(cur_tmem, va);
-                tc_ld_wait();
-                for (; t < it.t1; t += 2, gn += 2) {
-                    const bool edge = (p.causal && t == it.blk) || (t * kTile + kTile > p.S);
-                    const bool has_last = (p.S - 1) / kTile == t;
-                    const bool has_next = t + 2 < it.t1;
-                    const float* lse_t = lse_g + lb * kTile;
-                    if (p.pass == 2) group_bar(grp);          // this tile's lse values are in shared memory
-                    if (!(p.dbg & 4)) tc_ld64_issue(cur_tmem + 64, vb);  // second half in flight ...
-                    if (p.dbg & 1) { colsum += va[0] + va[63]; l += va[1]; }
-                    else if (p.pass == 1) pass1_half(va, t * kTile, edge, g, p, m, l);
-                    else pass2_half(va, lse_t, t * kTile, edge, g, has_last, (p.S - 1) % kTile, p, colsum, lastp);
-                    tc_ld_wait();                             // ... now in registers: accumulator is drained
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
-                    const uint32_t na = (gn + 2u) % (uint32_t)kAcc, nph = ((gn + 2u) / (uint32_t)kAcc) & 1u;
-                    const uint32_t nxt_tmem = tmem_lane + na * kTile;
-                    bool ready = false;
-                    if (has_next) {
-                        if (p.pass == 2) {
-                            const int qi = (t + 2) * kTile + gt;
-                            lse_g[(lb ^ 1u) * kTile + gt] = qi < p.S ? __ldg(p.lse2 + (size_t)it.bh * p.S + qi) : INFINITY;
-                        }
-                        ready = mbar_test(bar_tfull + 8 * na, nph);
-                        ready = __all_sync(0xffffffffu, ready);
-                        if (ready) {
-                            tc_fence_after();
-                            if (!(p.dbg & 4)) tc_ld64_issue(nxt_tmem, va);  // next tile's first half in flight ...
-                        }
-                    }
-                    if (p.dbg & 1) { colsum += vb[0] + vb[63]; l += vb[1]; }
-                    else if (p.pass == 1) pass1_half(vb, t * kTile + 64, edge, g, p, m, l);
-                    else pass2_half(vb, lse_t + 64, t * kTile + 64, edge, g, has_last, (p.S - 1) % kTile - 64, p, colsum, lastp);
-                    if (has_next) {
-                        if (!ready) {
-                            mbar_wait(bar_tfull + 8 * na, nph);
-                            tc_fence_after();
-                            if (!(p.dbg & 4)) tc_ld64_issue(nxt_tmem, va);
-                        }
-                        tc_ld_wait();                         // ... and landed
-                        lb ^= 1u;
-                        a = na;
-                        cur_tmem = nxt_tmem;
-                    }
+                m = -INFINITY; l = 0.f; colsum = 0.f; lastp = 0.f; saw_last = false;
+                st_it = ci;
+                st_k = ck;
+            }
+            const int g = ci.blk * kTile + row;     // global index of this thread's row
+            const bool edge = (causal && t == ci.blk) || (t * kTile + kTile > S);
+            const bool has_last = last_tile == t;
+            saw_last = saw_last || has_last;
+            const uint32_t lse_t = lse_w + lb * (kTile * 4u);
+
+            if (!(dbg & 4)) tc_ld64_issue(cur_tmem + 64, vb);  // second half in flight ...
+            if (dbg & 1) { colsum += va[0] + va[63]; l += va[1]; }
+            else if (PASS == 1) pass1_half(va, t * kTile, edge, g, S, causal, cs, m, l);
+            else pass2_half(va, lse_t, t * kTile, edge, g, has_last, last_col, causal, cs, colsum, lastp);
+            tc_ld_wait();                             // ... now in registers: accumulator is drained
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
+            const uint32_t na = (gn + 2u) % (uint32_t)kAcc, nph = ((gn + 2u) / (uint32_t)kAcc) & 1u;
+            bool ready = false;
+            if (has_next) {
+                if (PASS == 2) sts128(lse_w + (lb ^ 1u) * (kTile * 4u) + 16u * lane, lse_nx);
+                ready = mbar_test(bar_tfull + 8 * na, nph);
+                ready = __all_sync(0xffffffffu, ready);
+                if (ready) {
+                    tc_fence_after();
+                    if (!(dbg & 4)) tc_ld64_issue(tmem_lane + na * kTile, va);  // next tile's first half in flight ...
                 }
             }
-            // combine the two groups' partial results of every row through shared memory
-            float2* xch = reinterpret_cast<float2*>(gen + kXchOff);
-            if (grp == 1) xch[row] = p.pass == 1 ? make_float2(m, l) : make_float2(colsum, lastp);
-            asm volatile("bar.sync 3, 256;" ::: "memory");
-            if (grp == 0 && g < p.S) {
-                const float2 o2 = xch[row];
-                const size_t o = (size_t)it.bh * p.S + g;
-                if (p.pass == 1) {
-                    // at least one group saw a valid column (column 0 of the row block), so mm is finite
-                    const float mm = fmaxf(m, o2.x);
-                    const float la = m > -INFINITY ? l * ex2(m - mm) : 0.f;
-                    const float lb2 = o2.x > -INFINITY ? o2.y * ex2(o2.x - mm) : 0.f;
-                    p.lse2[o] = mm + log2f(la + lb2);
-                } else {
-                    p.part_col[o] = colsum + o2.x;
-                    p.part_last[o] = lastp + o2.y;
+            if (dbg & 1) { colsum += vb[0] + vb[63]; l += vb[1]; }
+            else if (PASS == 1) pass1_half(vb, t * kTile + 64, edge, g, S, causal, cs, m, l);
+            else pass2_half(vb, lse_t + 256u, t * kTile + 64, edge, g, has_last, last_col - 64, causal, cs, colsum, lastp);
+            if (has_next) {
+                if (!ready) {
+                    mbar_wait(bar_tfull + 8 * na, nph);
+                    tc_fence_after();
+                    if (!(dbg & 4)) tc_ld64_issue(tmem_lane + na * kTile, va);
                 }
+                tc_ld_wait();                         // ... and landed
+                __syncwarp();                         // the lse values staged by the other lanes are visible
+                lb ^= 1u;
+                gn += 2u;
             }
-            asm volatile("bar.sync 3, 256;" ::: "memory");
+            have = has_next;
+        }
+        // ---- end of the sequence: flush the last item and empty results for the rest
+        flush(st_it, m, l, colsum, lastp, saw_last);
+        {
+            Item e;
+            for (int kk = st_k + 1; item_at<PASS>(p, kk, e); ++kk) flush(e, -INFINITY, 0.f, 0.f, 0.f, false);
         }
     }
 
@@ -606,6 +692,19 @@ split_f16_kernel(const float* __restrict__ x, long long sb, long long sh, long l
             o1[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
         }
     }
+}
+
+// pass 1 leaves one (max, sum) pair per epilogue group and row; merge them into the log2-domain lse
+__global__ void __launch_bounds__(256)
+lse_combine_kernel(const float2* __restrict__ ml, size_t n, float* __restrict__ lse2) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float2 a = ml[i], b = ml[n + i];
+    // every row has at least one valid column (key 0), so the larger max is finite
+    const float mm = fmaxf(a.x, b.x);
+    const float la = a.x > -INFINITY ? a.y * exp2f(a.x - mm) : 0.f;
+    const float lb = b.x > -INFINITY ? b.y * exp2f(b.x - mm) : 0.f;
+    lse2[i] = mm + log2f(la + lb);
 }
 
 struct HeadW {
@@ -721,14 +820,14 @@ static int make_map(CUtensorMap* map, void* base, int S, long long n, size_t par
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
 
 struct WsLayout {
-    size_t q0, q1, k0, k1, lse, pcol, plast, total;  // fp16 h0 / h1 parts of Q and K, then per-(b,h,s) floats
+    size_t q0, q1, k0, k1, lse, pcol, plast, ml, total;  // fp16 h0 / h1 parts of Q and K, then per-(b,h,s) floats
 };
 static WsLayout ws_layout(int B, int H, int KVH, int S) {
     WsLayout w;
     const size_t q = align256((size_t)B * H * S * kHd * 2), k = align256((size_t)B * KVH * S * kHd * 2);
     const size_t v = align256((size_t)B * H * S * 4);
     w.q0 = 0; w.q1 = q; w.k0 = 2 * q; w.k1 = 2 * q + k;
-    w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + v; w.total = w.plast + v;
+    w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + v; w.ml = w.plast + v; w.total = w.ml + 4 * v;
     return w;
 }
 
@@ -806,6 +905,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     p.dbg = dbg;
     p.cs = scaling * 1.4426950408889634f;
     p.lse2 = (float*)(w8 + wl.lse);
+    p.ml = (float2*)(w8 + wl.ml);
     p.part_col = (float*)(w8 + wl.pcol);
     p.part_last = (float*)(w8 + wl.plast);
     p.q16 = (const uint4*)(w8 + wl.q0); p.k16 = (const uint4*)(w8 + wl.k0);
@@ -816,16 +916,24 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     SPLITQ_CUDA(cudaGetDevice(&dev));
     SPLITQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (dev < 64 && !attr_set[dev]) {
-        SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set[dev] = true;
     }
     const long long items = (long long)B * H * p.nb;
+    SPLITQ_REQUIRE(items < (1ll << 31), SPLITQ_ERR_ARG, "importance_fused: B*H*ceil(S/128)=%lld does not fit 31 bits", items);
     const int grid = (int)std::min<long long>(items, sms);
-    for (int pass = 1; pass <= 2; ++pass) {
-        p.pass = pass;
-        fused_importance_kernel<<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
-        SPLITQ_LAUNCH_CHECK("fused_importance_kernel");
-    }
+    const size_t rows = (size_t)B * H * S;
+    if (dbg) fused_importance_kernel<1, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+    else fused_importance_kernel<1, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+    SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 1)");
+    lse_combine_kernel<<<(unsigned)cdiv((long long)rows, 256), 256, 0, st>>>(p.ml, rows, p.lse2);
+    SPLITQ_CUDA(cudaMemsetAsync(p.part_col, 0, rows * sizeof(float), st));
+    if (dbg) fused_importance_kernel<2, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+    else fused_importance_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+    SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 2)");
     HeadW hw;
     for (int h = 0; h < H; ++h) hw.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
     dim3 fg(cdiv(S, 256), B);
