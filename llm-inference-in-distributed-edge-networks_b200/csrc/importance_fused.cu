@@ -172,43 +172,83 @@ struct Params {
     int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
     int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads (timing experiments only)
     float cs;          // scaling * log2(e)
-    float2* ml;        // (2 groups,B,H,S) pass-1 partial (max, sum) of each epilogue group
+    int tiles;         // tiles of one pass = B * H * tiles_per_bh
+    float2* ml;        // (kSlots,B,H,S) pass-1 partial (max, sum) per result slot, pre-set to (-inf, 0)
     float* lse2;       // (B,H,S) log2-domain log-sum-exp (lse_combine_kernel)
-    float* part_col;   // (B,H,S) sum_i p[i][j]
+    float* part_col;   // (kSlots,B,H,S) partial sum_i p[i][j] per result slot, pre-set to 0
     float* part_last;  // (B,H,S) p[S-1][j]
     const uint4 *q16, *k16;  // dense (n,S,64) fp16 h0 part; the h1 part follows at +q_part / +k_part uint4
     size_t q_part, k_part;
 };
 
-// Static schedule shared by all warp roles: items ranked by cost (tiles), dealt serpentine.
-struct Item {
-    int bh, blk, t0, t1;  // streamed block range [t0, t1)
+// ---- schedule, shared by all warp roles --------------------------------------------------------
+// The tiles of one pass form ONE sequence: (b,h) by (b,h), inside it item by item (an item = one
+// fixed 128-row block: a query block in pass 1, a key block in pass 2), inside an item the streamed
+// blocks in order.  CTA c takes the contiguous range [c*T/G, (c+1)*T/G): every CTA gets the same
+// number of tiles (+-1) whatever the causal triangle looks like, neighbouring CTAs stream the same
+// (b,h) operands (L2), and an item is cut at most once (G is chosen so that a range is at least as
+// long as the longest item).  The two pieces of a cut item, and the two epilogue groups inside a
+// piece, put their partial results into kSlots = 4 separate slots that are merged in a fixed order
+// afterwards, so the result does not depend on the schedule's timing.
+constexpr int kSlots = 4;
+struct Seg {
+    int bh, blk, ta, tb;  // streamed blocks [ta, tb) of item (bh, blk)
+    int part;             // 1 if an earlier CTA holds the first streamed blocks of this item
 };
 template <int PASS>
-__device__ __forceinline__ bool item_at(const Params& p, int k, Item& it) {
-    // Rank r of the k-th item of this CTA.  Items are ordered window by window (so that the CTAs
-    // running at any moment stream one window's operands and those stay in L2), inside a window by
-    // cost (number of streamed tiles, largest first), and dealt to CTAs in serpentine order.
-    const uint32_t G = gridDim.x, c = blockIdx.x;
-    const uint32_t total = (uint32_t)p.B * p.H * p.nb;  // < 2^31, checked on the host
-    const uint32_t r = (uint32_t)k * G + ((k & 1) ? (G - 1 - c) : c);
-    if (r >= total) return false;
-    const uint32_t per_window = (uint32_t)p.H * p.nb;
-    const uint32_t b = r / per_window;
-    const uint32_t q = r - b * per_window;
-    const uint32_t rank = q / (uint32_t)p.H;
-    it.bh = (int)(b * p.H + (q - rank * p.H));
-    if (PASS == 1) {
-        it.blk = p.nb - 1 - (int)rank;  // most key blocks first
-        it.t0 = 0;
-        it.t1 = p.causal ? it.blk + 1 : p.nb;
-    } else {
-        it.blk = (int)rank;        // most query blocks first
-        it.t0 = p.causal ? it.blk : 0;
-        it.t1 = p.nb;
+struct SegIter {
+    int bh, blk, t, rem, nb;
+    bool causal;
+    __device__ __forceinline__ int t0(int b) const { return PASS == 1 ? 0 : (causal ? b : 0); }
+    __device__ __forceinline__ int t1(int b) const { return PASS == 1 ? (causal ? b + 1 : nb) : nb; }
+    __device__ __forceinline__ void next_item() {
+        if (++blk == nb) { blk = 0; ++bh; }
     }
-    return true;
-}
+    // position on the n-th tile (n >= 0) of this CTA's range
+    __device__ __forceinline__ void init(const Params& p, int n) {
+        nb = p.nb;
+        causal = p.causal != 0;
+        const long long T = p.tiles;
+        const int lo = (int)(T * blockIdx.x / gridDim.x), hi = (int)(T * (blockIdx.x + 1) / gridDim.x);
+        rem = hi - lo - n;
+        const int per_bh = causal ? nb * (nb + 1) / 2 : nb * nb;
+        const int x = lo + n;
+        bh = x / per_bh;
+        int y = x - bh * per_bh;
+        blk = 0;
+        while (y >= t1(blk) - t0(blk)) {
+            y -= t1(blk) - t0(blk);
+            ++blk;
+        }
+        t = t0(blk) + y;
+    }
+    // the next run of tiles inside one item; false when the range is used up
+    __device__ __forceinline__ bool next(Seg& s) {
+        if (rem <= 0) return false;
+        const int e = t1(blk);
+        const int take = min(e - t, rem);
+        s.bh = bh; s.blk = blk; s.ta = t; s.tb = t + take;
+        s.part = t != t0(blk);
+        rem -= take;
+        if (s.tb == e) { next_item(); t = t0(blk); }
+        else t = s.tb;
+        return true;
+    }
+    // tile-wise use (epilogue): the current tile is (bh, blk, t); move n tiles on inside the range
+    __device__ __forceinline__ bool valid() const { return rem > 0; }
+    __device__ __forceinline__ void advance(int n) {
+        rem -= n;
+        t += n;
+        if (rem <= 0) return;
+        int e = t1(blk);
+        while (t >= e) {
+            const int carry = t - e;
+            next_item();
+            t = t0(blk) + carry;
+            e = t1(blk);
+        }
+    }
+};
 
 // ---- epilogue building blocks -------------------------------------------------------------------
 // 64 consecutive columns of this thread's TMEM lane; asynchronous until tc_ld_wait()
@@ -339,23 +379,6 @@ __device__ __forceinline__ void pass2_half(const float (&v)[64], uint32_t ls, in
         pass2_body<false>(v, ls, c0, false, g, -1, cs, colsum, lastp);
 }
 
-// Position in a CTA's tile sequence (items in schedule order, each item's streamed tiles in order).
-template <int PASS>
-struct TileCursor {
-    int k;         // item index of this CTA
-    uint32_t n0;   // sequence number of the item's first tile
-    Item it;
-    __device__ __forceinline__ bool start(const Params& p) { k = 0; n0 = 0; return item_at<PASS>(p, 0, it); }
-    // move to the item that holds tile number gn (>= n0); false when the sequence ends before it
-    __device__ __forceinline__ bool seek(const Params& p, uint32_t gn) {
-        while (gn >= n0 + (uint32_t)(it.t1 - it.t0)) {
-            n0 += (uint32_t)(it.t1 - it.t0);
-            if (!item_at<PASS>(p, ++k, it)) return false;
-        }
-        return true;
-    }
-};
-
 // PASS 1 = row log-sum-exp, 2 = column sums; DBG compiles the timing-experiment switches of Params::dbg in
 template <int PASS, bool DBG>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -415,11 +438,13 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             {
                 uint32_t stage = 0, sphase = 0;
                 const uint32_t tile_tx = p.x3 ? kOperandBytes : kPartBytes;
-                Item it;
-                for (int k = 0; item_at<PASS>(p, k, it); ++k) {
+                SegIter<PASS> si;
+                si.init(p, 0);
+                Seg it;
+                while (si.next(it)) {
                     const int b = it.bh / p.H, h = it.bh % p.H;
                     const int str_idx = PASS == 1 ? b * p.KVH + h / group : it.bh;
-                    for (int t = it.t0; t < it.t1; ++t) {
+                    for (int t = it.ta; t < it.tb; ++t) {
                         const uint32_t fb = bar_full + 8 * stage;
                         const uint32_t dst = ring_s + stage * kOperandBytes;
                         mbar_wait(bar_empty + 8 * stage, sphase ^ 1);
@@ -436,13 +461,15 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             // ===== MMA issuer: A (fixed operand) from TMEM, B (streamed slab) from shared memory =====
             {
                 uint32_t stage = 0, sphase = 0, acc = 0, aphase = 0;
-                Item it;
-                for (int k = 0; item_at<PASS>(p, k, it); ++k) {
+                SegIter<PASS> si;
+                si.init(p, 0);
+                Seg it;
+                for (int k = 0; si.next(it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
                     const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;
                     mbar_wait(bar_afull + 8 * ab, abphase);
                     tc_fence_after();
-                    for (int t = it.t0; t < it.t1; ++t) {
+                    for (int t = it.ta; t < it.tb; ++t) {
                         mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
                         mbar_wait(bar_full + 8 * stage, sphase);
                         tc_fence_after();
@@ -485,8 +512,10 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         const uint4* f16 = PASS == 1 ? p.q16 : p.k16;
         const size_t fpart = PASS == 1 ? p.q_part : p.k_part;
-        Item it;
-        for (int k = 0; item_at<PASS>(p, k, it); ++k) {
+        SegIter<PASS> si;
+        si.init(p, 0);
+        Seg it;
+        for (int k = 0; si.next(it); ++k) {
             const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
             const int b = it.bh / p.H, h = it.bh % p.H;
             const int fix_idx = PASS == 1 ? it.bh : b * p.KVH + h / group;
@@ -511,16 +540,14 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
     } else {
         reg_inc<200>();
-        // ===== epilogue: two groups of 4 warps; group g takes the tiles of parity g, counted over the
-        // CTA's whole tile sequence (item after item); tile n lives in TMEM accumulator n % 3; a
-        // thread owns one TMEM lane (tile row).  Every warp runs on its own: no block or group
-        // barrier anywhere, only the accumulator mbarriers.  The loop is software-pipelined across
-        // tiles AND items: while the exp2 loop runs on one 64-column half, the tcgen05.ld of the
-        // next half (or of the next tile's first half) is in flight, and the next tile's lse values
-        // (pass 2; each warp stages all 128 of them for itself) are on their way from L2.  When the
-        // sequence moves to another item the per-row partial results are flushed: pass 1 stores
-        // this group's (max, sum) pair, merged with the other group's by lse_combine_kernel; pass 2
-        // adds its column sum with one atomicAdd (two addends on a zeroed array: order-independent).
+        // ===== epilogue: two groups of 4 warps; group g takes the tiles of parity g of the CTA's
+        // range, tile n lives in TMEM accumulator n % 3; a thread owns one TMEM lane (tile row).
+        // Every warp runs on its own: no block or group barrier anywhere, only the accumulator
+        // mbarriers.  The loop is software-pipelined across tiles AND items: while the exp2 loop
+        // runs on one 64-column half, the tcgen05.ld of the next half (or of the next tile's first
+        // half) is in flight, and the next tile's lse values (pass 2; each warp stages all 128 of
+        // them for itself) are on their way from L2.  When the sequence moves to another item the
+        // per-row partial results are stored to this (piece, group) slot.
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
         const int grp = wg - 1;                     // tile parity of this group
         const int row = q4 * 32 + lane;
@@ -532,39 +559,42 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const float* __restrict__ lse2 = p.lse2;
         const bool lse_vec = (S & 3) == 0;
         const int last_tile = (S - 1) / kTile, last_col = (S - 1) % kTile;
-        float2* __restrict__ ml_g = p.ml + (size_t)grp * p.B * p.H * S;
+        const size_t rows = (size_t)p.B * p.H * S;
 
-        auto flush = [&](const Item& fi, float m, float l, float colsum, float lastp, bool saw_last) {
-            const int g = fi.blk * kTile + row;
-            if (g >= S) return;
-            const size_t o = (size_t)fi.bh * S + g;
+        SegIter<PASS> nx;                           // runs one tile ahead of the tile being processed
+        nx.init(p, 0);
+        const int first_bh = nx.bh, first_blk = nx.blk;
+        const int first_part = nx.t != nx.t0(nx.blk);  // the range starts inside an item
+        nx.advance(grp);
+        uint32_t gn = (uint32_t)grp;                // number of the tile inside the CTA's range
+        int st_bh = -1, st_blk = 0;                 // item whose partial results are in registers
+        float m = -INFINITY, l = 0.f;               // pass 1
+        float colsum = 0.f, lastp = 0.f;            // pass 2
+        bool saw_last = false;
+
+        auto flush = [&]() {
+            const int g = st_blk * kTile + row;
+            if (st_bh < 0 || g >= S) return;
+            const int slot = ((st_bh == first_bh && st_blk == first_blk) ? first_part * 2 : 0) + grp;
+            const size_t o = (size_t)st_bh * S + g;
             if (PASS == 1) {
-                ml_g[o] = make_float2(m, l);
+                p.ml[slot * rows + o] = make_float2(m, l);
             } else {
-                if (colsum != 0.f) atomicAdd(p.part_col + o, colsum);
+                p.part_col[slot * rows + o] = colsum;
                 if (saw_last) p.part_last[o] = lastp;
             }
         };
 
-        TileCursor<PASS> nx;                              // runs one tile ahead of the tile being processed
-        uint32_t gn = (uint32_t)grp;
-        bool have = nx.start(p) && nx.seek(p, gn);
-        Item st_it;                                 // item whose partial results are in registers
-        int st_k = 0;
-        item_at<PASS>(p, 0, st_it);
-        float m = -INFINITY, l = 0.f;               // pass 1
-        float colsum = 0.f, lastp = 0.f;            // pass 2
-        bool saw_last = false;
         float va[64], vb[64];
         if (dbg & 4) {
 #pragma unroll
             for (int i = 0; i < 64; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
         }
         uint32_t lb = 0;                            // lse buffer of the current tile
+        bool have = nx.valid();
         if (have) {
-            const int t = nx.it.t0 + (int)(gn - nx.n0);
             if (PASS == 2) {
-                sts128(lse_w + 16u * lane, load_lse4(lse2 + (size_t)nx.it.bh * S, t * kTile + lane * 4, S, lse_vec));
+                sts128(lse_w + 16u * lane, load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec));
                 __syncwarp();
             }
             const uint32_t a = gn % (uint32_t)kAcc;
@@ -574,32 +604,24 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             tc_ld_wait();
         }
         while (have) {
-            // ---- the tile being processed: number gn, described by nx (before it moves on)
-            const Item ci = nx.it;
-            const int ck = nx.k;
-            const int t = ci.t0 + (int)(gn - nx.n0);
+            // ---- the tile being processed: number gn = (bh, blk, t), where nx stands before it moves on
+            const int bh = nx.bh, blk = nx.blk, t = nx.t;
             const uint32_t a = gn % (uint32_t)kAcc;
             const uint32_t cur_tmem = tmem_lane + a * kTile;
             // ---- look one tile ahead and start fetching its lse values
-            const bool has_next = nx.seek(p, gn + 2u);
-            const int tn = has_next ? nx.it.t0 + (int)(gn + 2u - nx.n0) : 0;
+            nx.advance(2);
+            const bool has_next = nx.valid();
             float4 lse_nx = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (has_next && PASS == 2) lse_nx = load_lse4(lse2 + (size_t)nx.it.bh * S, tn * kTile + lane * 4, S, lse_vec);
-            // ---- entering a new item: flush what the registers hold (and empty results for items
-            // in which this group had no tile at all)
-            if (ck != st_k) {
-                flush(st_it, m, l, colsum, lastp, saw_last);
-                for (int kk = st_k + 1; kk < ck; ++kk) {
-                    Item e;
-                    item_at<PASS>(p, kk, e);
-                    flush(e, -INFINITY, 0.f, 0.f, 0.f, false);
-                }
+            if (PASS == 2 && has_next) lse_nx = load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec);
+            // ---- entering a new item: store what the registers hold
+            if (bh != st_bh || blk != st_blk) {
+                flush();
                 m = -INFINITY; l = 0.f; colsum = 0.f; lastp = 0.f; saw_last = false;
-                st_it = ci;
-                st_k = ck;
+                st_bh = bh;
+                st_blk = blk;
             }
-            const int g = ci.blk * kTile + row;     // global index of this thread's row
-            const bool edge = (causal && t == ci.blk) || (t * kTile + kTile > S);
+            const int g = blk * kTile + row;        // global index of this thread's row
+            const bool edge = (causal && t == blk) || (t * kTile + kTile > S);
             const bool has_last = last_tile == t;
             saw_last = saw_last || has_last;
             const uint32_t lse_t = lse_w + lb * (kTile * 4u);
@@ -639,12 +661,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             }
             have = has_next;
         }
-        // ---- end of the sequence: flush the last item and empty results for the rest
-        flush(st_it, m, l, colsum, lastp, saw_last);
-        {
-            Item e;
-            for (int kk = st_k + 1; item_at<PASS>(p, kk, e); ++kk) flush(e, -INFINITY, 0.f, 0.f, 0.f, false);
-        }
+        flush();
     }
 
     tc_fence_before();
@@ -659,7 +676,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
 // (b,h,s) strides into dense (n, S, 64) fp16 arrays (one 128-byte row per token) ----
 __global__ void __launch_bounds__(256)
 split_f16_kernel(const float* __restrict__ x, long long sb, long long sh, long long ss, int heads, int S,
-                 uint2* __restrict__ h0, uint2* __restrict__ h1, int vec) {
+                 uint2* __restrict__ h0, uint2* __restrict__ h1, int vec, float2* __restrict__ ml,
+                 float* __restrict__ part_col, size_t rows) {
     // grid.y = b * heads + h (one division per CTA); grid.x strides over the S*16 float4 of that
     // head, 4 per thread with 256-thread spacing so every warp access is contiguous
     const int bh = blockIdx.y;
@@ -690,36 +708,54 @@ split_f16_kernel(const float* __restrict__ x, long long sb, long long sh, long l
             const __half2 l23 = __floats2half2_rn(v[u].z - f23.x, v[u].w - f23.y);
             o0[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a01), *reinterpret_cast<const uint32_t*>(&a23));
             o1[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
+            if (ml && (i & 15) == 0) {  // the Q launch also presets the result slots of its (b,h,s) row
+                const size_t r = (size_t)bh * S + (i >> 4);
+#pragma unroll
+                for (int sl = 0; sl < kSlots; ++sl) {
+                    ml[sl * rows + r] = make_float2(-INFINITY, 0.f);
+                    part_col[sl * rows + r] = 0.f;
+                }
+            }
         }
     }
 }
 
-// pass 1 leaves one (max, sum) pair per epilogue group and row; merge them into the log2-domain lse
+// pass 1 leaves up to kSlots (max, sum) pairs per row (two pieces of a cut item x two epilogue
+// groups; unused slots hold (-inf, 0)); merge them in slot order into the log2-domain lse
 __global__ void __launch_bounds__(256)
 lse_combine_kernel(const float2* __restrict__ ml, size_t n, float* __restrict__ lse2) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const float2 a = ml[i], b = ml[n + i];
-    // every row has at least one valid column (key 0), so the larger max is finite
-    const float mm = fmaxf(a.x, b.x);
-    const float la = a.x > -INFINITY ? a.y * exp2f(a.x - mm) : 0.f;
-    const float lb = b.x > -INFINITY ? b.y * exp2f(b.x - mm) : 0.f;
-    lse2[i] = mm + log2f(la + lb);
+    float2 v[kSlots];
+    float mm = -INFINITY;
+#pragma unroll
+    for (int sl = 0; sl < kSlots; ++sl) {
+        v[sl] = ml[sl * n + i];
+        mm = fmaxf(mm, v[sl].x);
+    }
+    // every row has at least one valid column (key 0), so the largest max is finite
+    float sum = 0.f;
+#pragma unroll
+    for (int sl = 0; sl < kSlots; ++sl) sum += v[sl].x > -INFINITY ? v[sl].y * exp2f(v[sl].x - mm) : 0.f;
+    lse2[i] = mm + log2f(sum);
 }
 
 struct HeadW {
     float w[SPLITQ_MAX_HEADS];
 };
 __global__ void __launch_bounds__(256)
-fused_finalize_kernel(const float* __restrict__ part_col, const float* __restrict__ part_last, int H, int S, HeadW hw,
-                      float* __restrict__ out_col, float* __restrict__ out_last) {
+fused_finalize_kernel(const float* __restrict__ part_col, const float* __restrict__ part_last, size_t rows, int H, int S,
+                      HeadW hw, float* __restrict__ out_col, float* __restrict__ out_last) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int b = blockIdx.y;
     if (j >= S) return;
     float c = 0.f, l = 0.f;
     for (int h = 0; h < H; ++h) {
         const size_t o = ((size_t)b * H + h) * S + j;
-        c += hw.w[h] * part_col[o];
+        float pc = 0.f;
+#pragma unroll
+        for (int sl = 0; sl < kSlots; ++sl) pc += part_col[sl * rows + o];  // fixed order: schedule-independent
+        c += hw.w[h] * pc;
         l += hw.w[h] * part_last[o];
     }
     if (out_col) out_col[(size_t)b * S + j] = c / (float)S;
@@ -827,7 +863,8 @@ static WsLayout ws_layout(int B, int H, int KVH, int S) {
     const size_t q = align256((size_t)B * H * S * kHd * 2), k = align256((size_t)B * KVH * S * kHd * 2);
     const size_t v = align256((size_t)B * H * S * 4);
     w.q0 = 0; w.q1 = q; w.k0 = 2 * q; w.k1 = 2 * q + k;
-    w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + v; w.ml = w.plast + v; w.total = w.ml + 4 * v;
+    w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + kSlots * v; w.ml = w.plast + v;
+    w.total = w.ml + 2 * kSlots * v;
     return w;
 }
 
@@ -887,9 +924,11 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
         SPLITQ_REQUIRE((long long)B * H <= 65535, SPLITQ_ERR_ARG, "importance_fused: B*H=%lld > 65535", (long long)B * H);
         const unsigned gx = (unsigned)cdiv((long long)S * (kHd / 4), 256 * 4);
         split_f16_kernel<<<dim3(gx, B * H), 256, 0, st>>>(Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S,
-                                                       (uint2*)(w8 + wl.q0), (uint2*)(w8 + wl.q1), vec_ok(Q, q_strides_host));
+                                                       (uint2*)(w8 + wl.q0), (uint2*)(w8 + wl.q1), vec_ok(Q, q_strides_host),
+                                                       (float2*)(w8 + wl.ml), (float*)(w8 + wl.pcol), (size_t)B * H * S);
         split_f16_kernel<<<dim3(gx, B * KVH), 256, 0, st>>>(K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH, S,
-                                                         (uint2*)(w8 + wl.k0), (uint2*)(w8 + wl.k1), vec_ok(K, k_strides_host));
+                                                         (uint2*)(w8 + wl.k0), (uint2*)(w8 + wl.k1), vec_ok(K, k_strides_host),
+                                                         nullptr, nullptr, 0);
         SPLITQ_LAUNCH_CHECK("split_f16_kernel");
     }
 
@@ -922,22 +961,24 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
         SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set[dev] = true;
     }
-    const long long items = (long long)B * H * p.nb;
-    SPLITQ_REQUIRE(items < (1ll << 31), SPLITQ_ERR_ARG, "importance_fused: B*H*ceil(S/128)=%lld does not fit 31 bits", items);
-    const int grid = (int)std::min<long long>(items, sms);
+    const long long per_bh = p.causal ? (long long)p.nb * (p.nb + 1) / 2 : (long long)p.nb * p.nb;
+    const long long tiles = (long long)B * H * per_bh;
+    SPLITQ_REQUIRE(tiles < (1ll << 31), SPLITQ_ERR_ARG, "importance_fused: %lld tiles per pass do not fit 31 bits", tiles);
+    p.tiles = (int)tiles;
+    // every CTA's range is at least as long as the longest item (nb tiles), so an item is cut at most once
+    const int grid = (int)std::max<long long>(1, std::min<long long>(sms, tiles / p.nb));
     const size_t rows = (size_t)B * H * S;
     if (dbg) fused_importance_kernel<1, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     else fused_importance_kernel<1, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 1)");
     lse_combine_kernel<<<(unsigned)cdiv((long long)rows, 256), 256, 0, st>>>(p.ml, rows, p.lse2);
-    SPLITQ_CUDA(cudaMemsetAsync(p.part_col, 0, rows * sizeof(float), st));
     if (dbg) fused_importance_kernel<2, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     else fused_importance_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 2)");
     HeadW hw;
     for (int h = 0; h < H; ++h) hw.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
     dim3 fg(cdiv(S, 256), B);
-    fused_finalize_kernel<<<fg, 256, 0, st>>>(p.part_col, p.part_last, H, S, hw, out_col, out_last);
+    fused_finalize_kernel<<<fg, 256, 0, st>>>(p.part_col, p.part_last, rows, H, S, hw, out_col, out_last);
     SPLITQ_LAUNCH_CHECK("fused_finalize_kernel");
     return SPLITQ_OK;
 }
