@@ -159,7 +159,6 @@ __device__ __forceinline__ float ex2_ordered(float x) {
 }
 #endif
 constexpr int kExpBatch = 16;
-
 // K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {64 fp16, 128 rows} TMA box writes)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libsplitq.so")
+# SPLITQ_LIB points at another build of the same library (kernel-variant experiments)
+LIB_PATH = os.environ.get("SPLITQ_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libsplitq.so")
 
 OK = 0
 SCALE_GROUP, SCALE_TOKEN = 0, 1
