@@ -15,3 +15,6 @@ def t(mode,n=10):
     return a.elapsed_time(b)/n
 for name,mode in [("x3",0),("x1",1),("x3 nomath",16),("x1 nomath",17),("x3 nomma",32),("x1 nomma",33),("x3 nomath nomma",48),("x1 nomath nomma",49),("x3 nomma noload",96),("x3 noload",64)]:
     print(f"{name:18s} {t(mode):.3f} ms")
+
+if len(sys.argv) > 3:  # cycle accounting printed by the kernel (debug instantiation)
+    splitq.importance_fused(q,k,0.125,mode=int(sys.argv[3])); torch.cuda.synchronize()

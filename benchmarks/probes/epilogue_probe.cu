@@ -1,0 +1,130 @@
+// Microbenchmark: the K2 epilogue math bodies alone (no TMEM, no barriers, no bookkeeping), as the
+// kernel runs them: 2 warps per sub-partition, two 64-float register buffers per thread.
+// Prints clocks per warp-level EX2 per sub-partition (pipe floor: 8).
+// Build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o epilogue_probe epilogue_probe.cu
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+__device__ __forceinline__ float ex2_ordered(float x) {
+    float y;
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+constexpr int EB = 16;
+
+template <int NC>
+__device__ __forceinline__ void pass1_chunk(float (&v)[NC], float cs, float& m, float& l) {
+    float cm0 = v[0], cm1 = v[1];
+#pragma unroll
+    for (int i = 2; i < NC; i += 2) {
+        cm0 = fmaxf(cm0, v[i]);
+        cm1 = fmaxf(cm1, v[i + 1]);
+    }
+    const float cm = fmaxf(cm0, cm1) * cs;
+    if (cm > -CUDART_INF_F) {
+        const float mn = fmaxf(m, cm);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int i0 = 0; i0 < NC; i0 += EB) {
+            float e[EB];
+#pragma unroll
+            for (int j = 0; j < EB; ++j) e[j] = ex2_ordered(fmaf(v[i0 + j], cs, -mn));
+#pragma unroll
+            for (int j = 0; j < EB; j += 4) {
+                s0 += e[j + 0]; s1 += e[j + 1]; s2 += e[j + 2]; s3 += e[j + 3];
+            }
+        }
+        l = l * ex2(m - mn) + ((s0 + s1) + (s2 + s3));
+        m = mn;
+    }
+}
+template <int NC>
+__device__ __forceinline__ void pass2_chunk(const float (&v)[NC], uint32_t ls, float cs, float& colsum) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int i0 = 0; i0 < NC; i0 += EB) {
+        float e[EB];
+#pragma unroll
+        for (int j = 0; j < EB; j += 4) {
+            const float4 ls4 = lds128(ls + 4u * (i0 + j));
+            e[j + 0] = ex2_ordered(fmaf(v[i0 + j + 0], cs, -ls4.x));
+            e[j + 1] = ex2_ordered(fmaf(v[i0 + j + 1], cs, -ls4.y));
+            e[j + 2] = ex2_ordered(fmaf(v[i0 + j + 2], cs, -ls4.z));
+            e[j + 3] = ex2_ordered(fmaf(v[i0 + j + 3], cs, -ls4.w));
+        }
+#pragma unroll
+        for (int j = 0; j < EB; j += 4) {
+            s0 += e[j + 0]; s1 += e[j + 1]; s2 += e[j + 2]; s3 += e[j + 3];
+        }
+    }
+    colsum += (s0 + s1) + (s2 + s3);
+}
+
+// GAP = number of dependent integer instructions between two chunks (stand-in for bookkeeping)
+template <int PASS, int GAP>
+__global__ void __launch_bounds__(256, 1) probe(float* out, long long* clk, int iters, float cs) {
+    __shared__ __align__(16) float lse[128];
+    if (threadIdx.x < 128) lse[threadIdx.x] = 3.f + threadIdx.x * 1e-3f;
+    __syncthreads();
+    const uint32_t ls = (uint32_t)__cvta_generic_to_shared(lse);
+    float va[64], vb[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) { va[i] = (threadIdx.x + i) * 1e-3f; vb[i] = (threadIdx.x + 2 * i) * 1e-3f; }
+    float m = -CUDART_INF_F, l = 0.f, colsum = 0.f;
+    unsigned x = threadIdx.x;
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+        if (PASS == 1) pass1_chunk<64>(va, cs, m, l); else pass2_chunk<64>(va, ls, cs, colsum);
+#pragma unroll
+        for (int g = 0; g < GAP; ++g) x = x * 1664525u + 1013904223u;
+        va[x & 63 ? 0 : 1] += 1e-6f;
+        if (PASS == 1) pass1_chunk<64>(vb, cs, m, l); else pass2_chunk<64>(vb, ls + 256, cs, colsum);
+#pragma unroll
+        for (int g = 0; g < GAP; ++g) x = x * 1664525u + 1013904223u;
+        vb[x & 63 ? 0 : 1] += 1e-6f;
+    }
+    const long long t1 = clock64();
+    out[blockIdx.x * blockDim.x + threadIdx.x] = m + l + colsum + (float)x;
+    if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
+}
+
+template <int PASS, int GAP>
+static void run(float* out, long long* clk) {
+    const int iters = 1000;
+    for (int rep = 0; rep < 2; ++rep) probe<PASS, GAP><<<148, 256>>>(out, clk, iters, 0.18f);
+    cudaDeviceSynchronize();
+    long long h[148];
+    cudaMemcpy(h, clk, sizeof(h), cudaMemcpyDeviceToHost);
+    double c = 0;
+    for (int i = 0; i < 148; ++i) c += (double)h[i];
+    c /= 148;
+    printf("pass %d, %3d dependent instructions between chunks: %.2f clk per warp-level EX2 per sub-partition\n", PASS, GAP,
+           c / (iters * 128.0 * 2));
+}
+
+int main() {
+    float* out;
+    long long* clk;
+    cudaMalloc(&out, 148 * 256 * sizeof(float));
+    cudaMalloc(&clk, 148 * sizeof(long long));
+    run<1, 0>(out, clk);
+    run<1, 32>(out, clk);
+    run<1, 128>(out, clk);
+    run<2, 0>(out, clk);
+    run<2, 32>(out, clk);
+    run<2, 128>(out, clk);
+    printf("%s\n", cudaGetErrorString(cudaGetLastError()));
+    return 0;
+}

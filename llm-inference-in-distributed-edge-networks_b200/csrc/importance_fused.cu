@@ -38,13 +38,25 @@ constexpr uint32_t kPartBytes = 128 * 128;           // 128 rows x 64 fp16: one 
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // h0 + h1
 constexpr int kStages = 4;                           // streamed tiles in flight; one barrier pair and one TMA issue per tile
 constexpr int kAcc = 3;                              // TMEM accumulator buffers, used in rotation
-constexpr int kThreads = 512;                         // 4 warpgroups: control, epilogue x2, operand loaders
+#ifndef SPLITQ_K2_EPI_GROUPS
+#define SPLITQ_K2_EPI_GROUPS 2
+#endif
+constexpr int kEpiGroups = SPLITQ_K2_EPI_GROUPS;      // epilogue warpgroups; tile n goes to group n % kEpiGroups
+constexpr int kChunk = kEpiGroups == 2 ? 64 : 32;     // accumulator columns per register buffer (two buffers per thread)
+constexpr int kChunks = kTile / kChunk;
+constexpr int kEpiRegs = kEpiGroups == 2 ? 200 : 128; // setmaxnreg budgets; they add up to the launch-time pool
+constexpr int kCtlRegs = kEpiGroups == 2 ? 56 : 40;
+constexpr int kLdrRegs = 56;
+constexpr int kThreads = 128 * (kEpiGroups + 2);      // warpgroups: control, epilogue x kEpiGroups, operand loaders
+static_assert(kEpiGroups == 2 || kEpiGroups == 3, "2 or 3 epilogue groups");
+static_assert(128 * (kCtlRegs + kLdrRegs + kEpiGroups * kEpiRegs) <= kThreads * (65536 / kThreads / 8 * 8),
+              "setmaxnreg budgets exceed the registers the CTA is launched with");
 constexpr uint32_t kTmemCols = 512;                   // 3 accumulators (128 each) + 2 fixed-operand buffers (h0 32 + h1 32 each)
 constexpr uint32_t kTmemA = kAcc * 128;               // first column of the fixed-operand buffers
 constexpr uint32_t kTmemABuf = 64;                    // columns per fixed-operand buffer (two halfs per column)
 constexpr uint32_t kBarOff = kStages * kOperandBytes;
 constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
-constexpr uint32_t kSmemBytes = kLseOff + 8 * 2 * kTile * 4;  // lse: 8 epilogue warps x 2 buffers x 128 floats
+constexpr uint32_t kSmemBytes = kLseOff + 4 * kEpiGroups * 2 * kTile * 4;  // lse: per epilogue warp 2 buffers x 128 floats
 // (the dynamic smem base must be 1024-aligned; checked in the kernel)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -169,7 +181,7 @@ constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) <<
 struct Params {
     int B, H, KVH, S, nb;
     int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
-    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads (timing experiments only)
+    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads, bit3: print cycle accounting
     float cs;          // scaling * log2(e)
     int tiles;         // tiles of one pass = B * H * tiles_per_bh
     float2* ml;        // (kSlots,B,H,S) pass-1 partial (max, sum) per result slot, pre-set to (-inf, 0)
@@ -186,10 +198,10 @@ struct Params {
 // blocks in order.  CTA c takes the contiguous range [c*T/G, (c+1)*T/G): every CTA gets the same
 // number of tiles (+-1) whatever the causal triangle looks like, neighbouring CTAs stream the same
 // (b,h) operands (L2), and an item is cut at most once (G is chosen so that a range is at least as
-// long as the longest item).  The two pieces of a cut item, and the two epilogue groups inside a
-// piece, put their partial results into kSlots = 4 separate slots that are merged in a fixed order
+// long as the longest item).  The two pieces of a cut item, and the epilogue groups inside a
+// piece, put their partial results into kSlots = 2 x groups separate slots that are merged in a fixed order
 // afterwards, so the result does not depend on the schedule's timing.
-constexpr int kSlots = 4;
+constexpr int kSlots = 2 * kEpiGroups;
 struct Seg {
     int bh, blk, ta, tb;  // streamed blocks [ta, tb) of item (bh, blk)
     int part;             // 1 if an earlier CTA holds the first streamed blocks of this item
@@ -250,10 +262,11 @@ struct SegIter {
 };
 
 // ---- epilogue building blocks -------------------------------------------------------------------
-// 64 consecutive columns of this thread's TMEM lane; asynchronous until tc_ld_wait()
-__device__ __forceinline__ void tc_ld64_issue(uint32_t taddr, float (&v)[64]) {
+// NC (32 or 64) consecutive columns of this thread's TMEM lane; asynchronous until tc_ld_wait()
+template <int NC>
+__device__ __forceinline__ void tc_ld_issue(uint32_t taddr, float (&v)[NC]) {
 #pragma unroll
-    for (int hlf = 0; hlf < 2; ++hlf) {
+    for (int hlf = 0; hlf < NC / 32; ++hlf) {
         float* q = v + 32 * hlf;
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -297,32 +310,34 @@ __device__ __forceinline__ float4 load_lse4(const float* __restrict__ row0, int 
     r.w = q0 + 3 < S ? __ldg(row0 + q0 + 3) : INFINITY;
     return r;
 }
-// pass 1, 64 columns (= keys c0..c0+63) of query row g: online log-sum-exp in the log2 domain
-__device__ __forceinline__ void pass1_half(float (&v)[64], int c0, bool edge, int g, int S, bool causal, float cs, float& m,
-                                           float& l) {
+// pass 1, NC columns (= keys c0..c0+NC-1) of query row g: online log-sum-exp in the log2 domain
+template <int NC>
+__device__ __forceinline__ void pass1_chunk(float (&v)[NC], int c0, bool edge, int g, int S, bool causal, float cs, float& m,
+                                            float& l) {
+    constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
     if (edge) {  // valid iff key < S and (not causal or key <= query)
         const int jmax = min(S - 1, causal ? g : S - 1);
 #pragma unroll
-        for (int i = 0; i < 64; ++i)
+        for (int i = 0; i < NC; ++i)
             if (c0 + i > jmax) v[i] = -INFINITY;
     }
     float cm0 = v[0], cm1 = v[1];
 #pragma unroll
-    for (int i = 2; i < 64; i += 2) {
+    for (int i = 2; i < NC; i += 2) {
         cm0 = fmaxf(cm0, v[i]);
         cm1 = fmaxf(cm1, v[i + 1]);
     }
     const float cm = fmaxf(cm0, cm1) * cs;
-    if (cm > -INFINITY) {  // at least one valid column for this row in this half
+    if (cm > -INFINITY) {  // at least one valid column for this row in this chunk
         const float mn = fmaxf(m, cm);
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-        for (int i0 = 0; i0 < 64; i0 += kExpBatch) {
-            float e[kExpBatch];
+        for (int i0 = 0; i0 < NC; i0 += EB) {
+            float e[EB];
 #pragma unroll
-            for (int j = 0; j < kExpBatch; ++j) e[j] = ex2_ordered(fmaf(v[i0 + j], cs, -mn));
+            for (int j = 0; j < EB; ++j) e[j] = ex2_ordered(fmaf(v[i0 + j], cs, -mn));
 #pragma unroll
-            for (int j = 0; j < kExpBatch; j += 4) {
+            for (int j = 0; j < EB; j += 4) {
                 s0 += e[j + 0];
                 s1 += e[j + 1];
                 s2 += e[j + 2];
@@ -333,19 +348,20 @@ __device__ __forceinline__ void pass1_half(float (&v)[64], int c0, bool edge, in
         m = mn;
     }
 }
-// pass 2, 64 columns (= queries c0..c0+63) of key row g: sum of exp2(s*cs - lse2[query]); ls = shared
-// address of the 64 lse values.  SPECIAL = diagonal / last-row tiles (masking and the last-row
-// pick); the common tile runs the branch-free instantiation so that the 64 exp2 form one
+// pass 2, NC columns (= queries c0..c0+NC-1) of key row g: sum of exp2(s*cs - lse2[query]); ls = shared
+// address of the NC lse values.  SPECIAL = diagonal / last-row tiles (masking and the last-row
+// pick); the common tile runs the branch-free instantiation so that the exp2 form one
 // straight-line, fully scheduled block.
-template <bool SPECIAL>
-__device__ __forceinline__ void pass2_body(const float (&v)[64], uint32_t ls, int c0, bool mask, int g, int last_col,
+template <int NC, bool SPECIAL>
+__device__ __forceinline__ void pass2_body(const float (&v)[NC], uint32_t ls, int c0, bool mask, int g, int last_col,
                                            float cs, float& colsum, float& lastp) {
+    constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-    for (int i0 = 0; i0 < 64; i0 += kExpBatch) {
-        float e[kExpBatch];
+    for (int i0 = 0; i0 < NC; i0 += EB) {
+        float e[EB];
 #pragma unroll
-        for (int j = 0; j < kExpBatch; j += 4) {
+        for (int j = 0; j < EB; j += 4) {
             const float4 ls4 = lds128(ls + 4u * (i0 + j));
             e[j + 0] = ex2_ordered(fmaf(v[i0 + j + 0], cs, -ls4.x));
             e[j + 1] = ex2_ordered(fmaf(v[i0 + j + 1], cs, -ls4.y));
@@ -353,7 +369,7 @@ __device__ __forceinline__ void pass2_body(const float (&v)[64], uint32_t ls, in
             e[j + 3] = ex2_ordered(fmaf(v[i0 + j + 3], cs, -ls4.w));
         }
 #pragma unroll
-        for (int j = 0; j < kExpBatch; ++j) {
+        for (int j = 0; j < EB; ++j) {
             if (SPECIAL) {
                 const int i = i0 + j;  // valid iff query >= key (queries >= S carry lse = +inf -> 0)
                 e[j] = (mask && c0 + i < g) ? 0.f : e[j];
@@ -361,7 +377,7 @@ __device__ __forceinline__ void pass2_body(const float (&v)[64], uint32_t ls, in
             }
         }
 #pragma unroll
-        for (int j = 0; j < kExpBatch; j += 4) {
+        for (int j = 0; j < EB; j += 4) {
             s0 += e[j + 0];
             s1 += e[j + 1];
             s2 += e[j + 2];
@@ -370,12 +386,13 @@ __device__ __forceinline__ void pass2_body(const float (&v)[64], uint32_t ls, in
     }
     colsum += (s0 + s1) + (s2 + s3);
 }
-__device__ __forceinline__ void pass2_half(const float (&v)[64], uint32_t ls, int c0, bool edge, int g, bool has_last,
-                                           int last_col, bool causal, float cs, float& colsum, float& lastp) {
+template <int NC>
+__device__ __forceinline__ void pass2_chunk(const float (&v)[NC], uint32_t ls, int c0, bool edge, int g, bool has_last,
+                                            int last_col, bool causal, float cs, float& colsum, float& lastp) {
     if (edge || has_last)
-        pass2_body<true>(v, ls, c0, edge && causal, g, has_last ? last_col : -1, cs, colsum, lastp);
+        pass2_body<NC, true>(v, ls, c0, edge && causal, g, has_last ? last_col : -1, cs, colsum, lastp);
     else
-        pass2_body<false>(v, ls, c0, false, g, -1, cs, colsum, lastp);
+        pass2_body<NC, false>(v, ls, c0, false, g, -1, cs, colsum, lastp);
 }
 
 // PASS 1 = row log-sum-exp, 2 = column sums; DBG compiles the timing-experiment switches of Params::dbg in
@@ -428,7 +445,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     const int wg = warp >> 2;  // warpgroup: 0 control, 1-2 epilogue, 3 fixed-operand loaders
 
     if (wg == 0) {
-        reg_dec<56>();
+        reg_dec<kCtlRegs>();
         if (warp == 0) {
             // ===== TMA producer: one stage = one streamed 128-row tile (h0 + h1 parts); per tile ONE
             // barrier wait, one expect_tx and ONE 4-D TMA issue.  The per-transaction round trip
@@ -503,9 +520,9 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 }
             }
         }
-    } else if (wg == 3) {
+    } else if (wg == kEpiGroups + 1) {
         // ===== fixed-operand loaders: one thread per row; fp16 h0 / h1 parts -> TMEM (A operand) =====
-        reg_dec<56>();
+        reg_dec<kLdrRegs>();
         const int q4 = warp & 3;
         const int row = q4 * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
@@ -538,7 +555,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             if (lane == 0) mbar_arrive(bar_afull + 8 * ab);
         }
     } else {
-        reg_inc<200>();
+        reg_inc<kEpiRegs>();
         // ===== epilogue: two groups of 4 warps; group g takes the tiles of parity g of the CTA's
         // range, tile n lives in TMEM accumulator n % 3; a thread owns one TMEM lane (tile row).
         // Every warp runs on its own: no block or group barrier anywhere, only the accumulator
@@ -548,7 +565,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         // them for itself) are on their way from L2.  When the sequence moves to another item the
         // per-row partial results are stored to this (piece, group) slot.
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
-        const int grp = wg - 1;                     // tile parity of this group
+        const int grp = wg - 1;                     // this group takes tiles grp, grp + kEpiGroups, ...
         const int row = q4 * 32 + lane;
         const uint32_t tmem_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const uint32_t lse_w = base + kLseOff + (uint32_t)(warp - 4) * (2u * kTile * 4u);  // two 128-float buffers per warp
@@ -574,7 +591,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         auto flush = [&]() {
             const int g = st_blk * kTile + row;
             if (st_bh < 0 || g >= S) return;
-            const int slot = ((st_bh == first_bh && st_blk == first_blk) ? first_part * 2 : 0) + grp;
+            const int slot = ((st_bh == first_bh && st_blk == first_blk) ? first_part * kEpiGroups : 0) + grp;
             const size_t o = (size_t)st_bh * S + g;
             if (PASS == 1) {
                 p.ml[slot * rows + o] = make_float2(m, l);
@@ -584,12 +601,13 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             }
         };
 
-        float va[64], vb[64];
+        float va[kChunk], vb[kChunk];               // chunk c of a tile sits in va (c even) or vb (c odd)
         if (dbg & 4) {
 #pragma unroll
-            for (int i = 0; i < 64; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
+            for (int i = 0; i < kChunk; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
         }
         uint32_t lb = 0;                            // lse buffer of the current tile
+        long long clk_math = 0, clk_loop = DBG ? clock64() : 0;
         bool have = nx.valid();
         if (have) {
             if (PASS == 2) {
@@ -599,7 +617,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const uint32_t a = gn % (uint32_t)kAcc;
             mbar_wait(bar_tfull + 8 * a, (gn / (uint32_t)kAcc) & 1u);
             tc_fence_after();
-            if (!(dbg & 4)) tc_ld64_issue(tmem_lane + a * kTile, va);
+            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + a * kTile, va);
             tc_ld_wait();
         }
         while (have) {
@@ -608,7 +626,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const uint32_t a = gn % (uint32_t)kAcc;
             const uint32_t cur_tmem = tmem_lane + a * kTile;
             // ---- look one tile ahead and start fetching its lse values
-            nx.advance(2);
+            nx.advance(kEpiGroups);
             const bool has_next = nx.valid();
             float4 lse_nx = make_float4(0.f, 0.f, 0.f, 0.f);
             if (PASS == 2 && has_next) lse_nx = load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec);
@@ -624,43 +642,54 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const bool has_last = last_tile == t;
             saw_last = saw_last || has_last;
             const uint32_t lse_t = lse_w + lb * (kTile * 4u);
-
-            if (!(dbg & 4)) tc_ld64_issue(cur_tmem + 64, vb);  // second half in flight ...
-            if (dbg & 1) { colsum += va[0] + va[63]; l += va[1]; }
-            else if (PASS == 1) pass1_half(va, t * kTile, edge, g, S, causal, cs, m, l);
-            else pass2_half(va, lse_t, t * kTile, edge, g, has_last, last_col, causal, cs, colsum, lastp);
-            tc_ld_wait();                             // ... now in registers: accumulator is drained
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
-            const uint32_t na = (gn + 2u) % (uint32_t)kAcc, nph = ((gn + 2u) / (uint32_t)kAcc) & 1u;
+            const uint32_t na = (gn + kEpiGroups) % (uint32_t)kAcc, nph = ((gn + kEpiGroups) / (uint32_t)kAcc) & 1u;
             bool ready = false;
-            if (has_next) {
-                if (PASS == 2) sts128(lse_w + (lb ^ 1u) * (kTile * 4u) + 16u * lane, lse_nx);
-                ready = mbar_test(bar_tfull + 8 * na, nph);
-                ready = __all_sync(0xffffffffu, ready);
-                if (ready) {
-                    tc_fence_after();
-                    if (!(dbg & 4)) tc_ld64_issue(tmem_lane + na * kTile, va);  // next tile's first half in flight ...
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                float (&cur)[kChunk] = (c & 1) ? vb : va;
+                float (&oth)[kChunk] = (c & 1) ? va : vb;
+                if (c + 1 < kChunks) {                // next chunk of this tile in flight ...
+                    if (!(dbg & 4)) tc_ld_issue<kChunk>(cur_tmem + (c + 1) * kChunk, oth);
+                } else if (has_next) {                // ... or the next tile's first chunk, if its MMAs are done
+                    if (PASS == 2) sts128(lse_w + (lb ^ 1u) * (kTile * 4u) + 16u * lane, lse_nx);
+                    ready = mbar_test(bar_tfull + 8 * na, nph);
+                    ready = __all_sync(0xffffffffu, ready);
+                    if (ready) {
+                        tc_fence_after();
+                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
+                    }
                 }
-            }
-            if (dbg & 1) { colsum += vb[0] + vb[63]; l += vb[1]; }
-            else if (PASS == 1) pass1_half(vb, t * kTile + 64, edge, g, S, causal, cs, m, l);
-            else pass2_half(vb, lse_t + 256u, t * kTile + 64, edge, g, has_last, last_col - 64, causal, cs, colsum, lastp);
-            if (has_next) {
-                if (!ready) {
-                    mbar_wait(bar_tfull + 8 * na, nph);
-                    tc_fence_after();
-                    if (!(dbg & 4)) tc_ld64_issue(tmem_lane + na * kTile, va);
+                const long long tm0 = (DBG && (dbg & 8)) ? clock64() : 0;
+                if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
+                else if (PASS == 1) pass1_chunk<kChunk>(cur, t * kTile + c * kChunk, edge, g, S, causal, cs, m, l);
+                else pass2_chunk<kChunk>(cur, lse_t + c * (kChunk * 4u), t * kTile + c * kChunk, edge, g, has_last,
+                                         last_col - c * kChunk, causal, cs, colsum, lastp);
+                if (DBG && (dbg & 8)) clk_math += clock64() - tm0;
+                if (c + 1 < kChunks) {
+                    tc_ld_wait();
+                    if (c + 2 == kChunks) {           // the last chunk is in registers: accumulator drained
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
+                    }
+                } else if (has_next) {
+                    if (!ready) {
+                        mbar_wait(bar_tfull + 8 * na, nph);
+                        tc_fence_after();
+                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
+                    }
+                    tc_ld_wait();                     // next tile's first chunk landed
+                    __syncwarp();                     // the lse values staged by the other lanes are visible
+                    lb ^= 1u;
+                    gn += kEpiGroups;
                 }
-                tc_ld_wait();                         // ... and landed
-                __syncwarp();                         // the lse values staged by the other lanes are visible
-                lb ^= 1u;
-                gn += 2u;
             }
             have = has_next;
         }
         flush();
+        if (DBG && (dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))  // bit 3: cycle accounting
+            printf("K2 pass %d cta %d warp %d: %lld cycles in the math bodies of %lld in the tile loop, %d tiles\n", PASS,
+                   blockIdx.x, warp, clk_math, clock64() - clk_loop, (int)(gn / kEpiGroups));
     }
 
     tc_fence_before();
@@ -889,7 +918,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
                    "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
     SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
                    "materialised path splitq_importance_colmean", hd);
-    const int dbg = (mode >> 4) & 7;  // undocumented timing-experiment bits
+    const int dbg = (mode >> 4) & 15;  // undocumented timing-experiment bits
     mode &= 15;
     SPLITQ_REQUIRE(mode == SPLITQ_FUSED_F16X3 || mode == SPLITQ_FUSED_F16X1, SPLITQ_ERR_ARG,
                    "importance_fused: unknown mode %d", mode);
