@@ -401,7 +401,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
                         const Params p) {
     extern __shared__ uint8_t smem_raw[];
-    const uint32_t base = smem_u32(smem_raw);
+    uint32_t base;  // opaque copy: otherwise ptxas re-derives the shared-window address (S2UR + ULEA) at every use
+    asm volatile("mov.u32 %0, %1;" : "=r"(base) : "r"(smem_u32(smem_raw)));
     if (base & 1023u) __trap();  // swizzle-128B slabs need 1024-byte alignment; no static smem precedes
     uint8_t* gen = smem_raw;
     const uint32_t ring_s = base;
@@ -608,26 +609,31 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
         uint32_t lb = 0;                            // lse buffer of the current tile
         long long clk_math = 0, clk_loop = DBG ? clock64() : 0;
+        uint32_t acc_i = (uint32_t)grp % kAcc, acc_ph = 0;  // accumulator (gn % kAcc) and barrier phase of the current tile
         bool have = nx.valid();
         if (have) {
             if (PASS == 2) {
                 sts128(lse_w + 16u * lane, load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec));
                 __syncwarp();
             }
-            const uint32_t a = gn % (uint32_t)kAcc;
-            mbar_wait(bar_tfull + 8 * a, (gn / (uint32_t)kAcc) & 1u);
+            mbar_wait(bar_tfull + 8 * acc_i, acc_ph);
             tc_fence_after();
-            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + a * kTile, va);
+            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + acc_i * kTile, va);
             tc_ld_wait();
         }
         while (have) {
             // ---- the tile being processed: number gn = (bh, blk, t), where nx stands before it moves on
             const int bh = nx.bh, blk = nx.blk, t = nx.t;
-            const uint32_t a = gn % (uint32_t)kAcc;
+            const uint32_t a = acc_i;
             const uint32_t cur_tmem = tmem_lane + a * kTile;
-            // ---- look one tile ahead and start fetching its lse values
+            // ---- look one tile ahead: is its accumulator ready (asked early, the answer takes ~100
+            // cycles), and start fetching its lse values
+            uint32_t na = a + (uint32_t)(kEpiGroups % kAcc), nph = acc_ph;
+            if (na >= (uint32_t)kAcc) { na -= (uint32_t)kAcc; nph ^= 1u; }
+            if (kEpiGroups >= kAcc) nph ^= 1u;
             nx.advance(kEpiGroups);
             const bool has_next = nx.valid();
+            bool ready = has_next && mbar_test(bar_tfull + 8 * na, nph);
             float4 lse_nx = make_float4(0.f, 0.f, 0.f, 0.f);
             if (PASS == 2 && has_next) lse_nx = load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec);
             // ---- entering a new item: store what the registers hold
@@ -642,8 +648,6 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const bool has_last = last_tile == t;
             saw_last = saw_last || has_last;
             const uint32_t lse_t = lse_w + lb * (kTile * 4u);
-            const uint32_t na = (gn + kEpiGroups) % (uint32_t)kAcc, nph = ((gn + kEpiGroups) / (uint32_t)kAcc) & 1u;
-            bool ready = false;
 #pragma unroll
             for (int c = 0; c < kChunks; ++c) {
                 float (&cur)[kChunk] = (c & 1) ? vb : va;
@@ -652,7 +656,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     if (!(dbg & 4)) tc_ld_issue<kChunk>(cur_tmem + (c + 1) * kChunk, oth);
                 } else if (has_next) {                // ... or the next tile's first chunk, if its MMAs are done
                     if (PASS == 2) sts128(lse_w + (lb ^ 1u) * (kTile * 4u) + 16u * lane, lse_nx);
-                    ready = mbar_test(bar_tfull + 8 * na, nph);
+                    if (!ready) ready = mbar_test(bar_tfull + 8 * na, nph);
                     ready = __all_sync(0xffffffffu, ready);
                     if (ready) {
                         tc_fence_after();
@@ -682,6 +686,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     __syncwarp();                     // the lse values staged by the other lanes are visible
                     lb ^= 1u;
                     gn += kEpiGroups;
+                    acc_i = na;
+                    acc_ph = nph;
                 }
             }
             have = has_next;
