@@ -399,7 +399,9 @@ def main() -> None:
             nb = (S + 127) // 128
             tiles = B * H * nb * (nb + 1)  # causal tiles, two passes
             tile_flops = 2.0 * 128 * 128 * 64
-            bf16 = peaks.get("bf16_tflops", 1590.0)
+            # the kernel is timed inside a long back-to-back step loop: the sustained cuBLAS figure is its peak
+            bf16_key = "bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "bf16_tflops"
+            bf16 = peaks.get(bf16_key, 1590.0)
             x3 = args.fused_mode == "f16x3"
             issued = tiles * tile_flops * (3 if x3 else 1)        # h0*h0 (+ h1*h0 + h0*h1), all kind::f16
             peak_mix = bf16                                       # kind::f16 runs at the measured cuBLAS bf16 rate
@@ -412,8 +414,9 @@ def main() -> None:
                 "traffic": (captured_traffic("r1_h_ncu_full_k2_summary.csv", "fused_importance_kernel")
                             if args.workload == DEFAULT_WORKLOAD and B == cfg["B_fused"] and x3 else None),
                 "traffic_note": "DRAM bytes of the two tensor-core passes (ncu); operands are re-read from L2, not HBM",
-                "peak_source": ("MEASURED_PEAKS.json bf16_tflops" if peaks else "fallback 1590") +
-                               " (kind::f16 rate)",
+                "peak_source": (f"MEASURED_PEAKS.json {bf16_key}" if peaks else "fallback 1590 (B200_PROFILING.md)") +
+                               " (kind::f16 runs at the cuBLAS bf16 rate; burst figure: " +
+                               f"{peaks.get('bf16_tflops', 1590.0):.0f})",
                 "flops_counted": "issued tcgen05 MMA flops: causal tiles x 2 passes x 3 fp16 products (split operands)",
                 "issued_flops_per_launch": issued, "dense_equivalent_tflops": dense_equiv / (score_ms * 1e-3) / 1e12,
                 "kernel_ms": score_ms, "co_bound_mufu_frac": mufu_ms / score_ms,
