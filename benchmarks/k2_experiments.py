@@ -13,7 +13,7 @@ def t(mode,n=10):
     for _ in range(n): splitq.importance_fused(q,k,0.125,mode=mode)
     b.record(); torch.cuda.synchronize()
     return a.elapsed_time(b)/n
-for name,mode in [("x3",0),("x1",1),("x3 nomath",16),("x1 nomath",17),("x3 nomma",32),("x1 nomma",33),("x3 nomath nomma",48),("x1 nomath nomma",49),("x3 nomma noload",96),("x3 noload",64)]:
+for name,mode in [("x3",0),("x1",1),("x3 nomath",16),("x1 nomath",17),("x3 nomma",32),("x1 nomma",33),("x3 nomath nomma",48),("x1 nomath nomma",49),("x3 nomma noload",96),("x3 noload",64),("x3 no operand fetch",256),("x3 nomath nomma no operand fetch",256+48)]:
     print(f"{name:18s} {t(mode):.3f} ms")
 
 if len(sys.argv) > 3:  # cycle accounting printed by the kernel (debug instantiation)

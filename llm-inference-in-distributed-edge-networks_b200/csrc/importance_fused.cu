@@ -181,7 +181,7 @@ constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) <<
 struct Params {
     int B, H, KVH, S, nb;
     int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
-    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads, bit3: print cycle accounting
+    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads, bit3: print cycle accounting, bit4: loaders skip their global loads
     float cs;          // scaling * log2(e)
     int tiles;         // tiles of one pass = B * H * tiles_per_bh
     float2* ml;        // (kSlots,B,H,S) pass-1 partial (max, sum) per result slot, pre-set to (-inf, 0)
@@ -297,6 +297,11 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ float lds32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
@@ -310,22 +315,35 @@ __device__ __forceinline__ float4 load_lse4(const float* __restrict__ row0, int 
     r.w = q0 + 3 < S ? __ldg(row0 + q0 + 3) : INFINITY;
     return r;
 }
-// pass 1, NC columns (= keys c0..c0+NC-1) of query row g: online log-sum-exp in the log2 domain
-template <int NC>
-__device__ __forceinline__ void pass1_chunk(float (&v)[NC], int c0, bool edge, int g, int S, bool causal, float cs, float& m,
-                                            float& l) {
+// One column of this thread's TMEM lane (the last query's logit for pass 2's last-row importance)
+__device__ __forceinline__ void tc_ld1_issue(uint32_t taddr, float& v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=f"(v) : "r"(taddr) : "memory");
+}
+// Masked tiles (the causal diagonal, the ragged last block) are handled per batch of kExpBatch
+// columns with warp-uniform tests: a batch that is invalid for all 32 rows of the warp is skipped
+// outright (no exp2 at all: the diagonal tile costs about half a normal one), a batch valid for
+// all rows runs the plain code, and only the one or two batches the boundary crosses pay a
+// compare + select per element.  r = this thread's row and w0 = the warp's first row, both
+// relative to the tile; columns are tile-relative too.
+//
+// pass 1, NC columns (= keys cr0..cr0+NC-1) of one query row: online log-sum-exp in the log2
+// domain.  EDGE: key c is valid iff c <= jmax (this row) ; jlo / jhi = the smallest / largest jmax in the warp.
+template <int NC, bool EDGE>
+__device__ __forceinline__ void pass1_body(float (&v)[NC], int cr0, int jmax, int jlo, int jhi, float cs, float& m, float& l) {
     constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
-    if (edge) {  // valid iff key < S and (not causal or key <= query)
-        const int jmax = min(S - 1, causal ? g : S - 1);
+    float cm0 = -INFINITY, cm1 = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < NC; ++i)
-            if (c0 + i > jmax) v[i] = -INFINITY;
-    }
-    float cm0 = v[0], cm1 = v[1];
+    for (int i0 = 0; i0 < NC; i0 += EB) {
+        if (EDGE && cr0 + i0 > jhi) continue;            // nothing valid for any row of the warp
+        if (EDGE && cr0 + i0 + EB - 1 > jlo) {           // the boundary crosses this batch
 #pragma unroll
-    for (int i = 2; i < NC; i += 2) {
-        cm0 = fmaxf(cm0, v[i]);
-        cm1 = fmaxf(cm1, v[i + 1]);
+            for (int j = 0; j < EB; ++j) v[i0 + j] = (cr0 + i0 + j > jmax) ? -INFINITY : v[i0 + j];
+        }
+#pragma unroll
+        for (int j = 0; j < EB; j += 2) {
+            cm0 = fmaxf(cm0, v[i0 + j]);
+            cm1 = fmaxf(cm1, v[i0 + j + 1]);
+        }
     }
     const float cm = fmaxf(cm0, cm1) * cs;
     if (cm > -INFINITY) {  // at least one valid column for this row in this chunk
@@ -333,6 +351,7 @@ __device__ __forceinline__ void pass1_chunk(float (&v)[NC], int c0, bool edge, i
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
         for (int i0 = 0; i0 < NC; i0 += EB) {
+            if (EDGE && cr0 + i0 > jhi) continue;
             float e[EB];
 #pragma unroll
             for (int j = 0; j < EB; ++j) e[j] = ex2_ordered(fmaf(v[i0 + j], cs, -mn));
@@ -348,17 +367,16 @@ __device__ __forceinline__ void pass1_chunk(float (&v)[NC], int c0, bool edge, i
         m = mn;
     }
 }
-// pass 2, NC columns (= queries c0..c0+NC-1) of key row g: sum of exp2(s*cs - lse2[query]); ls = shared
-// address of the NC lse values.  SPECIAL = diagonal / last-row tiles (masking and the last-row
-// pick); the common tile runs the branch-free instantiation so that the exp2 form one
-// straight-line, fully scheduled block.
-template <int NC, bool SPECIAL>
-__device__ __forceinline__ void pass2_body(const float (&v)[NC], uint32_t ls, int c0, bool mask, int g, int last_col,
-                                           float cs, float& colsum, float& lastp) {
+// pass 2, NC columns (= queries cr0..cr0+NC-1) of one key row: sum of exp2(s*cs - lse2[query]); ls =
+// shared address of the NC lse values (queries >= S carry lse = +inf -> 0, so the ragged last
+// block needs no mask).  DIAG: the causal diagonal tile, query c is valid iff c >= r.
+template <int NC, bool DIAG>
+__device__ __forceinline__ void pass2_body(const float (&v)[NC], uint32_t ls, int cr0, int r, int w0, float cs, float& colsum) {
     constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
     for (int i0 = 0; i0 < NC; i0 += EB) {
+        if (DIAG && cr0 + i0 + EB <= w0) continue;       // all queries of the batch precede every key of the warp
         float e[EB];
 #pragma unroll
         for (int j = 0; j < EB; j += 4) {
@@ -368,13 +386,9 @@ __device__ __forceinline__ void pass2_body(const float (&v)[NC], uint32_t ls, in
             e[j + 2] = ex2_ordered(fmaf(v[i0 + j + 2], cs, -ls4.z));
             e[j + 3] = ex2_ordered(fmaf(v[i0 + j + 3], cs, -ls4.w));
         }
+        if (DIAG && cr0 + i0 < w0 + 31) {                // the diagonal crosses this batch
 #pragma unroll
-        for (int j = 0; j < EB; ++j) {
-            if (SPECIAL) {
-                const int i = i0 + j;  // valid iff query >= key (queries >= S carry lse = +inf -> 0)
-                e[j] = (mask && c0 + i < g) ? 0.f : e[j];
-                lastp = (last_col == i) ? e[j] : lastp;
-            }
+            for (int j = 0; j < EB; ++j) e[j] = (cr0 + i0 + j < r) ? 0.f : e[j];
         }
 #pragma unroll
         for (int j = 0; j < EB; j += 4) {
@@ -385,14 +399,6 @@ __device__ __forceinline__ void pass2_body(const float (&v)[NC], uint32_t ls, in
         }
     }
     colsum += (s0 + s1) + (s2 + s3);
-}
-template <int NC>
-__device__ __forceinline__ void pass2_chunk(const float (&v)[NC], uint32_t ls, int c0, bool edge, int g, bool has_last,
-                                            int last_col, bool causal, float cs, float& colsum, float& lastp) {
-    if (edge || has_last)
-        pass2_body<NC, true>(v, ls, c0, edge && causal, g, has_last ? last_col : -1, cs, colsum, lastp);
-    else
-        pass2_body<NC, false>(v, ls, c0, false, g, -1, cs, colsum, lastp);
 }
 
 // PASS 1 = row log-sum-exp, 2 = column sums; DBG compiles the timing-experiment switches of Params::dbg in
@@ -540,14 +546,14 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const uint4* src = f16 + ((size_t)fix_idx * p.S + (g < p.S ? g : 0)) * (kHd * 2 / 16);
             uint4 q[8];  // this row: 64 halfs = 128 B = 32 TMEM columns per part; h0 is fetched ahead of the wait
 #pragma unroll
-            for (int i = 0; i < 8; ++i) q[i] = g < p.S ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
+            for (int i = 0; i < 8; ++i) q[i] = (g < p.S && !(DBG && (p.dbg & 16))) ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
             mbar_wait_quiet(bar_aempty + 8 * ab, abphase ^ 1);
             tc_fence_after();
             const uint32_t a0 = tmem_base + kTmemA + ab * kTmemABuf + lane_addr;
             tc_st32(a0, q);
             if (p.x3) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) q[i] = g < p.S ? __ldg(src + fpart + i) : make_uint4(0u, 0u, 0u, 0u);
+                for (int i = 0; i < 8; ++i) q[i] = (g < p.S && !(DBG && (p.dbg & 16))) ? __ldg(src + fpart + i) : make_uint4(0u, 0u, 0u, 0u);
                 tc_st32(a0 + 32u, q);
             }
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -643,11 +649,17 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 st_bh = bh;
                 st_blk = blk;
             }
-            const int g = blk * kTile + row;        // global index of this thread's row
-            const bool edge = (causal && t == blk) || (t * kTile + kTile > S);
-            const bool has_last = last_tile == t;
+            const bool diag = causal && t == blk;   // the causal boundary runs through this tile
+            const bool has_last = PASS == 2 && last_tile == t;
             saw_last = saw_last || has_last;
             const uint32_t lse_t = lse_w + lb * (kTile * 4u);
+            // pass 1: largest valid tile-relative key of this row, and its range over the warp
+            const int s_hi = S - 1 - t * kTile;      // last key of the sequence, tile-relative (>= 127: no limit)
+            const int jmax = min(diag ? row : kTile - 1, s_hi);
+            const int jlo = min(diag ? q4 * 32 : kTile - 1, s_hi), jhi = min(diag ? q4 * 32 + 31 : kTile - 1, s_hi);
+            const bool edge1 = diag || s_hi < kTile - 1;
+            float lastv = 0.f;
+            if (has_last && !(dbg & 4)) tc_ld1_issue(cur_tmem + (uint32_t)last_col, lastv);  // lands with the next wait
 #pragma unroll
             for (int c = 0; c < kChunks; ++c) {
                 float (&cur)[kChunk] = (c & 1) ? vb : va;
@@ -665,12 +677,18 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 }
                 const long long tm0 = (DBG && (dbg & 8)) ? clock64() : 0;
                 if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
-                else if (PASS == 1) pass1_chunk<kChunk>(cur, t * kTile + c * kChunk, edge, g, S, causal, cs, m, l);
-                else pass2_chunk<kChunk>(cur, lse_t + c * (kChunk * 4u), t * kTile + c * kChunk, edge, g, has_last,
-                                         last_col - c * kChunk, causal, cs, colsum, lastp);
+                else if (PASS == 1) {
+                    if (edge1) pass1_body<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                    else pass1_body<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                } else {
+                    if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
+                    else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
+                }
                 if (DBG && (dbg & 8)) clk_math += clock64() - tm0;
                 if (c + 1 < kChunks) {
                     tc_ld_wait();
+                    if (c == 0 && has_last)           // p[S-1][key]: the last query is never masked
+                        lastp = ex2(fmaf(lastv, cs, -lds32(lse_t + 4u * (uint32_t)last_col)));
                     if (c + 2 == kChunks) {           // the last chunk is in registers: accumulator drained
                         tc_fence_before();
                         __syncwarp();
@@ -924,7 +942,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
                    "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
     SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
                    "materialised path splitq_importance_colmean", hd);
-    const int dbg = (mode >> 4) & 15;  // undocumented timing-experiment bits
+    const int dbg = (mode >> 4) & 31;  // undocumented timing-experiment bits
     mode &= 15;
     SPLITQ_REQUIRE(mode == SPLITQ_FUSED_F16X3 || mode == SPLITQ_FUSED_F16X1, SPLITQ_ERR_ARG,
                    "importance_fused: unknown mode %d", mode);
