@@ -51,6 +51,7 @@ def main():
     ap.add_argument("--out", default=os.path.join(ROOT, "profiles", "sweep.json"))
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--max-s", type=int, default=16384)
+    ap.add_argument("--md", default=None, help="also write the table as markdown")
     ap.add_argument("--mem-gb", type=float, default=24.0, help="cap on the attention-map batch")
     args = ap.parse_args()
     peaks = {}
@@ -113,6 +114,28 @@ def main():
             S *= 2
     with open(args.out, "w") as f:
         json.dump({"peaks": {"hbm_gbs": hbm, "f16_tflops": bf16}, "points": results}, f, indent=1)
+    if args.md:
+        write_md(args.md, results, hbm, bf16, args.iters)
+
+
+def write_md(path, results, hbm, bf16, iters):
+    lines = ["# Round-1 microbench sweep (BASELINE.json configs[4]) - B200, `python benchmarks/sweep.py --iters %d`" % iters, "",
+             "Peaks: HBM %.1f GB/s (measured copy), fp16/bf16 tensor %.1f TFLOP/s (measured cuBLAS bf16, burst).  "
+             "K2 = three fp16 products per tile (split operands), causal; its TFLOP/s are issued MMA flops." % (hbm, bf16), "",
+             "| shape | S | K1 materialised: B, ms, Mtok/s, GB/s, frac HBM | K2 fused: B, ms, Mtok/s, TFLOP/s issued, frac f16 peak "
+             "| select ms | quant+pack GB/s (frac HBM) |", "|---|---|---|---|---|---|"]
+    for r in results:
+        m, f, q = r.get("materialised", {}), r["fused"], r["quant_pack"]
+        k1 = ("B=%d, %.3f, %.1f, %.0f, %.2f" % (m["B"], m["k1_ms"], m["tokens_per_s"] / 1e6, m["GBps"], m["frac_of_hbm_peak"])
+              if "k1_ms" in m else m.get("skipped", "-"))
+        lines.append("| %s | %d | %s | B=%d, %.3f, %.1f, %.0f, %.2f | %.3f | %.0f (%.2f) |" % (
+            r["model_shape"], r["S"], k1, f["B"], f["k2_ms"], f["tokens_per_s"] / 1e6, f["issued_f16_tflops"],
+            f["frac_of_f16_peak"], r["select_ms"], q["GBps"], q["frac_of_hbm_peak"]))
+    lines += ["", "Single-call CUDA-event timings include ~5-8 us of launch gap per kernel, which is why the small kernels "
+              "(select, quant+pack) read lower here than in the ncu launch list of the bench (quant+pack 31 us for 160 MB = 5.2 TB/s), "
+              "and K2's six launches weigh on the small-S points."]
+    with open(path, "w") as fh:
+        fh.write("\n".join(lines) + "\n")
 
 
 if __name__ == "__main__":
