@@ -267,6 +267,10 @@ def main() -> None:
                     help="fused: scores from the split layer's Q,K (K2, no attention matrix); "
                          "materialised: scores from attention probabilities already in HBM (K1)")
     ap.add_argument("--fused-mode", default="f16x3", choices=["f16x3", "f16x1"])
+    ap.add_argument("--transfer", default="auto", choices=["auto", "nccl", "ipc"],
+                    help="payload hop between paired ranks in the device-resident loop: NCCL send/recv, or a "
+                         "copy-engine pull over CUDA IPC ordered by stream memory operations (auto = ipc, "
+                         "falling back to nccl if the mapping cannot be set up)")
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
@@ -325,6 +329,24 @@ def main() -> None:
     # software pipeline over steps: hop + dequantise of step i on a side stream under the scoring of i+1
     ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused)
     dev_inputs = (q, k, h) if fused else (A, h)
+    ipc, transfer_name = None, "nccl pair exchange" if world > 1 else "device-to-device copy"
+    if world > 1 and args.transfer in ("auto", "ipc"):
+        from splitq.transport import IpcPairExchange
+        ok = torch.ones(1, device=device)
+        try:
+            ipc = IpcPairExchange(ob.plans, rank, world)
+        except Exception as e:  # noqa: BLE001 - e.g. a virtual-memory allocator, no peer access
+            if args.transfer == "ipc":
+                raise
+            print(f"[bench] rank {rank}: IPC exchange unavailable ({e}); using NCCL", file=sys.stderr)
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks use the same transport
+        if ok.item() > 0:
+            for pl in ob.plans:
+                pl.transport = ipc
+            transfer_name = "copy-engine pull over CUDA IPC (NVLink P2P) ordered by stream memory operations; no SM"
+        else:
+            ipc = None
 
     def step(timed_events=None):
         ob.step(*dev_inputs, score_events=timed_events)
@@ -351,6 +373,8 @@ def main() -> None:
         torch.cuda.synchronize()
     elapsed_ms = t0.elapsed_time(t1)
     score_ms = sum(a.elapsed_time(b) for a, b in k_events) / args.steps
+    if ipc is not None:
+        ipc.close()
 
     # ---- end to end through the public host-buffer API (splitq.HostPipeline): every step uploads its
     # inputs from pinned host memory, runs the path, and downloads the dequantised hidden states;
@@ -446,7 +470,7 @@ def main() -> None:
                        "ladder": ladder, "scale_mode": "token" if cfg["scale_mode"] else "group",
                        "importance_impl": args.importance + (f" ({args.fused_mode})" if fused else ""),
                        "payload_bytes_per_window": plan.nbytes,
-                       "transfer": "nccl pair exchange" if world > 1 else "device-to-device copy", "l2": l2_note,
+                       "transfer": transfer_name, "l2": l2_note,
                        "pipelining": "hop + dequantise of step i on a side stream, overlapping the scoring of step i+1"},
             "roofline": roofline,
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,

@@ -176,6 +176,27 @@ int splitq_channel_fake_quant(const float* h, int B, int S, int D, int method, f
 int splitq_transfer_peer(void* dst, int dst_device, const void* src, int src_device, size_t bytes,
                          splitq_stream_t stream);
 
+/* ---- transfer between two processes (one per GPU) without any SM --------------------------
+ * No reference counterpart (the reference only simulates the hop, pythia_model.py:176-188; its
+ * distributed deployment is the paper's premise, not code).  The receiving rank's copy engine
+ * pulls the partner's payload through a CUDA-IPC mapping (NVLink P2P between two GPUs, a plain
+ * device copy when both ranks share one GPU), and the two sides order themselves with stream
+ * memory operations on 32-bit flags, so nothing competes with the persistent scoring kernel for
+ * SMs (splitq/transport.py IpcPairExchange shows the protocol).
+ *   splitq_ipc_export: handle_out[SPLITQ_IPC_HANDLE_BYTES] + byte offset of dev_ptr inside its
+ *     cudaMalloc allocation, to be sent to the partner process by any host channel.
+ *   splitq_ipc_open / _close: map / unmap the partner's buffer (not in the exporting process).
+ *   splitq_stream_write_u32: after all earlier work of the stream, store value at dev_addr.
+ *   splitq_stream_wait_geq_u32: hold the stream until (int32)(*dev_addr - value) >= 0.
+ *   splitq_copy_async: cudaMemcpyAsync over unified addressing (local, peer or IPC-mapped). */
+#define SPLITQ_IPC_HANDLE_BYTES 64
+int splitq_ipc_export(const void* dev_ptr, void* handle_out, size_t* offset_out);
+int splitq_ipc_open(const void* handle, size_t offset, void** dev_ptr_out);
+int splitq_ipc_close(void* dev_ptr, size_t offset);
+int splitq_stream_write_u32(void* dev_addr, uint32_t value, splitq_stream_t stream);
+int splitq_stream_wait_geq_u32(const void* dev_addr, uint32_t value, splitq_stream_t stream);
+int splitq_copy_async(void* dst, const void* src, size_t bytes, splitq_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

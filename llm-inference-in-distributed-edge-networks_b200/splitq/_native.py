@@ -46,7 +46,14 @@ SIGNATURES = {
     "splitq_channel_workspace_bytes": (_sz, [_i, _i, _i]),
     "splitq_channel_fake_quant": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "splitq_transfer_peer": (_i, [_vp, _i, _vp, _i, _sz, _vp]),
+    "splitq_ipc_export": (_i, [_vp, _vp, C.POINTER(C.c_size_t)]),
+    "splitq_ipc_open": (_i, [_vp, _sz, C.POINTER(C.c_void_p)]),
+    "splitq_ipc_close": (_i, [_vp, _sz]),
+    "splitq_stream_write_u32": (_i, [_vp, C.c_uint32, _vp]),
+    "splitq_stream_wait_geq_u32": (_i, [_vp, C.c_uint32, _vp]),
+    "splitq_copy_async": (_i, [_vp, _vp, _sz, _vp]),
 }
+IPC_HANDLE_BYTES = 64
 
 
 class SplitqError(RuntimeError):

@@ -473,7 +473,12 @@ class OverlappedBoundary:
             p.score(inputs[0])
         if score_events is not None:
             score_events[1].record(self.main)
+        tr = p.transport
+        if hasattr(tr, "before_pack"):  # transport.IpcPairExchange: the partner has fetched this slot's last payload
+            tr.before_pack(p)
         p.send(inputs[-1])
+        if hasattr(tr, "after_pack"):   # ... and may fetch the new one
+            tr.after_pack(p)
         packed = torch.cuda.Event()
         packed.record(self.main)
         with torch.cuda.stream(self.side):
