@@ -332,20 +332,15 @@ def main() -> None:
     ipc, transfer_name = None, "nccl pair exchange" if world > 1 else "device-to-device copy"
     if world > 1 and args.transfer in ("auto", "ipc"):
         from splitq.transport import IpcPairExchange
-        ok = torch.ones(1, device=device)
-        try:
+        try:  # the constructor fails on all ranks or on none
             ipc = IpcPairExchange(ob.plans, rank, world)
-        except Exception as e:  # noqa: BLE001 - e.g. a virtual-memory allocator, no peer access
-            if args.transfer == "ipc":
-                raise
-            print(f"[bench] rank {rank}: IPC exchange unavailable ({e}); using NCCL", file=sys.stderr)
-            ok.zero_()
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks use the same transport
-        if ok.item() > 0:
             for pl in ob.plans:
                 pl.transport = ipc
             transfer_name = "copy-engine pull over CUDA IPC (NVLink P2P) ordered by stream memory operations; no SM"
-        else:
+        except N.SplitqError as e:  # e.g. a virtual-memory allocator, no peer access
+            if args.transfer == "ipc":
+                raise
+            print(f"[bench] rank {rank}: {e}; using NCCL", file=sys.stderr)
             ipc = None
 
     def step(timed_events=None):

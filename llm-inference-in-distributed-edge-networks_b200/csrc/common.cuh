@@ -26,6 +26,7 @@ int validate_ladder(int S, const int* k, const int* bits, int n);
     do {                                                                                   \
         cudaError_t e__ = (call);                                                          \
         if (e__ != cudaSuccess) {                                                          \
+            (void)cudaGetLastError(); /* reported here: do not leave it for the caller's next CUDA call */ \
             splitq::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
                               __LINE__);                                                   \
             return SPLITQ_ERR_CUDA;                                                        \

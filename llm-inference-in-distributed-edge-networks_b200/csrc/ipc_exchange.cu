@@ -45,6 +45,7 @@ extern "C" int splitq_ipc_export(const void* dev_ptr, void* handle_out, size_t* 
     SPLITQ_REQUIRE(r == CUDA_SUCCESS, SPLITQ_ERR_CUDA, "ipc_export: cuMemGetAddressRange failed (%d)", (int)r);
     cudaIpcMemHandle_t h;
     cudaError_t e = cudaIpcGetMemHandle(&h, (void*)base);
+    if (e != cudaSuccess) (void)cudaGetLastError();  // reported below; keep it out of the caller's next CUDA call
     SPLITQ_REQUIRE(e == cudaSuccess, SPLITQ_ERR_CUDA,
                    "ipc_export: cudaIpcGetMemHandle failed: %s (the buffer must come from cudaMalloc, not from a "
                    "virtual-memory allocator such as PyTorch's expandable segments)",
@@ -60,6 +61,7 @@ extern "C" int splitq_ipc_open(const void* handle, size_t offset, void** dev_ptr
     memcpy(&h, handle, sizeof(h));
     void* base = nullptr;
     cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) (void)cudaGetLastError();
     SPLITQ_REQUIRE(e == cudaSuccess, SPLITQ_ERR_CUDA, "ipc_open: cudaIpcOpenMemHandle failed: %s (a handle cannot be "
                    "opened by the process that exported it, and the two devices need peer access)",
                    cudaGetErrorString(e));

@@ -115,25 +115,42 @@ class IpcPairExchange:
         self.peer_flags = None
         self._opened = []
         lib = N.load()
-        exported = []
-        for t in [p.payload_src for p in self.plans] + [self.flags]:
-            handle = (C.c_ubyte * N.IPC_HANDLE_BYTES)()
-            off = C.c_size_t(0)
-            N.check(lib.splitq_ipc_export(C.c_void_p(t.data_ptr()), handle, C.byref(off)))
-            exported.append((bytes(handle), off.value))
-        torch.cuda.synchronize(self.dev)  # the zeroed flags are in memory before anyone maps them
+        # Every rank goes through the same two collectives whatever fails locally, and all ranks
+        # raise together: a rank that bailed out alone would leave its partner waiting.
+        err, exported = None, []
+        try:
+            for t in [p.payload_src for p in self.plans] + [self.flags]:
+                handle = (C.c_ubyte * N.IPC_HANDLE_BYTES)()
+                off = C.c_size_t(0)
+                N.check(lib.splitq_ipc_export(C.c_void_p(t.data_ptr()), handle, C.byref(off)))
+                exported.append((bytes(handle), off.value))
+            torch.cuda.synchronize(self.dev)  # the zeroed flags are in memory before anyone maps them
+        except Exception as e:  # noqa: BLE001
+            err = e
         everyone = [None] * self.world
-        dist.all_gather_object(everyone, exported, group=group)
-        if self.partner != self.rank:
-            ptrs = []
-            for handle, off in everyone[self.partner]:
-                out = C.c_void_p()
-                buf = (C.c_ubyte * N.IPC_HANDLE_BYTES).from_buffer_copy(handle)
-                N.check(lib.splitq_ipc_open(buf, C.c_size_t(off), C.byref(out)))
-                ptrs.append(out.value)
-                self._opened.append((out.value, off))
-            self.peer_payload, self.peer_flags = ptrs[:self.depth], ptrs[self.depth]
-        dist.barrier(group=group)  # nobody starts before every mapping exists
+        dist.all_gather_object(everyone, None if err else exported, group=group)
+        if err is None and self.partner != self.rank:
+            try:
+                if everyone[self.partner] is None:
+                    raise N.SplitqError(f"rank {self.partner} could not export its buffers")
+                ptrs = []
+                for handle, off in everyone[self.partner]:
+                    out = C.c_void_p()
+                    buf = (C.c_ubyte * N.IPC_HANDLE_BYTES).from_buffer_copy(handle)
+                    N.check(lib.splitq_ipc_open(buf, C.c_size_t(off), C.byref(out)))
+                    ptrs.append(out.value)
+                    self._opened.append((out.value, off))
+                self.peer_payload, self.peer_flags = ptrs[:self.depth], ptrs[self.depth]
+            except Exception as e:  # noqa: BLE001
+                err = e
+        status = [None] * self.world
+        dist.all_gather_object(status, None if err is None else f"rank {self.rank}: {err}", group=group)
+        failed = [m for m in status if m]
+        if failed:  # nobody starts unless every mapping exists
+            for ptr, off in self._opened:
+                lib.splitq_ipc_close(C.c_void_p(ptr), C.c_size_t(off))
+            self._opened = []
+            raise N.SplitqError("IPC exchange unavailable: " + "; ".join(failed))
 
     # -- hooks called by OverlappedBoundary ---------------------------------------------------
     def _stream(self):
