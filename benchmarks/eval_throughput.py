@@ -44,6 +44,7 @@ def main():
     ap.add_argument("--importance", default="fused", choices=["fused", "materialised"])
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--batch-methods", action="store_true", help="methods of one (layer, ratio) as one downstream batch")
+    ap.add_argument("--batch-combos", action="store_true", help="all (method, ratio > 0) variants of a layer as one batch")
     args = ap.parse_args()
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -61,7 +62,8 @@ def main():
     n_tokens = S + (args.windows - 1) * stride
     ids = torch.randint(0, cfg["vocab_size"], (1, n_tokens), generator=torch.Generator().manual_seed(1234))
     fn = evalloop.make_importance_fn(wrapper, params["methods"], args.importance, layers=params["layers_of_interest"])
-    kw = dict(reduce_device=dev if world > 1 else None, log=lambda *a: None, batch_methods=args.batch_methods)
+    kw = dict(reduce_device=dev if world > 1 else None, log=lambda *a: None, batch_methods=args.batch_methods,
+              batch_combos=args.batch_combos)
     evaluate = lambda: evaluate_once(params, wrapper, ids, fn, S, kw)  # noqa: E731
     evaluate()  # warm-up (cuBLAS heuristics, workspaces)
     torch.cuda.synchronize()
@@ -75,7 +77,7 @@ def main():
     dt = time.perf_counter() - t0
     combos = len(params["methods"]) * len(params["layers_of_interest"]) * len(params["ratios"])
     out = {"family": args.family, "n_gpus": world, "windows": res.windows, "S": S, "combos_per_window": combos,
-           "importance_impl": args.importance, "batch_methods": args.batch_methods, "seconds": dt, "window_tokens_per_s": res.windows * S / dt,
+           "importance_impl": args.importance, "batch_methods": args.batch_methods, "batch_combos": args.batch_combos, "seconds": dt, "window_tokens_per_s": res.windows * S / dt,
            "split_forward_tokens_per_s": res.windows * S * combos / dt, "ppl_no_quant": res.ppl[0][0][0]}
     if rank == 0 and not args.no_cpu:
         # the CPU port of the reference loop lives in oracle/ and is only ever executed by bench.py

@@ -67,7 +67,7 @@ class _Dist:
 
 def evaluate(params: dict, wrapper, input_ids: torch.Tensor, importance_fn: Callable, max_length: int,
              out_prefix: Optional[str] = None, checkpoint_every: int = 1000, reduce_device=None, group=None,
-             log: Callable = print, batch_methods: bool = False) -> EvalResult:
+             log: Callable = print, batch_methods: bool = False, batch_combos: bool = False) -> EvalResult:
     """Run the (method, layer, ratio) sweep over this rank's share of the windows.
 
     params         the reference's params.json dict: ratios, layers_of_interest, methods, stride
@@ -77,6 +77,9 @@ def evaluate(params: dict, wrapper, input_ids: torch.Tensor, importance_fn: Call
     importance_fn  (window_ids (1,S)) -> {method: [importance (S,) per layer]}
     batch_methods  push the M methods of one (layer, ratio) through the downstream half as one batch
                    (same arithmetic per row; cuBLAS may pick other kernels, so NLLs agree to ~1e-6)
+    batch_combos   push ALL (method, ratio > 0) variants of one split layer through the downstream half
+                   as one batch (the payloads of different ratios have different widths; they are
+                   dequantised one by one and their rows concatenated): M*(R-1) rows per forward
     out_prefix     if set, rank 0 writes <prefix>total_nll*.pkl / n_tokens*.pkl / avg_ppl_results*.pkl
     """
     ratios, lois, methods = params["ratios"], params["layers_of_interest"], params["methods"]
@@ -101,6 +104,23 @@ def evaluate(params: dict, wrapper, input_ids: torch.Tensor, importance_fn: Call
                 hidden = wrapper.upstream(ids, loi)  # once per split layer
                 shape = tuple(ids.shape)
                 base = None
+                if batch_combos and hidden.shape[0] == 1:
+                    hid_m = hidden.expand(M, -1, -1).contiguous()
+                    imp_m = torch.stack([imp[method][loi] for method in methods])
+                    pos_r = [r for r, ratio in enumerate(ratios) if ratio > 0]
+                    if pos_r:
+                        payloads = [wrapper.boundary_hop(wrapper.boundary_send(hid_m, imp_m, ratios[r])) for r in pos_r]
+                        rows = M * len(pos_r)
+                        nll = wrapper.downstream((rows, shape[1]), target.expand(rows, -1), loi, payload=payloads,
+                                                 per_sequence=True).view(len(pos_r), M)
+                        for j, r in enumerate(pos_r):
+                            nll_dev[:, l, r] = nll[j]
+                    if len(pos_r) < R:  # ratio 0 does not depend on the method
+                        base = wrapper.downstream(shape, target, loi, hidden=hidden)
+                        for r, ratio in enumerate(ratios):
+                            if not ratio > 0:
+                                nll_dev[:, l, r] = base
+                    continue
                 if batch_methods and M > 1 and hidden.shape[0] == 1:
                     # one downstream pass per ratio with the M methods as the batch
                     hid_m = hidden.expand(M, -1, -1).contiguous()

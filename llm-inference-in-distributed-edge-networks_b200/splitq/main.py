@@ -55,7 +55,9 @@ def run(family: str, params: dict, n_tokens: int, device: str, seed: int = 0, ti
     fn = make_importance_fn(wrapper, params["methods"], params.get("importance_impl", "fused"), head_w,
                             layers=params["layers_of_interest"])
     return evaluate(params, wrapper, ids, fn, max_length, out_prefix=out_prefix,
-                    reduce_device=wrapper.device if torch.distributed.is_initialized() else None, log=log)
+                    reduce_device=wrapper.device if torch.distributed.is_initialized() else None, log=log,
+                    batch_methods=bool(params.get("batch_methods", False)),
+                    batch_combos=bool(params.get("batch_combos", False)))
 
 
 def main() -> None:

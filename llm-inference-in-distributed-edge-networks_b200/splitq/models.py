@@ -171,7 +171,9 @@ class _LayerWiseModel:
 
     def downstream(self, ids_shape, target, layer_of_interest, payload=None, hidden=None, per_sequence=False):
         """Layers layer_of_interest+1.. + final norm + loss on the downstream device, starting
-        either from a payload (dequantise fused into the first norm) or from raw hidden states."""
+        either from a payload (dequantise fused into the first norm) or from raw hidden states.
+        `payload` may be a list of payloads of different widths (one per ratio); their rows are
+        dequantised separately and run through the layers as ONE batch of ids_shape[0] rows."""
         model = self._down
         dev = self.down_device
         B, S = ids_shape
@@ -179,10 +181,16 @@ class _LayerWiseModel:
         layers = compat.decoder_layers(model.base_model)
         ids_stub = torch.empty(B, S, dtype=torch.long, device=dev)
         nxt = layer_of_interest + 1
-        if payload is not None and self.fuse_norm:
+        payloads = None if payload is None else (list(payload) if isinstance(payload, (list, tuple)) else [payload])
+        cat = lambda ts: ts[0] if len(ts) == 1 else torch.cat(ts, dim=0)  # noqa: E731
+        if payloads is not None:
+            assert sum(p.shape[0] for p in payloads) == B, "ids_shape[0] must count the rows of all payloads"
+        if payloads is not None and self.fuse_norm:
             if nxt < self.num_layers:
                 kind, g1, b1, eps, g2, b2 = self._first_norm_params(layers[nxt])
-                resid, n1, n2 = boundary.dequant_norm(payload, S, D, kind, g1, b1, eps, g2, b2)
+                outs = [boundary.dequant_norm(p, S, D, kind, g1, b1, eps, g2, b2) for p in payloads]
+                resid, n1 = cat([o[0] for o in outs]), cat([o[1] for o in outs])
+                n2 = cat([o[2] for o in outs]) if outs[0][2] is not None else None
                 pos = self._positions(model, resid, ids_stub)
                 hidden = self._run_prenormed_layer(layers[nxt], resid, n1, n2, pos)
                 nxt += 1
@@ -190,11 +198,11 @@ class _LayerWiseModel:
                 fn = self._final_norm(model)
                 kind = N.NORM_LAYERNORM if isinstance(fn, torch.nn.LayerNorm) else N.NORM_RMSNORM
                 eps = fn.eps if kind == N.NORM_LAYERNORM else fn.variance_epsilon
-                _, post_norm, _ = boundary.dequant_norm(payload, S, D, kind, fn.weight, getattr(fn, "bias", None),
-                                                        eps, want_resid=False)
+                post_norm = cat([boundary.dequant_norm(p, S, D, kind, fn.weight, getattr(fn, "bias", None), eps,
+                                                       want_resid=False)[1] for p in payloads])
                 return self.last_portion(post_norm, target, model, per_sequence)
-        elif payload is not None:
-            hidden = boundary.dequant(payload, S, D)
+        elif payloads is not None:
+            hidden = cat([boundary.dequant(p, S, D) for p in payloads])
         else:
             hidden = hidden.to(dev)
         if nxt < self.num_layers:

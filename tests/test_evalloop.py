@@ -146,3 +146,28 @@ def test_batching_methods_through_downstream_changes_nothing():
     b = evalloop.evaluate(params, w, ids, fn, 128, log=lambda *x: None, batch_methods=True)
     assert a.n_tokens == b.n_tokens
     assert torch.allclose(torch.tensor(a.total_nll), torch.tensor(b.total_nll), rtol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("family", ["qwen", "pythia"])
+def test_batching_all_method_ratio_variants_changes_nothing(family):
+    """batch_combos: the payloads of different ratios (different widths) are dequantised one by one
+    and their rows run through the downstream half as one batch; NLLs equal the one-by-one loop,
+    including the split at the last layer (dequantise fused into the final norm)."""
+    from splitq import compat
+    from splitq.models import Pythia70Model, QwenPointFiveBModel
+    ratios = [0, 0.25, 0.75, 1]
+    if family == "qwen":
+        cfg = dict(compat.QWEN2_TINY, hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=256)
+        w = QwenPointFiveBModel.from_config("cuda:0", cfg=cfg, seed=0)
+    else:
+        cfg = dict(compat.PYTHIA_TINY, hidden_size=256, num_attention_heads=4, intermediate_size=256)
+        w = Pythia70Model.from_config("cuda:0", ratios, cfg=cfg, seed=0)
+    last = w.num_layers - 1
+    params = {"ratios": ratios, "layers_of_interest": [0, last], "methods": ["regular_importance", "last_row"], "stride": 32}
+    ids = torch.randint(0, 512, (1, 200), generator=torch.Generator().manual_seed(6))
+    fn = evalloop.make_importance_fn(w, params["methods"], "fused")
+    a = evalloop.evaluate(params, w, ids, fn, 128, log=lambda *x: None)
+    b = evalloop.evaluate(params, w, ids, fn, 128, log=lambda *x: None, batch_combos=True)
+    assert a.n_tokens == b.n_tokens
+    assert torch.allclose(torch.tensor(a.total_nll), torch.tensor(b.total_nll), rtol=1e-5)
