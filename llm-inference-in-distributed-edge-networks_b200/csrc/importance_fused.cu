@@ -484,17 +484,24 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             // ===== MMA issuer: A (fixed operand) from TMEM, B (streamed slab) from shared memory =====
             {
                 uint32_t stage = 0, sphase = 0, acc = 0, aphase = 0;
+                long long w_afull = 0, w_tempty = 0, w_full = 0, c_start = DBG ? clock64() : 0;  // DBG bit 3
                 SegIter<PASS> si;
                 si.init(p, 0);
                 Seg it;
                 for (int k = 0; si.next(it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
                     const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;
+                    const bool acct = DBG && (p.dbg & 8);
+                    long long c0 = acct ? clock64() : 0;
                     mbar_wait(bar_afull + 8 * ab, abphase);
+                    if (acct) w_afull += clock64() - c0;
                     tc_fence_after();
                     for (int t = it.ta; t < it.tb; ++t) {
+                        c0 = acct ? clock64() : 0;
                         mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
+                        const long long c1 = acct ? clock64() : 0;
                         mbar_wait(bar_full + 8 * stage, sphase);
+                        if (acct) { w_tempty += c1 - c0; w_full += clock64() - c1; }
                         tc_fence_after();
                         const uint32_t d = tmem_base + acc * kTile;
                         const uint32_t st0 = ring_s + stage * kOperandBytes;
@@ -525,6 +532,9 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     if (elect_one()) tc_commit(bar_aempty + 8 * ab);      // fixed-operand buffer reusable
                     __syncwarp();
                 }
+                if (DBG && (p.dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
+                    printf("K2 pass %d cta %d MMA warp: waited %lld cycles for the fixed operand, %lld for a free accumulator, "
+                           "%lld for streamed tiles, of %lld\n", PASS, blockIdx.x, w_afull, w_tempty, w_full, clock64() - c_start);
             }
         }
     } else if (wg == kEpiGroups + 1) {
