@@ -170,7 +170,10 @@ __device__ __forceinline__ float ex2_ordered(float x) {
     return y;
 }
 #endif
-constexpr int kExpBatch = 16;
+#ifndef SPLITQ_K2_EXP_BATCH
+#define SPLITQ_K2_EXP_BATCH 16
+#endif
+constexpr int kExpBatch = SPLITQ_K2_EXP_BATCH;
 // K-major, 128-byte swizzle, 8-row groups 1024 B apart (what a {64 fp16, 128 rows} TMA box writes)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
