@@ -452,7 +452,8 @@ def main() -> None:
             if args.workload == DEFAULT_WORKLOAD and B == cfg["B"]:  # the committed capture is of exactly this launch
                 traffic = captured_traffic("r1_a_ncu_full_summary.csv", "colsum_partial_kernel")
             roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                        "frac": achieved / peak, "frac_of_8tbs_spec": achieved / 8000.0, "traffic": traffic,
+                        "peak_source": peak_src,
                         "traffic_source": "profiles/r1_a_ncu_full_summary.csv (ncu --set full, dram read+write)" if traffic else None,
                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": score_ms}
             l2_note = f"inputs per step ({alg_bytes / 1e6:.0f} MB) exceed the 126 MB L2; no flush"
