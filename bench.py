@@ -472,7 +472,7 @@ def main() -> None:
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
                     "api": "splitq.HostPipeline.submit/drain (pinned host buffers, 3 streams, depth 2)"},
-            "gpu_launches": (plan.launches_per_run(fused) - (3 if fused and cfg["method"] == "last_row" else 0)) * args.steps,
+            "gpu_launches": (plan.launches_per_run(fused) - (4 if fused and cfg["method"] == "last_row" else 0)) * args.steps,
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
@@ -484,6 +484,9 @@ def main() -> None:
                 "sample": f"{len(times)} passes over 1 window of {S} tokens (same H, D, ladder; starts from "
                           f"{'Q,K' if fused else 'materialised attention'}), torch CPU fp32, "
                           f"mean {1e3 * statistics.mean(times):.1f} ms/window"}
+            one = cpu_reference_leg(cfg, ladder, fused, inputs, min(2.0, args.cpu_seconds), 1)
+            out["cpu_baseline"]["value_1_thread"] = S / statistics.mean(one)
+            torch.set_num_threads(threads)
         print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
