@@ -144,3 +144,24 @@ def test_fused_is_bit_reproducible_and_schedule_independent():
         # the split of an item between two CTAs moves, so the (max, sum) pairs are merged at other
         # points of the row: equal to fp32 rounding of the merge, not to the bit
         assert max_rel(col1[0], col0[b]) <= 2e-6 and max_rel(last1[0], last0[b]) <= 2e-6
+
+
+@pytest.mark.parametrize("B,H,KVH,S,causal", [(1, 2, 1, 8192, True), (3, 4, 4, 4096, True), (1, 2, 2, 3000, False)])
+def test_fused_long_windows_against_fp64_attention(B, H, KVH, S, causal):
+    """Long windows (many CTA ranges, items cut between CTAs, 64 blocks per row) against fp64 eager
+    attention computed on the GPU head by head."""
+    gen = torch.Generator(device=DEV).manual_seed(S + B)
+    q = torch.randn(B, H, S, 64, device=DEV, generator=gen)
+    k = torch.randn(B, KVH, S, 64, device=DEV, generator=gen)
+    want_col = torch.zeros(B, S, device=DEV, dtype=torch.float64)
+    want_last = torch.zeros(B, S, device=DEV, dtype=torch.float64)
+    mask = torch.full((S, S), float("-inf"), device=DEV, dtype=torch.float64).triu(1) if causal else 0.0
+    for b in range(B):
+        for h in range(H):
+            s = q[b, h].double() @ k[b, h // (H // KVH)].double().T * 0.125 + mask
+            A = torch.softmax(s, dim=-1)
+            want_col[b] += A.mean(dim=0) / H
+            want_last[b] += A[-1] / H
+    col, last = splitq.importance_fused(q, k, 0.125, causal=causal, want_last=True)
+    assert max_rel(col, want_col.float()) <= 1e-5
+    assert max_rel(last, want_last.float()) <= 1e-5
