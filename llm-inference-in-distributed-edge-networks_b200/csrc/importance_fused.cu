@@ -18,9 +18,10 @@
 // of the tensor time of one tf32 product plus two fp16 corrections, and with half the operand bytes.
 // Valid for |x| < 65504; beyond that fp16 overflows and the scores come out NaN (loudly wrong).
 // SPLITQ_FUSED_F16X1 keeps only h0*h0.  Four warpgroups per CTA: control (warp 0 = TMA producer of
-// the streamed operand, warp 1 = MMA issuer), two epilogue groups (alternate tiles, three TMEM
-// accumulators in rotation), and loaders that put the fixed operand of the next work item into
-// tensor memory, so the MMA reads A from TMEM and only B from shared memory.
+// the streamed operand, warps 1 and 2 = MMA issuers of alternate tiles), two epilogue groups
+// (alternate tiles, three TMEM accumulators in rotation), and loaders that put the fixed operand
+// of the next work item into tensor memory, so the MMA reads A from TMEM and only B from shared
+// memory.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <math.h>
@@ -47,6 +48,11 @@ constexpr int kChunks = kTile / kChunk;
 constexpr int kEpiRegs = kEpiGroups == 2 ? 200 : 128; // setmaxnreg budgets; they add up to the launch-time pool
 constexpr int kCtlRegs = kEpiGroups == 2 ? 56 : 40;
 constexpr int kLdrRegs = 56;
+#ifndef SPLITQ_K2_MMA_WARPS
+#define SPLITQ_K2_MMA_WARPS 2
+#endif
+constexpr int kMmaWarps = SPLITQ_K2_MMA_WARPS;        // warps 1.. of the control group issue the MMAs of alternate tiles
+static_assert(kMmaWarps == 1 || kMmaWarps == 2, "1 or 2 MMA-issuing warps");
 constexpr int kThreads = 128 * (kEpiGroups + 2);      // warpgroups: control, epilogue x kEpiGroups, operand loaders
 static_assert(kEpiGroups == 2 || kEpiGroups == 3, "2 or 3 epilogue groups");
 static_assert(128 * (kCtlRegs + kLdrRegs + kEpiGroups * kEpiRegs) <= kThreads * (65536 / kThreads / 8 * 8),
@@ -419,7 +425,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     const uint32_t bar_afull = bar0, bar_aempty = bar0 + 16;          // fixed operand in TMEM, 2 buffers
     const uint32_t bar_full = bar0 + 32, bar_empty = bar_full + 8 * kStages;
     const uint32_t bar_tfull = bar_empty + 8 * kStages, bar_tempty = bar_tfull + 8 * kAcc;
-    static_assert(32 + 16 * kStages + 16 * kAcc <= 504, "barrier region overflow");
+    const uint32_t bar_turn = bar_tempty + 8 * kAcc;                   // two MMA warps: "passed the waits of my tile"
+    static_assert(32 + 16 * kStages + 16 * kAcc + 16 <= 504, "barrier region overflow");
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen + kBarOff + 504);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -427,12 +434,13 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     if (threadIdx.x == 0) {
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_afull + 8 * a, 4);   // one arrive per loader warp
-            mbar_init(bar_aempty + 8 * a, 1);  // tcgen05.commit of the item's last MMA
+            mbar_init(bar_aempty + 8 * a, kMmaWarps);  // tcgen05.commit after each issuing warp's last MMA of the item
         }
         for (int s = 0; s < kStages; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
         }
+        for (int w = 0; w < 2; ++w) mbar_init(bar_turn + 8 * w, 1);
         for (int a = 0; a < kAcc; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
             mbar_init(bar_tempty + 8 * a, 4);  // one arrive per warp of the epilogue group that drained it
@@ -483,9 +491,13 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     }
                 }
             }
-        } else if (warp == 1) {
-            // ===== MMA issuer: A (fixed operand) from TMEM, B (streamed slab) from shared memory =====
+        } else if (warp <= kMmaWarps) {
+            // ===== MMA issuer(s): A (fixed operand) from TMEM, B (streamed slab) from shared memory.
+            // With two issuing warps each takes every other tile: `tcgen05.mma` blocks while the
+            // pipe's queue is full, so one warp's barrier waits run under the other's MMAs =====
             {
+                const uint32_t mi = (uint32_t)warp - 1u;
+                uint32_t n_tile = 0;
                 uint32_t stage = 0, sphase = 0, acc = 0, aphase = 0;
                 long long w_afull = 0, w_tempty = 0, w_full = 0, c_start = DBG ? clock64() : 0;  // DBG bit 3
                 SegIter<PASS> si;
@@ -499,12 +511,27 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     mbar_wait(bar_afull + 8 * ab, abphase);
                     if (acct) w_afull += clock64() - c0;
                     tc_fence_after();
-                    for (int t = it.ta; t < it.tb; ++t) {
+                    for (int t = it.ta; t < it.tb; ++t, ++n_tile) {
+                        if (kMmaWarps > 1 && (n_tile & 1u) != mi) {  // the other warp's tile
+                            if (++stage == kStages) { stage = 0; sphase ^= 1; }
+                            if (++acc == kAcc) { acc = 0; aphase ^= 1; }
+                            continue;
+                        }
+                        if (kMmaWarps > 1 && n_tile > 0) {
+                            // The other warp must be past the waits of tile n - 1 first: parity waits are only
+                            // sound one phase apart, so the two warps may not drift by more than a tile.
+                            const uint32_t k_other = mi ? (n_tile >> 1) : (n_tile >> 1) - 1u;
+                            mbar_wait(bar_turn + 8 * (mi ^ 1u), k_other & 1u);
+                        }
                         c0 = acct ? clock64() : 0;
                         mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
                         const long long c1 = acct ? clock64() : 0;
                         mbar_wait(bar_full + 8 * stage, sphase);
                         if (acct) { w_tempty += c1 - c0; w_full += clock64() - c1; }
+                        if (kMmaWarps > 1) {
+                            if (elect_one()) mbar_arrive(bar_turn + 8 * mi);
+                            __syncwarp();
+                        }
                         tc_fence_after();
                         const uint32_t d = tmem_base + acc * kTile;
                         const uint32_t st0 = ring_s + stage * kOperandBytes;
