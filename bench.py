@@ -271,6 +271,8 @@ def main() -> None:
                     help="payload hop between paired ranks in the device-resident loop: NCCL send/recv, or a "
                          "copy-engine pull over CUDA IPC ordered by stream memory operations (auto = ipc, "
                          "falling back to nccl if the mapping cannot be set up)")
+    ap.add_argument("--pack-on-main", action="store_true",
+                    help="keep select + quantise/pack on the scoring stream (default: on the side stream with hop + dequantise)")
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
@@ -327,7 +329,7 @@ def main() -> None:
         return pl
 
     # software pipeline over steps: hop + dequantise of step i on a side stream under the scoring of i+1
-    ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused)
+    ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused, pack_on_side=not args.pack_on_main)
     dev_inputs = (q, k, h) if fused else (A, h)
     ipc, transfer_name = None, "nccl pair exchange" if world > 1 else "device-to-device copy"
     if world > 1 and args.transfer in ("auto", "ipc"):
@@ -467,7 +469,8 @@ def main() -> None:
                        "importance_impl": args.importance + (f" ({args.fused_mode})" if fused else ""),
                        "payload_bytes_per_window": plan.nbytes,
                        "transfer": transfer_name, "l2": l2_note,
-                       "pipelining": "hop + dequantise of step i on a side stream, overlapping the scoring of step i+1"},
+                       "pipelining": ("hop + dequantise" if args.pack_on_main else "select + quantise/pack + hop + dequantise") +
+                                     " of step i on a side stream, overlapping the scoring of step i+1"},
             "roofline": roofline,
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,

@@ -447,23 +447,35 @@ class HostPipeline:
 
 
 class OverlappedBoundary:
-    """Device-resident variant of the same software pipeline: scoring + select + quantise/pack of
-    step i+1 run on the main stream while the payload hop (peer copy or NCCL pair exchange) and the
-    dequantise of step i run on a side stream; `depth` payload/output buffer sets alternate."""
+    """Device-resident variant of the same software pipeline: the scoring of step i+1 runs on the
+    main stream while select + quantise/pack, the payload hop (peer copy, IPC pull or NCCL pair
+    exchange) and the dequantise of step i run on a side stream; `depth` buffer sets alternate.
+    With `pack_on_side=False` select + quantise/pack stay on the main stream behind the scoring
+    (they then delay the next step's scoring by their ~50 us instead of running beside its
+    memory-bound operand split)."""
 
-    def __init__(self, make_plan, depth: int = 2, fused: bool = True):
+    def __init__(self, make_plan, depth: int = 2, fused: bool = True, pack_on_side: bool = True):
         self.plans = [make_plan() for _ in range(depth)]
         self.fused = fused
+        self.pack_on_side = pack_on_side
         self.main = torch.cuda.current_stream(self.plans[0].src)
         self.side = torch.cuda.Stream(self.plans[0].src)
         self.slot = 0
         for p in self.plans:
             p._xfer_done = None
 
+    def _pack(self, p, h) -> None:
+        tr = p.transport
+        if hasattr(tr, "before_pack"):  # transport.IpcPairExchange: the partner has fetched this slot's last payload
+            tr.before_pack(p)
+        p.send(h)
+        if hasattr(tr, "after_pack"):   # ... and may fetch the new one
+            tr.after_pack(p)
+
     def step(self, *inputs: torch.Tensor, score_events=None) -> "BoundaryPlan":
         p = self.plans[self.slot]
         self.slot = (self.slot + 1) % len(self.plans)
-        if p._xfer_done is not None:  # this slot's payload and output buffers are free again
+        if p._xfer_done is not None:  # this slot's importance, payload and output buffers are free again
             self.main.wait_event(p._xfer_done)
         if score_events is not None:
             score_events[0].record(self.main)
@@ -473,16 +485,14 @@ class OverlappedBoundary:
             p.score(inputs[0])
         if score_events is not None:
             score_events[1].record(self.main)
-        tr = p.transport
-        if hasattr(tr, "before_pack"):  # transport.IpcPairExchange: the partner has fetched this slot's last payload
-            tr.before_pack(p)
-        p.send(inputs[-1])
-        if hasattr(tr, "after_pack"):   # ... and may fetch the new one
-            tr.after_pack(p)
-        packed = torch.cuda.Event()
-        packed.record(self.main)
+        if not self.pack_on_side:
+            self._pack(p, inputs[-1])
+        handoff = torch.cuda.Event()
+        handoff.record(self.main)
         with torch.cuda.stream(self.side):
-            self.side.wait_event(packed)
+            self.side.wait_event(handoff)
+            if self.pack_on_side:
+                self._pack(p, inputs[-1])
             p.hop()
             p.receive()
             p._xfer_done = torch.cuda.Event()
