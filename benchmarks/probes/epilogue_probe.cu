@@ -73,11 +73,33 @@ __device__ __forceinline__ void pass2_chunk(const float (&v)[NC], uint32_t ls, f
 }
 
 // GAP = number of dependent integer instructions between two chunks (stand-in for bookkeeping)
+// Threads 256.. (if launched) do what the kernel's producer / MMA / loader warps do most of the time:
+// spin on an mbarrier that does not complete, until the exp2 warps are done.
 template <int PASS, int GAP>
-__global__ void __launch_bounds__(256, 1) probe(float* out, long long* clk, int iters, float cs) {
+__global__ void __launch_bounds__(512, 1) probe(float* out, long long* clk, int iters, float cs, int hint_ns) {
     __shared__ __align__(16) float lse[128];
+    __shared__ __align__(8) unsigned long long bar;
+    __shared__ volatile int done_flag;
     if (threadIdx.x < 128) lse[threadIdx.x] = 3.f + threadIdx.x * 1e-3f;
+    if (threadIdx.x == 0) {
+        done_flag = 0;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&bar)));
+    }
     __syncthreads();
+    if (threadIdx.x >= 256) {
+        const uint32_t b = (uint32_t)__cvta_generic_to_shared(&bar);
+        while (!done_flag) {
+            uint32_t ok;
+            if (hint_ns > 0)
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(ok) : "r"(b), "r"(0u), "r"((uint32_t)hint_ns) : "memory");
+            else
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(ok) : "r"(b), "r"(0u) : "memory");
+            if (ok) break;
+        }
+        return;
+    }
     const uint32_t ls = (uint32_t)__cvta_generic_to_shared(lse);
     float va[64], vb[64];
 #pragma unroll
@@ -96,22 +118,23 @@ __global__ void __launch_bounds__(256, 1) probe(float* out, long long* clk, int 
         vb[x & 63 ? 0 : 1] += 1e-6f;
     }
     const long long t1 = clock64();
-    out[blockIdx.x * blockDim.x + threadIdx.x] = m + l + colsum + (float)x;
+    out[blockIdx.x * 256 + threadIdx.x] = m + l + colsum + (float)x;
+    done_flag = 1;
     if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
 }
 
 template <int PASS, int GAP>
-static void run(float* out, long long* clk) {
+static void run(float* out, long long* clk, int spinners = 0, int hint_ns = 0) {
     const int iters = 1000;
-    for (int rep = 0; rep < 2; ++rep) probe<PASS, GAP><<<148, 256>>>(out, clk, iters, 0.18f);
+    for (int rep = 0; rep < 2; ++rep) probe<PASS, GAP><<<148, 256 + 32 * spinners>>>(out, clk, iters, 0.18f, hint_ns);
     cudaDeviceSynchronize();
     long long h[148];
     cudaMemcpy(h, clk, sizeof(h), cudaMemcpyDeviceToHost);
     double c = 0;
     for (int i = 0; i < 148; ++i) c += (double)h[i];
     c /= 148;
-    printf("pass %d, %3d dependent instructions between chunks: %.2f clk per warp-level EX2 per sub-partition\n", PASS, GAP,
-           c / (iters * 128.0 * 2));
+    printf("pass %d, %3d dependent instructions between chunks, %d spinning warps (hint %d ns): %.2f clk per warp-level EX2 per "
+           "sub-partition\n", PASS, GAP, spinners, hint_ns, c / (iters * 128.0 * 2));
 }
 
 int main() {
@@ -125,6 +148,10 @@ int main() {
     run<2, 0>(out, clk);
     run<2, 32>(out, clk);
     run<2, 128>(out, clk);
+    run<1, 32>(out, clk, 8, 0);
+    run<2, 32>(out, clk, 8, 0);
+    run<1, 32>(out, clk, 8, 100000);
+    run<2, 32>(out, clk, 8, 100000);
     printf("%s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;
 }
