@@ -76,7 +76,13 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// Protocol guard: a wait that does not complete within ~2 s traps instead of hanging the GPU.  The
+// debug instantiation of the kernel (any timing-experiment bit set in `mode`) also says which
+// barrier; the production kernel only traps, because a dozen inlined printf call sequences cost
+// ~10 % of a code size that sits at the edge of the instruction cache, and force registers that are
+// live across the call (the loaders' prefetched operand row) through local memory.
+template <bool VERBOSE>
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
     const long long t0 = clock64();
     while (true) {
@@ -88,30 +94,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             : "r"(bar), "r"(parity)
             : "memory");
         if (done) return;
-        if (clock64() - t0 > 4000000000LL) {  // ~2 s: a protocol bug must fault, not hang the GPU
-            printf("splitq K2: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x,
-                   threadIdx.x, bar, parity);
+        if (clock64() - t0 > 4000000000LL) {
+            if (VERBOSE)
+                printf("splitq K2: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x,
+                       bar, parity);
             __trap();
         }
-    }
-}
-// 4-D box {64 fp16, 128 rows, 1, parts}: a whole streamed tile (h0 and h1 parts) in ONE transaction,
-// landing as [part][128 rows][128 B] = two swizzle-128B slabs
-// same protocol guard without the printf: a call in the wait loop would force every register that is
-// live across it (the loaders' prefetched operand row) through local memory
-__device__ __forceinline__ void mbar_wait_quiet(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    const long long t0 = clock64();
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(bar), "r"(parity)
-            : "memory");
-        if (done) return;
-        if (clock64() - t0 > 4000000000LL) __trap();
     }
 }
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
@@ -481,7 +469,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     for (int t = it.ta; t < it.tb; ++t) {
                         const uint32_t fb = bar_full + 8 * stage;
                         const uint32_t dst = ring_s + stage * kOperandBytes;
-                        mbar_wait(bar_empty + 8 * stage, sphase ^ 1);
+                        mbar_wait_t<DBG>(bar_empty + 8 * stage, sphase ^ 1);
                         if (elect_one()) {
                             mbar_expect_tx(fb, tile_tx);
                             tma_load_4d(dst, str_map, fb, 0, t * kTile, str_idx, 0);
@@ -508,7 +496,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;
                     const bool acct = DBG && (p.dbg & 8);
                     long long c0 = acct ? clock64() : 0;
-                    mbar_wait(bar_afull + 8 * ab, abphase);
+                    mbar_wait_t<DBG>(bar_afull + 8 * ab, abphase);
                     if (acct) w_afull += clock64() - c0;
                     tc_fence_after();
                     for (int t = it.ta; t < it.tb; ++t, ++n_tile) {
@@ -521,12 +509,12 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                             // The other warp must be past the waits of tile n - 1 first: parity waits are only
                             // sound one phase apart, so the two warps may not drift by more than a tile.
                             const uint32_t k_other = mi ? (n_tile >> 1) : (n_tile >> 1) - 1u;
-                            mbar_wait(bar_turn + 8 * (mi ^ 1u), k_other & 1u);
+                            mbar_wait_t<DBG>(bar_turn + 8 * (mi ^ 1u), k_other & 1u);
                         }
                         c0 = acct ? clock64() : 0;
-                        mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
+                        mbar_wait_t<DBG>(bar_tempty + 8 * acc, aphase ^ 1);
                         const long long c1 = acct ? clock64() : 0;
-                        mbar_wait(bar_full + 8 * stage, sphase);
+                        mbar_wait_t<DBG>(bar_full + 8 * stage, sphase);
                         if (acct) { w_tempty += c1 - c0; w_full += clock64() - c1; }
                         if (kMmaWarps > 1) {
                             if (elect_one()) mbar_arrive(bar_turn + 8 * mi);
@@ -587,7 +575,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             uint4 q[8];  // this row: 64 halfs = 128 B = 32 TMEM columns per part; h0 is fetched ahead of the wait
 #pragma unroll
             for (int i = 0; i < 8; ++i) q[i] = (g < p.S && !(DBG && (p.dbg & 16))) ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
-            mbar_wait_quiet(bar_aempty + 8 * ab, abphase ^ 1);
+            mbar_wait_t<false>(bar_aempty + 8 * ab, abphase ^ 1);
             tc_fence_after();
             const uint32_t a0 = tmem_base + kTmemA + ab * kTmemABuf + lane_addr;
             tc_st32(a0, q);
@@ -662,7 +650,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 sts128(lse_w + 16u * lane, load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec));
                 __syncwarp();
             }
-            mbar_wait(bar_tfull + 8 * acc_i, acc_ph);
+            mbar_wait_t<DBG>(bar_tfull + 8 * acc_i, acc_ph);
             tc_fence_after();
             if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + acc_i * kTile, va);
             tc_ld_wait();
@@ -736,7 +724,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     }
                 } else if (has_next) {
                     if (!ready) {
-                        mbar_wait(bar_tfull + 8 * na, nph);
+                        mbar_wait_t<DBG>(bar_tfull + 8 * na, nph);
                         tc_fence_after();
                         if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
                     }
