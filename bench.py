@@ -271,6 +271,9 @@ def main() -> None:
                     help="payload hop between paired ranks in the device-resident loop: NCCL send/recv, or a "
                          "copy-engine pull over CUDA IPC ordered by stream memory operations (auto = ipc, "
                          "falling back to nccl if the mapping cannot be set up)")
+    ap.add_argument("--main-priority", type=int, default=-3,
+                    help="CUDA priority of the scoring stream (negative = above the side stream's default 0: the "
+                         "persistent scoring kernels then get SMs ahead of queued pack / dequantise CTAs)")
     ap.add_argument("--pack-on-main", action="store_true",
                     help="keep select + quantise/pack on the scoring stream (default: on the side stream with hop + dequantise)")
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
@@ -329,7 +332,8 @@ def main() -> None:
         return pl
 
     # software pipeline over steps: hop + dequantise of step i on a side stream under the scoring of i+1
-    ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused, pack_on_side=not args.pack_on_main)
+    ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused, pack_on_side=not args.pack_on_main,
+                                   main_priority=args.main_priority)
     dev_inputs = (q, k, h) if fused else (A, h)
     ipc, transfer_name = None, "nccl pair exchange" if world > 1 else "device-to-device copy"
     if world > 1 and args.transfer in ("auto", "ipc"):
@@ -362,7 +366,7 @@ def main() -> None:
     t0.record()
     for i in range(args.steps):
         step(k_events[i])
-    ob.main.wait_stream(ob.side)  # the clock stops when the last step's dequantise has finished
+    ob.join()  # the clock stops when the last step's dequantise has finished
     t1.record()
     torch.cuda.synchronize()
     if dist is not None:

@@ -454,12 +454,19 @@ class OverlappedBoundary:
     (they then delay the next step's scoring by their ~50 us instead of running beside its
     memory-bound operand split)."""
 
-    def __init__(self, make_plan, depth: int = 2, fused: bool = True, pack_on_side: bool = True):
+    def __init__(self, make_plan, depth: int = 2, fused: bool = True, pack_on_side: bool = True,
+                 side_priority: int = 0, main_priority=None):
+        """main_priority: None = score on the caller's current stream; an int = score on a stream of
+        that CUDA priority (-1 and below: higher than default), which lets the block scheduler place
+        the scoring kernels' CTAs ahead of the side stream's whenever an SM frees up.  The caller's
+        current stream is joined at every step and can be re-joined with `join()`."""
         self.plans = [make_plan() for _ in range(depth)]
         self.fused = fused
         self.pack_on_side = pack_on_side
-        self.main = torch.cuda.current_stream(self.plans[0].src)
-        self.side = torch.cuda.Stream(self.plans[0].src)
+        dev = self.plans[0].src
+        self.caller = torch.cuda.current_stream(dev)
+        self.main = self.caller if main_priority is None else torch.cuda.Stream(dev, priority=main_priority)
+        self.side = torch.cuda.Stream(dev, priority=side_priority)
         self.slot = 0
         for p in self.plans:
             p._xfer_done = None
@@ -475,18 +482,21 @@ class OverlappedBoundary:
     def step(self, *inputs: torch.Tensor, score_events=None) -> "BoundaryPlan":
         p = self.plans[self.slot]
         self.slot = (self.slot + 1) % len(self.plans)
+        if self.main is not self.caller:  # inputs were produced on the caller's stream
+            self.main.wait_stream(self.caller)
         if p._xfer_done is not None:  # this slot's importance, payload and output buffers are free again
             self.main.wait_event(p._xfer_done)
         if score_events is not None:
             score_events[0].record(self.main)
-        if self.fused:
-            p.score_fused(inputs[0], inputs[1])
-        else:
-            p.score(inputs[0])
-        if score_events is not None:
-            score_events[1].record(self.main)
-        if not self.pack_on_side:
-            self._pack(p, inputs[-1])
+        with torch.cuda.stream(self.main):
+            if self.fused:
+                p.score_fused(inputs[0], inputs[1])
+            else:
+                p.score(inputs[0])
+            if score_events is not None:
+                score_events[1].record(self.main)
+            if not self.pack_on_side:
+                self._pack(p, inputs[-1])
         handoff = torch.cuda.Event()
         handoff.record(self.main)
         with torch.cuda.stream(self.side):
@@ -498,6 +508,12 @@ class OverlappedBoundary:
             p._xfer_done = torch.cuda.Event()
             p._xfer_done.record(self.side)
         return p
+
+    def join(self) -> None:
+        """Make the caller's stream wait for everything submitted so far (no host sync)."""
+        self.main.wait_stream(self.side)
+        if self.main is not self.caller:
+            self.caller.wait_stream(self.main)
 
     def drain(self) -> None:
         self.side.synchronize()
