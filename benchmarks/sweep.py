@@ -31,7 +31,9 @@ SHAPES = [("pythia-70m", 512, 8, 8), ("qwen2-0.5b", 896, 14, 2)]
 FRACS = [(0.25, 2), (0.25, 4), (0.25, 8)]
 
 
-def timeit(fn, iters):
+def timeit(fn, iters, inner=1):
+    """Median over `iters` event pairs of the time per call; `inner` back-to-back calls per pair for
+    kernels so short (tens of microseconds) that the event pair and the launch gap would dominate."""
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
@@ -39,10 +41,11 @@ def timeit(fn, iters):
     for _ in range(iters):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        fn()
+        for _ in range(inner):
+            fn()
         b.record()
         torch.cuda.synchronize()
-        times.append(a.elapsed_time(b))
+        times.append(a.elapsed_time(b) / inner)
     return statistics.median(times)
 
 
@@ -77,8 +80,8 @@ def main():
             roff = torch.empty(Bf, S, dtype=torch.int32, device=dev)
             payload = torch.empty(Bf, nbytes, dtype=torch.uint8, device=dev)
             t_k2 = timeit(lambda: splitq.importance_fused(q, k, 0.125, out_col=imp), args.iters)
-            t_sel = timeit(lambda: splitq.select_bits(imp, ladder, D, bits, roff), args.iters)
-            t_qp = timeit(lambda: splitq.quant_pack(h, bits, roff, N.SCALE_TOKEN, nbytes, payload), args.iters)
+            t_sel = timeit(lambda: splitq.select_bits(imp, ladder, D, bits, roff), args.iters, inner=8)
+            t_qp = timeit(lambda: splitq.quant_pack(h, bits, roff, N.SCALE_TOKEN, nbytes, payload), args.iters, inner=8)
             nb = (S + 127) // 128
             issued = Bf * H * nb * (nb + 1) * 2.0 * 128 * 128 * 64 * 3
             qp_bytes = Bf * (4 * S * D + 5 * S + nbytes)
@@ -131,9 +134,9 @@ def write_md(path, results, hbm, bf16, iters):
         lines.append("| %s | %d | %s | B=%d, %.3f, %.1f, %.0f, %.2f | %.3f | %.0f (%.2f) |" % (
             r["model_shape"], r["S"], k1, f["B"], f["k2_ms"], f["tokens_per_s"] / 1e6, f["issued_f16_tflops"],
             f["frac_of_f16_peak"], r["select_ms"], q["GBps"], q["frac_of_hbm_peak"]))
-    lines += ["", "Single-call CUDA-event timings include ~5-8 us of launch gap per kernel, which is why the small kernels "
-              "(select, quant+pack) read lower here than in the ncu launch list of the bench (quant+pack 31 us for 160 MB = 5.2 TB/s), "
-              "and K2's six launches weigh on the small-S points."]
+    lines += ["", "CUDA-event timings.  select and quant+pack (tens of microseconds) are timed as 8 back-to-back calls per "
+              "event pair; the inputs of a point (>= 256 MB) exceed the L2, so repeated calls still stream from HBM.  "
+              "K2's six launches per call weigh on the small-S points."]
     with open(path, "w") as fh:
         fh.write("\n".join(lines) + "\n")
 
