@@ -452,7 +452,8 @@ class OverlappedBoundary:
     exchange) and the dequantise of step i run on a side stream; `depth` buffer sets alternate.
     With `pack_on_side=False` select + quantise/pack stay on the main stream behind the scoring
     (they then delay the next step's scoring by their ~50 us instead of running beside its
-    memory-bound operand split)."""
+    memory-bound operand split).  The input tensors of a step are read on both streams: keep them
+    alive and unmodified until `join()` / `drain()` or until the same slot comes round again."""
 
     def __init__(self, make_plan, depth: int = 2, fused: bool = True, pack_on_side: bool = True,
                  side_priority: int = 0, main_priority=None):
