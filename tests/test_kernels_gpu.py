@@ -353,15 +353,17 @@ def test_pipelined_front_ends_give_the_same_bytes_as_the_plain_plan():
     for q, k, h in steps:
         r = ref_plan.run_fused(q, k, h)
         want.append((r.payload.clone(), r.hidden.clone()))
-    ob = splitq.OverlappedBoundary(mk, depth=2, fused=True)
-    got = []
-    for q, k, h in steps:
-        p = ob.step(q, k, h)
-        ob.side.synchronize()
-        got.append((p.payload_dst.clone(), p.h_out.clone()))
-    ob.drain()
-    for (wp, wh), (gp, gh) in zip(want, got):
-        assert torch.equal(wp, gp) and torch.equal(wh, gh)
+    for kw in ({}, {"pack_on_side": False}, {"main_priority": -1}, {"main_priority": -2, "pack_on_side": False}):
+        ob = splitq.OverlappedBoundary(mk, depth=2, fused=True, **kw)
+        got = []
+        for q, k, h in steps:
+            p = ob.step(q, k, h)
+            ob.side.synchronize()
+            got.append((p.payload_dst.clone(), p.h_out.clone()))
+        ob.join()
+        ob.drain()
+        for (wp, wh), (gp, gh) in zip(want, got):
+            assert torch.equal(wp, gp) and torch.equal(wh, gh), kw
     pipe = splitq.HostPipeline(mk, depth=2, fused=True)
     outs = [torch.empty(B, S, D, pin_memory=True) for _ in steps]
     for (q, k, h), o in zip(steps, outs):
