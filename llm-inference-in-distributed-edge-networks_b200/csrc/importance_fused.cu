@@ -643,6 +643,10 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
         uint32_t lb = 0;                            // lse buffer of the current tile
         long long clk_math = 0, clk_loop = DBG ? clock64() : 0;
+        long long clk_seg[1 + 2 * kChunks] = {};    // DBG bit 3: loop head, then per chunk: before / after its body
+        long long clk_late = 0, clk_ldw = 0;
+        int n_late = 0;
+        const bool acct = DBG && (p.dbg & 8);
         uint32_t acc_i = (uint32_t)grp % kAcc, acc_ph = 0;  // accumulator (gn % kAcc) and barrier phase of the current tile
         bool have = nx.valid();
         if (have) {
@@ -656,6 +660,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             tc_ld_wait();
         }
         while (have) {
+            long long tseg = acct ? clock64() : 0;
             // ---- the tile being processed: number gn = (bh, blk, t), where nx stands before it moves on
             const int bh = nx.bh, blk = nx.blk, t = nx.t;
             const uint32_t a = acc_i;
@@ -688,6 +693,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const bool edge1 = diag || s_hi < kTile - 1;
             float lastv = 0.f;
             if (has_last && !(dbg & 4)) tc_ld1_issue(cur_tmem + (uint32_t)last_col, lastv);  // lands with the next wait
+            if (acct) { const long long now = clock64(); clk_seg[0] += now - tseg; tseg = now; }
 #pragma unroll
             for (int c = 0; c < kChunks; ++c) {
                 float (&cur)[kChunk] = (c & 1) ? vb : va;
@@ -704,6 +710,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     }
                 }
                 const long long tm0 = (DBG && (dbg & 8)) ? clock64() : 0;
+                if (acct) clk_seg[1 + 2 * c] += tm0 - tseg;
                 if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
                 else if (PASS == 1) {
                     if (edge1) pass1_body<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
@@ -712,7 +719,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
                     else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
                 }
-                if (DBG && (dbg & 8)) clk_math += clock64() - tm0;
+                if (acct) { tseg = clock64(); clk_math += tseg - tm0; }
                 if (c + 1 < kChunks) {
                     tc_ld_wait();
                     if (c == 0 && has_last)           // p[S-1][key]: the last query is never masked
@@ -724,24 +731,34 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     }
                 } else if (has_next) {
                     if (!ready) {
+                        const long long w0 = acct ? clock64() : 0;
                         mbar_wait_t<DBG>(bar_tfull + 8 * na, nph);
+                        if (acct) { clk_late += clock64() - w0; ++n_late; }
                         tc_fence_after();
                         if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
                     }
+                    const long long w1 = acct ? clock64() : 0;
                     tc_ld_wait();                     // next tile's first chunk landed
+                    if (acct) clk_ldw += clock64() - w1;
                     __syncwarp();                     // the lse values staged by the other lanes are visible
                     lb ^= 1u;
                     gn += kEpiGroups;
                     acc_i = na;
                     acc_ph = nph;
                 }
+                if (acct) { const long long now = clock64(); clk_seg[2 + 2 * c] += now - tseg; tseg = now; }
             }
             have = has_next;
         }
         flush();
         if (DBG && (dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))  // bit 3: cycle accounting
-            printf("K2 pass %d cta %d warp %d: %lld cycles in the math bodies of %lld in the tile loop, %d tiles\n", PASS,
-                   blockIdx.x, warp, clk_math, clock64() - clk_loop, (int)(gn / kEpiGroups));
+            printf("K2 pass %d cta %d warp %d: %lld cycles in the math bodies of %lld in the tile loop, %d tiles; loop head %lld, "
+                   "before/after body 0: %lld / %lld, before/after the last body: %lld / %lld\n", PASS, blockIdx.x, warp, clk_math,
+                   clock64() - clk_loop, (int)(gn / kEpiGroups), clk_seg[0], clk_seg[1], clk_seg[2], clk_seg[2 * kChunks - 1],
+                   clk_seg[2 * kChunks]);
+        if (DBG && (dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
+            printf("K2 pass %d cta %d warp %d: next accumulator not ready after the last body %d times (%lld cycles waited), "
+                   "%lld cycles in the wait for its first TMEM load\n", PASS, blockIdx.x, warp, n_late, clk_late, clk_ldw);
     }
 
     tc_fence_before();
