@@ -38,7 +38,14 @@ constexpr int kHd = 64;
 constexpr uint32_t kPartBytes = 128 * 128;           // 128 rows x 64 fp16: one swizzle-128B slab (h0 or h1 part)
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // h0 + h1
 constexpr int kStages = 4;                           // streamed tiles in flight; one barrier pair and one TMA issue per tile
-constexpr int kAcc = 3;                              // TMEM accumulator buffers, used in rotation
+// SPLITQ_K2_A_SMEM = 1: the fixed operand stays in shared memory (SS-mode MMA, brought in by TMA like
+// the streamed one) instead of tensor memory; the 128 TMEM columns this frees hold a FOURTH
+// accumulator, and the loader warps have nothing to do.
+#ifndef SPLITQ_K2_A_SMEM
+#define SPLITQ_K2_A_SMEM 0
+#endif
+constexpr bool kASmem = SPLITQ_K2_A_SMEM != 0;
+constexpr int kAcc = kASmem ? 4 : 3;                 // TMEM accumulator buffers, used in rotation
 #ifndef SPLITQ_K2_EPI_GROUPS
 #define SPLITQ_K2_EPI_GROUPS 2
 #endif
@@ -57,10 +64,11 @@ constexpr int kThreads = 128 * (kEpiGroups + 2);      // warpgroups: control, ep
 static_assert(kEpiGroups == 2 || kEpiGroups == 3, "2 or 3 epilogue groups");
 static_assert(128 * (kCtlRegs + kLdrRegs + kEpiGroups * kEpiRegs) <= kThreads * (65536 / kThreads / 8 * 8),
               "setmaxnreg budgets exceed the registers the CTA is launched with");
-constexpr uint32_t kTmemCols = 512;                   // 3 accumulators (128 each) + 2 fixed-operand buffers (h0 32 + h1 32 each)
+constexpr uint32_t kTmemCols = 512;                   // 3 accumulators (128 each) + 2 fixed-operand buffers (h0 32 + h1 32 each), or 4 accumulators
 constexpr uint32_t kTmemA = kAcc * 128;               // first column of the fixed-operand buffers
 constexpr uint32_t kTmemABuf = 64;                    // columns per fixed-operand buffer (two halfs per column)
-constexpr uint32_t kBarOff = kStages * kOperandBytes;
+constexpr uint32_t kASmemOff = kStages * kOperandBytes;              // two fixed-operand buffers (kASmem only)
+constexpr uint32_t kBarOff = kASmemOff + (kASmem ? 2 * kOperandBytes : 0);
 constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
 constexpr uint32_t kSmemBytes = kLseOff + 4 * kEpiGroups * 2 * kTile * 4;  // lse: per epilogue warp 2 buffers x 128 floats
 // (the dynamic smem base must be 1024-aligned; checked in the kernel)
@@ -112,6 +120,15 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// both operands from shared memory (K-major, 128-byte swizzle)
+__device__ __forceinline__ void tc_mma_f16_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
 }
 // A operand (M = 128 rows on the 128 TMEM lanes, K along columns, two halfs per column) read from
 // tensor memory; fp16 operands, K = 16 per instruction
@@ -421,7 +438,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
 
     if (threadIdx.x == 0) {
         for (int a = 0; a < 2; ++a) {
-            mbar_init(bar_afull + 8 * a, 4);   // one arrive per loader warp
+            mbar_init(bar_afull + 8 * a, kASmem ? 1 : 4);  // one arrive per loader warp, or the producer's expect_tx
             mbar_init(bar_aempty + 8 * a, kMmaWarps);  // tcgen05.commit after each issuing warp's last MMA of the item
         }
         for (int s = 0; s < kStages; ++s) {
@@ -447,6 +464,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     const uint32_t tmem_base = *tmem_slot;
 
     const CUtensorMap* str_map = PASS == 1 ? &mapK : &mapQ;  // streamed operand, h0 and h1 parts in dim 3
+    const CUtensorMap* fix_map = PASS == 1 ? &mapQ : &mapK;  // fixed operand (kASmem: by TMA as well)
     const int group = p.H / p.KVH;
     const int wg = warp >> 2;  // warpgroup: 0 control, 1-2 epilogue, 3 fixed-operand loaders
 
@@ -463,10 +481,37 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 SegIter<PASS> si;
                 si.init(p, 0);
                 Seg it;
-                while (si.next(it)) {
+                // kASmem: the same warp also brings in the fixed operand of each segment (one more tile of
+                // the other tensor), up to two segments ahead of the streaming (two buffers)
+                SegIter<PASS> sa;
+                Seg ia;
+                int ka = 0;                     // segments whose fixed operand has been requested
+                bool a_more = false;
+                if (kASmem) {
+                    sa.init(p, 0);
+                    a_more = sa.next(ia);
+                }
+                auto request_fixed = [&](bool block) {
+                    const uint32_t ab = ka & 1, abphase = (ka >> 1) & 1;
+                    if (block) mbar_wait_t<DBG>(bar_aempty + 8 * ab, abphase ^ 1);
+                    else if (!mbar_test(bar_aempty + 8 * ab, abphase ^ 1)) return;
+                    const int fb_ = ia.bh / p.H, fh_ = ia.bh % p.H;
+                    const int fix_idx = PASS == 1 ? ia.bh : fb_ * p.KVH + fh_ / group;
+                    if (elect_one()) {
+                        mbar_expect_tx(bar_afull + 8 * ab, tile_tx);
+                        tma_load_4d(ring_s + kASmemOff + ab * kOperandBytes, fix_map, bar_afull + 8 * ab, 0, ia.blk * kTile,
+                                    fix_idx, 0);
+                    }
+                    __syncwarp();
+                    ++ka;
+                    a_more = sa.next(ia);
+                };
+                for (int k = 0; si.next(it); ++k) {
                     const int b = it.bh / p.H, h = it.bh % p.H;
                     const int str_idx = PASS == 1 ? b * p.KVH + h / group : it.bh;
+                    if (kASmem && ka == k) request_fixed(true);   // this segment's own operand (first segment only)
                     for (int t = it.ta; t < it.tb; ++t) {
+                        if (kASmem && a_more && ka == k + 1) request_fixed(false);  // the next segment's, once its buffer is free
                         const uint32_t fb = bar_full + 8 * stage;
                         const uint32_t dst = ring_s + stage * kOperandBytes;
                         mbar_wait_t<DBG>(bar_empty + 8 * stage, sphase ^ 1);
@@ -477,6 +522,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         __syncwarp();
                         if (++stage == kStages) { stage = 0; sphase ^= 1; }
                     }
+                    if (kASmem && a_more && ka == k + 1) request_fixed(true);  // must be on its way before its tiles are
                 }
             }
         } else if (warp <= kMmaWarps) {
@@ -493,7 +539,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 Seg it;
                 for (int k = 0; si.next(it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
-                    const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;
+                    const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;           // TMEM columns
+                    const uint32_t as_h0 = ring_s + kASmemOff + ab * kOperandBytes, as_h1 = as_h0 + kPartBytes;  // kASmem
                     const bool acct = DBG && (p.dbg & 8);
                     long long c0 = acct ? clock64() : 0;
                     mbar_wait_t<DBG>(bar_afull + 8 * ab, abphase);
@@ -530,14 +577,17 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                                 const uint32_t s_h0 = st0, s_h1 = st0 + kPartBytes;
 #pragma unroll
                                 for (int kk = 0; kk < 4; ++kk)   // h0(F) * h0(T)
-                                    tc_mma_f16_ts(d, a_h0 + kk * 8u, umma_desc(s_h0 + kk * 32u), kIdescF16, (uint32_t)kk);
+                                    if (kASmem) tc_mma_f16_ss(d, umma_desc(as_h0 + kk * 32u), umma_desc(s_h0 + kk * 32u), kIdescF16, (uint32_t)kk);
+                                    else tc_mma_f16_ts(d, a_h0 + kk * 8u, umma_desc(s_h0 + kk * 32u), kIdescF16, (uint32_t)kk);
                                 if (p.x3) {
 #pragma unroll
                                     for (int kk = 0; kk < 4; ++kk)  // h1(F) * h0(T)
-                                        tc_mma_f16_ts(d, a_h1 + kk * 8u, umma_desc(s_h0 + kk * 32u), kIdescF16, 1u);
+                                        if (kASmem) tc_mma_f16_ss(d, umma_desc(as_h1 + kk * 32u), umma_desc(s_h0 + kk * 32u), kIdescF16, 1u);
+                                        else tc_mma_f16_ts(d, a_h1 + kk * 8u, umma_desc(s_h0 + kk * 32u), kIdescF16, 1u);
 #pragma unroll
                                     for (int kk = 0; kk < 4; ++kk)  // h0(F) * h1(T)
-                                        tc_mma_f16_ts(d, a_h0 + kk * 8u, umma_desc(s_h1 + kk * 32u), kIdescF16, 1u);
+                                        if (kASmem) tc_mma_f16_ss(d, umma_desc(as_h0 + kk * 32u), umma_desc(s_h1 + kk * 32u), kIdescF16, 1u);
+                                        else tc_mma_f16_ts(d, a_h0 + kk * 8u, umma_desc(s_h1 + kk * 32u), kIdescF16, 1u);
                                 }
                             }
                             tc_commit(bar_empty + 8 * stage);   // stage reusable once these MMAs retire
@@ -566,7 +616,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         SegIter<PASS> si;
         si.init(p, 0);
         Seg it;
-        for (int k = 0; si.next(it); ++k) {
+        for (int k = 0; !kASmem && si.next(it); ++k) {   // kASmem: the producer's TMA does this job
             const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
             const int b = it.bh / p.H, h = it.bh % p.H;
             const int fix_idx = PASS == 1 ? it.bh : b * p.KVH + h / group;
