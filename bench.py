@@ -349,8 +349,8 @@ def main() -> None:
             print(f"[bench] rank {rank}: {e}; using NCCL", file=sys.stderr)
             ipc = None
 
-    def step(timed_events=None):
-        ob.step(*dev_inputs, score_events=timed_events)
+    def step(timed_events=None, side_event=None):
+        ob.step(*dev_inputs, score_events=timed_events, side_event=side_event)
 
     for _ in range(args.warmup):
         step()
@@ -362,18 +362,53 @@ def main() -> None:
     sampler = ClockSampler(local)
     sampler.start()
     k_events = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    side_events = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    host_t = [0.0] * (args.steps + 1)
+    if ipc is not None:
+        ipc.trace = []
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     for i in range(args.steps):
-        step(k_events[i])
+        host_t[i] = time.perf_counter()
+        step(k_events[i], side_events[i])
+    host_t[args.steps] = time.perf_counter()
     ob.join()  # the clock stops when the last step's dequantise has finished
     t1.record()
     torch.cuda.synchronize()
+    host_done = time.perf_counter()
     if dist is not None:
         dist.barrier()
         torch.cuda.synchronize()
     elapsed_ms = t0.elapsed_time(t1)
     score_ms = sum(a.elapsed_time(b) for a, b in k_events) / args.steps
+    # where each rank's time went, step by step (all from CUDA events on the streams the work ran on,
+    # plus the host's submit clock): a step whose completion interval is far above the median names
+    # the stall; `main_gap` = scoring stream idle between two scorings (waits for a free slot),
+    # `partner_wait` = side stream held by splitq_stream_wait_geq_u32 until the partner's payload is
+    # complete, `host_submit` = wall time the host needed to enqueue one step (>= the step time
+    # means the GPU is starved by the launch path, not by kernels)
+    done_at = [t0.elapsed_time(e) for e in side_events]
+    step_ms = [done_at[0]] + [done_at[i] - done_at[i - 1] for i in range(1, args.steps)]
+    score_each = [a.elapsed_time(b) for a, b in k_events]
+    main_gap = [k_events[i - 1][1].elapsed_time(k_events[i][0]) for i in range(1, args.steps)] or [0.0]
+    host_submit = [1e3 * (host_t[i + 1] - host_t[i]) for i in range(args.steps)]
+    partner_wait = [a.elapsed_time(b) for a, b in (ipc.trace if ipc is not None else [])][-args.steps:] or [0.0]
+    med = statistics.median
+    per_rank = {
+        "rank": rank, "total_ms": elapsed_ms,
+        "step_ms": {"min": min(step_ms), "median": med(step_ms), "max": max(step_ms), "slowest_step": step_ms.index(max(step_ms))},
+        "score_ms": {"median": med(score_each), "max": max(score_each), "slowest_step": score_each.index(max(score_each))},
+        "main_gap_ms": {"median": med(main_gap), "max": max(main_gap), "sum": sum(main_gap)},
+        "partner_wait_ms": {"median": med(partner_wait), "max": max(partner_wait), "sum": sum(partner_wait)},
+        "host_submit_ms": {"median": med(host_submit), "max": max(host_submit), "sum": sum(host_submit),
+                           "host_ran_ahead_ms": 1e3 * (host_done - host_t[args.steps])},
+    }
+    if dist is not None:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, per_rank)
+        per_rank_all = gathered
+    else:
+        per_rank_all = [per_rank]
     if ipc is not None:
         ipc.close()
 
@@ -479,6 +514,11 @@ def main() -> None:
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
                     "api": "splitq.HostPipeline.submit/drain (pinned host buffers, 3 streams, depth 2)"},
+            "per_rank_ms": per_rank_all,
+            "median_step": {"ms": max(r["step_ms"]["median"] for r in per_rank_all),
+                            "value": tokens_per_step / (max(r["step_ms"]["median"] for r in per_rank_all) * 1e-3),
+                            "note": "tokens/s at the slowest rank's MEDIAN step-completion interval; `value` above "
+                                    "stays total tokens / total time"},
             "gpu_launches": (plan.launches_per_run(fused) - (4 if fused and cfg["method"] == "last_row" else 0)) * args.steps,
             "clocks": clocks,
         }

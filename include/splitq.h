@@ -19,7 +19,7 @@
  * Payload ("SPQ1", little-endian, one per window; windows of a batch are `payload_stride`
  * bytes apart; every section starts on a 16-byte boundary):
  *   [0,32)   u32 magic 'SPQ1', u32 scale_mode, u32 S, u32 D, u32 n_scales, u32 codes_offset,
- *            u32 payload_bytes, u32 0
+ *            u32 payload_bytes, u32 flags (bit 0 = SPLITQ_HDR_DEQUANT_RECIP, else 0)
  *   bits     u8[S]   per-token width: 2, 4, 8 or 32 (= raw fp32 row)
  *   row_off  u32[S]  row start, in 16-byte units from codes_offset
  *   scales   f32[n_scales]  group mode: 4 slots (8-bit, 4-bit, 2-bit, unused); token mode: S
@@ -47,6 +47,15 @@ extern "C" {
 #define SPLITQ_HEADER_BYTES 32
 #define SPLITQ_SCALE_GROUP 0 /* one absmax per width class (reference: one per selected set) */
 #define SPLITQ_SCALE_TOKEN 1 /* one absmax per token (extension) */
+/* OR into splitq_quant_pack's scale_mode: the receiver dequantises as (q * fl(1/L)) * m instead of
+ * (q / L) * m.  The reference writes `quantized_values / 7 * max_val` (pythia_model.py:186); CPU
+ * ATen divides (the default here, bit-identical), CUDA ATen -- the device every reference entry
+ * point hard-codes (last_row_exp.py:57) -- multiplies a tensor by the reciprocal of a Python
+ * scalar, which differs from the quotient by one ulp for some codes.  With this flag the
+ * dequantised values are bit-identical to the reference run on a GPU.  Codes are the same either
+ * way (`x / max_val` divides by a tensor on both devices).  Stored in header word 7. */
+#define SPLITQ_FLAG_DEQUANT_RECIP 0x100
+#define SPLITQ_HDR_DEQUANT_RECIP 1u
 #define SPLITQ_BITS_RAW 32
 #define SPLITQ_MAX_LADDER 3
 #define SPLITQ_MAX_HEADS 128
@@ -111,7 +120,9 @@ int splitq_select_bits(const float* imp, int B, int S, int D, const int* ladder_
  * Replaces the scale/clamp/round block (pythia_model.py:176-184, qwen_layer_wise.py:60-66)
  * and emits what the reference never materialises: integer codes packed into one payload.
  * Codes are round_half_even(clamp(h / m * L, -(L+1), L)), L = 2^(bits-1) - 1, with IEEE
- * division and no contraction, so they are bit-identical to the ATen sequence. */
+ * division and no contraction, so they are bit-identical to the ATen sequence on CPU and on CUDA
+ * (tests/test_cuda_aten_parity_gpu.py runs the reference's op sequence with torch on the GPU).
+ * scale_mode = SPLITQ_SCALE_GROUP / _TOKEN, optionally | SPLITQ_FLAG_DEQUANT_RECIP. */
 size_t splitq_payload_bytes(int S, int D, const int* ladder_k_host, const int* ladder_bits_host,
                             int n_ladder, int scale_mode);
 size_t splitq_quant_pack_workspace_bytes(int B, int S, int D, int scale_mode);
@@ -140,8 +151,10 @@ int splitq_quant_pack_group_noalloc(const float* h, int B, int S, int D, const u
 
 /* ---- dequantise (K4) -------------------------------------------------------------------
  * Replaces quantized/7*max + index_put (pythia_model.py:186-188, qwen_layer_wise.py:68-70):
- * h_out (B,S,D) = every token of the window, raw rows copied, coded rows as (q / L) * m.
- * Group mode with a zero class scale yields NaN rows, as the reference's 0/0 does. */
+ * h_out (B,S,D) = every token of the window, raw rows copied, coded rows as (q / L) * m with the
+ * correctly rounded quotient (bit-identical to CPU ATen; within one ulp of CUDA ATen), or as
+ * (q * fl(1/L)) * m when the payload header carries SPLITQ_HDR_DEQUANT_RECIP (bit-identical to CUDA
+ * ATen).  Group mode with a zero class scale yields NaN rows, as the reference's 0/0 does. */
 int splitq_dequant(const uint8_t* payload, size_t payload_stride, int B, int S, int D,
                    float* h_out, splitq_stream_t stream);
 

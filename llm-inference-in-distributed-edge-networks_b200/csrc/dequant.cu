@@ -37,19 +37,26 @@ __device__ __forceinline__ float div_levels(float q, float L, float rL) {
     const float e = __fmaf_rn(-L, y, q);
     return __fmaf_rn(e, rL, y);
 }
-__device__ __forceinline__ float decode_field(uint32_t w, int i, int nb, float L, float rL, float m) {
+// recip: the flavour CUDA ATen computes for `q / 7 * m` -- a tensor divided by a Python scalar is
+// multiplied by fl(1/7) there (BinaryDivTrueKernel.cu), which differs from the IEEE quotient by up
+// to one ulp for some codes; the default is the correctly rounded quotient (CPU ATen).
+__device__ __forceinline__ float decode_field(uint32_t w, int i, int nb, float L, float rL, float m, bool recip) {
     const int q = (int)(w << (32 - nb * (i + 1))) >> (32 - nb);  // sign-extend field i
-    return __fmul_rn(div_levels((float)q, L, rL), m);
+    return __fmul_rn(recip ? __fmul_rn((float)q, rL) : div_levels((float)q, L, rL), m);
 }
 
 struct RowInfo {
     int nb;
     float m, L, rL;
-    bool nan_row, bad;
+    bool nan_row, bad, recip;
     const uint8_t* src;
 };
 
-__device__ __forceinline__ RowInfo row_info(const uint8_t* P, int S, int D, int t) {
+// `limit` = bytes the caller says one window's payload may span (payload_stride; 0 = unknown).  The
+// payload crosses process and device boundaries, so nothing read from it is trusted: a header that
+// does not describe this (S, D, mode) layout, or a row that would end past the declared size or
+// past `limit`, marks the row bad (NaN output) instead of being dereferenced.
+__device__ __forceinline__ RowInfo row_info(const uint8_t* P, int S, int D, int t, size_t limit) {
     RowInfo r;
     // every index load below is independent of the others (section offsets depend only on S), so
     // they are all in flight at once; only the row data depends on them
@@ -63,7 +70,13 @@ __device__ __forceinline__ RowInfo row_info(const uint8_t* P, int S, int D, int 
     const int mode = (int)h0.y;
     r.bad = h0.x != SPLITQ_MAGIC || h0.z != (uint32_t)S || h0.w != (uint32_t)D ||
             (mode != SPLITQ_SCALE_GROUP && mode != SPLITQ_SCALE_TOKEN);
+    if (!r.bad) {
+        const uint32_t nbw = (nb == 2 || nb == 4 || nb == 8 || nb == SPLITQ_BITS_RAW) ? (uint32_t)nb : 8u;
+        const unsigned long long end = (unsigned long long)h1.y + 16ull * off16 + row_bytes((uint32_t)D, nbw);
+        r.bad = h1.y != payload_layout((uint32_t)S, mode).codes_off || end > h1.z || (limit != 0 && h1.z > limit);
+    }
     r.nb = nb;
+    r.recip = (h1.w & SPLITQ_HDR_DEQUANT_RECIP) != 0u;
     r.src = P + h1.y /* codes_offset */ + (size_t)off16 * 16u;
     r.m = 0.f;
     r.L = 1.f;
@@ -93,7 +106,7 @@ dequant_kernel(const uint8_t* __restrict__ payload, size_t stride, int S, int D,
     const int b = blockIdx.y;
     if (t >= S) return;
     const uint8_t* P = payload + (size_t)b * stride;
-    const RowInfo r = row_info(P, S, D, t);
+    const RowInfo r = row_info(P, S, D, t, stride);
     const int nch = D >> 2;
     const size_t tok = (size_t)b * S + t;
     const float qnan = __uint_as_float(0x7fc00000u);
@@ -123,10 +136,10 @@ dequant_kernel(const uint8_t* __restrict__ payload, size_t stride, int S, int D,
         }
 #pragma unroll
         for (int u = 0; u < MAXCH; ++u) {
-            v[u].x = decode_field(w[u], 0, r.nb, r.L, r.rL, r.m);
-            v[u].y = decode_field(w[u], 1, r.nb, r.L, r.rL, r.m);
-            v[u].z = decode_field(w[u], 2, r.nb, r.L, r.rL, r.m);
-            v[u].w = decode_field(w[u], 3, r.nb, r.L, r.rL, r.m);
+            v[u].x = decode_field(w[u], 0, r.nb, r.L, r.rL, r.m, r.recip);
+            v[u].y = decode_field(w[u], 1, r.nb, r.L, r.rL, r.m, r.recip);
+            v[u].z = decode_field(w[u], 2, r.nb, r.L, r.rL, r.m, r.recip);
+            v[u].w = decode_field(w[u], 3, r.nb, r.L, r.rL, r.m, r.recip);
             if (r.nan_row) v[u] = make_float4(qnan, qnan, qnan, qnan);
         }
     }
@@ -203,7 +216,7 @@ dequant_generic_kernel(const uint8_t* __restrict__ payload, size_t stride, int S
     const int b = blockIdx.y;
     if (t >= S) return;
     const uint8_t* P = payload + (size_t)b * stride;
-    const RowInfo r = row_info(P, S, D, t);
+    const RowInfo r = row_info(P, S, D, t, stride);
     const size_t tok = (size_t)b * S + t;
     const float qnan = __uint_as_float(0x7fc00000u);
     auto value = [&](int d) -> float {
@@ -211,7 +224,7 @@ dequant_generic_kernel(const uint8_t* __restrict__ payload, size_t stride, int S
         if (r.nb == SPLITQ_BITS_RAW) return reinterpret_cast<const float*>(r.src)[d];
         const int per = 8 / r.nb;
         const uint32_t byte = r.src[d / per];
-        return decode_field(byte, d % per, r.nb, r.L, r.rL, r.m);
+        return decode_field(byte, d % per, r.nb, r.L, r.rL, r.m, r.recip);
     };
     if (h_out)
         for (int d = lane; d < D; d += 32) h_out[tok * D + d] = value(d);

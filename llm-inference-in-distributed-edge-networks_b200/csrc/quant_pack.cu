@@ -53,7 +53,7 @@ __device__ __forceinline__ uint32_t pack4(float4 v, float m, float rcp, float L,
 // only the owner of the last token knows), zeroed section padding, and the group-scale slots.
 template <bool GROUP>
 __device__ __forceinline__ void write_window_index(uint8_t* P, int S, int D, const PayloadLayout& lay,
-                                                   const uint32_t* class_max_w, int lane) {
+                                                   const uint32_t* class_max_w, int lane, uint32_t hdr_flags) {
     if (lane < 8 && lane != 6) {
         uint32_t w = 0;
         switch (lane) {
@@ -63,7 +63,7 @@ __device__ __forceinline__ void write_window_index(uint8_t* P, int S, int D, con
             case 3: w = (uint32_t)D; break;
             case 4: w = lay.n_scales; break;
             case 5: w = lay.codes_off; break;
-            default: w = 0; break;
+            default: w = hdr_flags; break;  // word 7: SPLITQ_HDR_DEQUANT_RECIP
         }
         reinterpret_cast<uint32_t*>(P)[lane] = w;
     }
@@ -118,7 +118,7 @@ template <int MAXCH, bool GROUP>
 __global__ void __launch_bounds__(kQWarps * 32)
 quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
                   const uint32_t* __restrict__ row_off, uint8_t* __restrict__ payload, size_t stride,
-                  const uint32_t* __restrict__ class_max) {
+                  const uint32_t* __restrict__ class_max, uint32_t hdr_flags) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int t = blockIdx.x * kQWarps + warp;
     const int b = blockIdx.y;
@@ -139,7 +139,7 @@ quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __re
     }
 
     float* scales = reinterpret_cast<float*>(P + lay.scales_off);
-    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane);
+    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane, hdr_flags);
     if (lane == 0) {
         P[lay.bits_off + t] = (uint8_t)nb;
         reinterpret_cast<uint32_t*>(P + lay.rowoff_off)[t] = off16;
@@ -198,7 +198,7 @@ template <bool GROUP>
 __global__ void __launch_bounds__(kQWarps * 32)
 quant_pack_generic_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
                           const uint32_t* __restrict__ row_off, uint8_t* __restrict__ payload,
-                          size_t stride, const uint32_t* __restrict__ class_max) {
+                          size_t stride, const uint32_t* __restrict__ class_max, uint32_t hdr_flags) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int t = blockIdx.x * kQWarps + warp;
     const int b = blockIdx.y;
@@ -210,7 +210,7 @@ quant_pack_generic_kernel(const float* __restrict__ h, int S, int D, const uint8
     const uint32_t off16 = row_off[tok];
     const float* row = h + tok * D;
     float* scales = reinterpret_cast<float*>(P + lay.scales_off);
-    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane);
+    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane, hdr_flags);
     if (lane == 0) {
         P[lay.bits_off + t] = (uint8_t)nb;
         reinterpret_cast<uint32_t*>(P + lay.rowoff_off)[t] = off16;
@@ -248,6 +248,52 @@ quant_pack_generic_kernel(const float* __restrict__ h, int S, int D, const uint8
     }
 }
 
+template <bool GROUP> constexpr auto quant_pack_kernel_4 = quant_pack_kernel<4, GROUP>;
+template <bool GROUP> constexpr auto quant_pack_kernel_8 = quant_pack_kernel<8, GROUP>;
+template <bool GROUP> constexpr auto quant_pack_kernel_16 = quant_pack_kernel<16, GROUP>;
+template <bool GROUP> constexpr auto quant_pack_kernel_32 = quant_pack_kernel<32, GROUP>;
+
+// Both entry points launch through here: the optional class-maximum phase (group mode; `class_max`
+// = B x 4 words that this function clears first) and the pack kernel sized for the row width.
+static int launch_quant_pack(const char* who, const float* h, int B, int S, int D, const uint8_t* bits,
+                             const uint32_t* row_off, bool group, uint8_t* payload, size_t payload_stride,
+                             uint32_t* class_max, uint32_t hdr_flags, cudaStream_t st) {
+    SPLITQ_REQUIRE(aligned16(payload) && payload_stride % 16 == 0, SPLITQ_ERR_ALIGN,
+                   "%s: payload and payload_stride must be 16-byte aligned", who);
+    // the payload cannot be larger than an all-raw window; the caller sizes it with
+    // splitq_payload_bytes(), we can only bound-check the stride against the smallest legal size
+    const PayloadLayout lay = payload_layout((uint32_t)S, group ? SPLITQ_SCALE_GROUP : SPLITQ_SCALE_TOKEN);
+    SPLITQ_REQUIRE(B == 1 || payload_stride >= lay.codes_off, SPLITQ_ERR_WORKSPACE,
+                   "%s: payload_stride %zu smaller than the payload index (%u)", who, payload_stride, lay.codes_off);
+    if (int rc = check_arch()) return rc;
+    const bool vec = (D % 4 == 0) && aligned16(h) && D <= 4096;
+    if (group) {
+        // the scratch keeps whatever the previous call left: the maxima must start from zero
+        SPLITQ_CUDA(cudaMemsetAsync(class_max, 0, (size_t)B * 4 * sizeof(uint32_t), st));
+        dim3 g1(cdiv(S, kQWarps * 4), B);
+        if (vec) class_absmax_kernel<true><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
+        else class_absmax_kernel<false><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
+        SPLITQ_LAUNCH_CHECK("class_absmax_kernel");
+    }
+    dim3 grid(cdiv(S, kQWarps), B);
+#define SPLITQ_QP(KERNEL)                                                                                      \
+    do {                                                                                                       \
+        if (group)                                                                                             \
+            KERNEL<true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride, class_max, hdr_flags); \
+        else                                                                                                   \
+            KERNEL<false><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride, class_max, hdr_flags); \
+    } while (0)
+    const int nch = D / 4;
+    if (!vec) SPLITQ_QP(quant_pack_generic_kernel);
+    else if (nch <= 32 * 4) SPLITQ_QP(quant_pack_kernel_4);
+    else if (nch <= 32 * 8) SPLITQ_QP(quant_pack_kernel_8);
+    else if (nch <= 32 * 16) SPLITQ_QP(quant_pack_kernel_16);
+    else SPLITQ_QP(quant_pack_kernel_32);
+#undef SPLITQ_QP
+    SPLITQ_LAUNCH_CHECK("quant_pack_kernel");
+    return SPLITQ_OK;
+}
+
 }  // namespace splitq
 
 using namespace splitq;
@@ -255,7 +301,7 @@ using namespace splitq;
 extern "C" size_t splitq_quant_pack_workspace_bytes(int B, int S, int D, int scale_mode) {
     (void)S; (void)D;
     if (B <= 0) return 0;
-    return scale_mode == SPLITQ_SCALE_GROUP ? (size_t)B * 4 * sizeof(uint32_t) : 0;
+    return (scale_mode & 0xff) == SPLITQ_SCALE_GROUP ? (size_t)B * 4 * sizeof(uint32_t) : 0;
 }
 
 extern "C" int splitq_quant_pack(const float* h, int B, int S, int D, const uint8_t* bits,
@@ -265,58 +311,18 @@ extern "C" int splitq_quant_pack(const float* h, int B, int S, int D, const uint
     SPLITQ_REQUIRE(h && bits && row_off && payload, SPLITQ_ERR_ARG, "quant_pack: NULL buffer");
     SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0, SPLITQ_ERR_ARG, "quant_pack: bad shape B=%d S=%d D=%d", B, S, D);
     SPLITQ_REQUIRE(B <= 65535, SPLITQ_ERR_ARG, "quant_pack: B=%d > 65535", B);
+    const uint32_t hdr_flags = (scale_mode & SPLITQ_FLAG_DEQUANT_RECIP) ? SPLITQ_HDR_DEQUANT_RECIP : 0u;
+    scale_mode &= ~SPLITQ_FLAG_DEQUANT_RECIP;
     SPLITQ_REQUIRE(scale_mode == SPLITQ_SCALE_GROUP || scale_mode == SPLITQ_SCALE_TOKEN, SPLITQ_ERR_ARG,
                    "quant_pack: unknown scale_mode %d", scale_mode);
-    SPLITQ_REQUIRE(aligned16(payload) && payload_stride % 16 == 0, SPLITQ_ERR_ALIGN,
-                   "quant_pack: payload and payload_stride must be 16-byte aligned");
-    // the payload cannot be larger than an all-raw window; the caller sizes it with
-    // splitq_payload_bytes(), we can only bound-check the stride against the smallest legal size
-    const PayloadLayout lay = payload_layout((uint32_t)S, scale_mode);
-    SPLITQ_REQUIRE(B == 1 || payload_stride >= lay.codes_off, SPLITQ_ERR_WORKSPACE,
-                   "quant_pack: payload_stride %zu smaller than the payload index (%u)", payload_stride,
-                   lay.codes_off);
-    if (int rc = check_arch()) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
     const bool group = scale_mode == SPLITQ_SCALE_GROUP;
-    const bool vec = (D % 4 == 0) && aligned16(h) && D <= 4096;
-    uint32_t* class_max = nullptr;
     if (group) {
         const size_t need = (size_t)B * 4 * sizeof(uint32_t);
         SPLITQ_REQUIRE(ws && ws_bytes >= need, SPLITQ_ERR_WORKSPACE, "quant_pack: workspace %zu < %zu bytes",
                        ws_bytes, need);
-        class_max = (uint32_t*)ws;
-        SPLITQ_CUDA(cudaMemsetAsync(class_max, 0, need, st));
-        dim3 g1(cdiv(S, kQWarps * 4), B);
-        if (vec) class_absmax_kernel<true><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
-        else class_absmax_kernel<false><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
-        SPLITQ_LAUNCH_CHECK("class_absmax_kernel");
     }
-    dim3 grid(cdiv(S, kQWarps), B);
-#define SPLITQ_QP(MAXCH)                                                                          \
-    do {                                                                                          \
-        if (group)                                                                                \
-            quant_pack_kernel<MAXCH, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, \
-                                                                          payload_stride, class_max); \
-        else                                                                                      \
-            quant_pack_kernel<MAXCH, false><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, \
-                                                                           payload_stride, class_max); \
-    } while (0)
-    if (vec) {
-        const int nch = D / 4;
-        if (nch <= 32 * 4) SPLITQ_QP(4);
-        else if (nch <= 32 * 8) SPLITQ_QP(8);
-        else if (nch <= 32 * 16) SPLITQ_QP(16);
-        else SPLITQ_QP(32);
-    } else if (group) {
-        quant_pack_generic_kernel<true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload,
-                                                                       payload_stride, class_max);
-    } else {
-        quant_pack_generic_kernel<false><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload,
-                                                                        payload_stride, class_max);
-    }
-#undef SPLITQ_QP
-    SPLITQ_LAUNCH_CHECK("quant_pack_kernel");
-    return SPLITQ_OK;
+    return launch_quant_pack("quant_pack", h, B, S, D, bits, row_off, group, payload, payload_stride, (uint32_t*)ws,
+                             hdr_flags, (cudaStream_t)stream);
 }
 
 // ---- allocation-free group-mode variant -------------------------------------------------------
@@ -362,40 +368,9 @@ extern "C" int splitq_quant_pack_group_noalloc(const float* h, int B, int S, int
                    "quant_pack_group_noalloc: B=%d windows exceeds the built-in scratch (max %d per call); "
                    "split the batch or use splitq_quant_pack with a caller workspace",
                    B, SPLITQ_NOALLOC_MAX_WINDOWS);
-    SPLITQ_REQUIRE(aligned16(payload) && payload_stride % 16 == 0, SPLITQ_ERR_ALIGN,
-                   "quant_pack_group_noalloc: payload and payload_stride must be 16-byte aligned");
-    const PayloadLayout lay = payload_layout((uint32_t)S, SPLITQ_SCALE_GROUP);
-    SPLITQ_REQUIRE(B == 1 || payload_stride >= lay.codes_off, SPLITQ_ERR_WORKSPACE,
-                   "quant_pack_group_noalloc: payload_stride %zu smaller than the payload index (%u)",
-                   payload_stride, lay.codes_off);
     if (int rc = check_arch()) return rc;
     uint32_t* class_max = nullptr;
     if (int rc = static_class_max_ptr(&class_max)) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
-    // the array keeps whatever the previous call left: the maxima must start from zero
-    SPLITQ_CUDA(cudaMemsetAsync(class_max, 0, (size_t)B * 4 * sizeof(uint32_t), st));
-    const bool vec = (D % 4 == 0) && aligned16(h) && D <= 4096;
-    dim3 g1(cdiv(S, kQWarps * 4), B);
-    if (vec) class_absmax_kernel<true><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
-    else class_absmax_kernel<false><<<g1, kQWarps * 32, 0, st>>>(h, S, D, bits, class_max);
-    SPLITQ_LAUNCH_CHECK("class_absmax_kernel");
-    dim3 grid(cdiv(S, kQWarps), B);
-    const int nch = D / 4;
-    if (!vec)
-        quant_pack_generic_kernel<true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload,
-                                                                       payload_stride, class_max);
-    else if (nch <= 32 * 4)
-        quant_pack_kernel<4, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
-                                                                  class_max);
-    else if (nch <= 32 * 8)
-        quant_pack_kernel<8, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
-                                                                  class_max);
-    else if (nch <= 32 * 16)
-        quant_pack_kernel<16, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
-                                                                   class_max);
-    else
-        quant_pack_kernel<32, true><<<grid, kQWarps * 32, 0, st>>>(h, S, D, bits, row_off, payload, payload_stride,
-                                                                   class_max);
-    SPLITQ_LAUNCH_CHECK("quant_pack_kernel");
-    return SPLITQ_OK;
+    return launch_quant_pack("quant_pack_group_noalloc", h, B, S, D, bits, row_off, true, payload, payload_stride,
+                             class_max, 0u, (cudaStream_t)stream);
 }

@@ -17,6 +17,7 @@ SCALE_GROUP, SCALE_TOKEN = 0, 1
 BITS_RAW = 32
 NORM_LAYERNORM, NORM_RMSNORM = 0, 1
 FLAG_CAUSAL_HINT = 1
+FLAG_DEQUANT_RECIP = 0x100  # OR into quant_pack's scale_mode: receiver computes (q * fl(1/L)) * m like CUDA ATen
 MAX_SELECT_S = 32768
 NOALLOC_MAX_WINDOWS = 1024
 FUSED_F16X3, FUSED_F16X1 = 0, 1

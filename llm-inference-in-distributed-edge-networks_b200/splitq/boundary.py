@@ -156,8 +156,11 @@ def select_bits(imp: torch.Tensor, ladder: Ladder, D: int, bits_out: Optional[to
 
 
 def quant_pack(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, scale_mode: int, nbytes: int,
-               payload: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """h: (B,S,D) -> payload uint8 (B, nbytes).  `nbytes` = payload_bytes(S, D, ladder, scale_mode)."""
+               payload: Optional[torch.Tensor] = None, cuda_aten_dequant: bool = False) -> torch.Tensor:
+    """h: (B,S,D) -> payload uint8 (B, nbytes).  `nbytes` = payload_bytes(S, D, ladder, scale_mode).
+    cuda_aten_dequant marks the payload so that the receiver dequantises with q * fl(1/L) -- what the
+    reference's `quantized / 7 * max_val` evaluates to when it runs on a GPU -- instead of the
+    correctly rounded quotient CPU ATen computes (the default)."""
     h = _need_cuda_f32(h, "hidden_states")
     if h.dim() == 2:
         h = h.unsqueeze(0)
@@ -168,7 +171,8 @@ def quant_pack(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, scale
     ws_bytes = lib.splitq_quant_pack_workspace_bytes(B, S, D, scale_mode)
     ws = _WS.get(h.device, "quant", ws_bytes) if ws_bytes else None
     with torch.cuda.device(h.device):
-        N.check(lib.splitq_quant_pack(_ptr(h), B, S, D, _ptr(bits), _ptr(row_off), scale_mode, _ptr(payload),
+        N.check(lib.splitq_quant_pack(_ptr(h), B, S, D, _ptr(bits), _ptr(row_off),
+                                      scale_mode | (N.FLAG_DEQUANT_RECIP if cuda_aten_dequant else 0), _ptr(payload),
                                       payload.stride(0), _ptr(ws), ws_bytes, _stream(h)))
     return payload
 
@@ -480,7 +484,9 @@ class OverlappedBoundary:
         if hasattr(tr, "after_pack"):   # ... and may fetch the new one
             tr.after_pack(p)
 
-    def step(self, *inputs: torch.Tensor, score_events=None) -> "BoundaryPlan":
+    def step(self, *inputs: torch.Tensor, score_events=None, side_event=None) -> "BoundaryPlan":
+        """score_events = (start, end) timing events recorded around the scoring on the main stream;
+        side_event = an event recorded on the side stream when this step's dequantise is enqueued."""
         p = self.plans[self.slot]
         self.slot = (self.slot + 1) % len(self.plans)
         if self.main is not self.caller:  # inputs were produced on the caller's stream
@@ -508,6 +514,8 @@ class OverlappedBoundary:
             p.receive()
             p._xfer_done = torch.cuda.Event()
             p._xfer_done.record(self.side)
+            if side_event is not None:
+                side_event.record(self.side)
         return p
 
     def join(self) -> None:

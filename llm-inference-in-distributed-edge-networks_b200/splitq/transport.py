@@ -110,6 +110,7 @@ class IpcPairExchange:
         self.depth = len(self.plans)
         self.dev = self.plans[0].src
         self.n_pack = 0
+        self.trace = None  # a list: send() appends (before, after) timing events around its wait for the partner
         self.flags = torch.zeros(2, dtype=torch.int32, device=self.dev)  # [ready, free], written by the partner
         self.peer_payload = [None] * self.depth
         self.peer_flags = None
@@ -176,7 +177,13 @@ class IpcPairExchange:
         slot = next(i for i, p in enumerate(self.plans) if p.payload_src is payload_src)
         n = self.plans[slot]._ipc_step
         st = self._stream()
+        if self.trace is not None:
+            before, after = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            before.record(torch.cuda.current_stream(self.dev))
         self._N.check(lib.splitq_stream_wait_geq_u32(C.c_void_p(self.flags.data_ptr()), n, st))
+        if self.trace is not None:
+            after.record(torch.cuda.current_stream(self.dev))
+            self.trace.append((before, after))
         self._N.check(lib.splitq_copy_async(C.c_void_p(payload_dst.data_ptr()), C.c_void_p(self.peer_payload[slot]),
                                             payload_dst.numel(), st))
         self._N.check(lib.splitq_stream_write_u32(C.c_void_p(self.peer_flags + 4), n, st))

@@ -164,6 +164,57 @@ def golden_wrappers():
         json.dump(nll_book, f, indent=1)
 
 
+def golden_fullsize():
+    """Reference wrappers at the window lengths BASELINE.json's configs name (the small fixtures of
+    golden_wrappers stop at S = 128): Pythia-70M S=512 column-mean and S=2048 last-row, both split
+    after layer 3 (layer_of_interest 2); Qwen2-0.5B S=512 split at layer 12 (11), the notebook's
+    setting.  Records the NLL of every ratio, the importance vector the reference selected with,
+    the hidden states entering the boundary, and -- for one ratio -- the rows the reference's
+    in-place int4 block rewrote (the other rows are untouched by construction, which is asserted)."""
+    gen = torch.Generator().manual_seed(2468)
+    specs = [
+        ("pythia_70m_s512", "gpt_neox", compat.PYTHIA_70M, 512, 2, "regular_importance"),
+        ("pythia_70m_s2048", "gpt_neox", compat.PYTHIA_70M, 2048, 2, "last_row"),
+        ("qwen2_05b_s512", "qwen2", compat.QWEN2_05B, 512, 11, "regular_importance"),
+    ]
+    ratios = [0, 0.25, 0.5, 0.75, 1]
+    keep_ratio = 0.25
+    fq, nll_book = {}, {}
+    for name, family, cfg, S, loi, method in specs:
+        model = compat.build_causal_lm(family, cfg, seed=0, attn_implementation="sdpa")
+        eager = compat.clone_with_attention(model, "eager")
+        tuple_shim(model)
+        wrapper = make_pythia_wrapper(model, ratios) if family == "gpt_neox" else make_qwen_wrapper(model)
+        layers = model.base_model.layers
+        ids = torch.randint(0, cfg["vocab_size"], (1, S), generator=gen)
+        with torch.no_grad():
+            att = eager(input_ids=ids, output_attentions=True).attentions
+            hf_loss = eager(input_ids=ids, labels=ids).loss.item()
+        imp = last_row_exp.get_importance_order(method, att, len(layers))[loi]
+        del att, eager
+        book = {"S": S, "ids": ids[0].tolist(), "hf_loss": hf_loss, "method": method, "layer": loi, "nll": {}}
+        for ratio in ratios:
+            pre, post, nll = capture_boundary(wrapper, layers, wrapper.final_layer_norm, ids, imp, ratio, loi)
+            book["nll"][f"{method}|{loi}|{ratio}"] = nll.item()
+            if ratio == keep_ratio:
+                changed = (pre[0] != post[0]).any(dim=1).nonzero().flatten()
+                k = int(ratio * S)
+                sel = torch.argsort(imp)[:k]
+                assert set(changed.tolist()) <= set(sel.tolist())
+                rows = torch.sort(sel).values
+                fq[f"{name}|pre"] = pre[0].numpy()
+                fq[f"{name}|imp"] = imp.numpy()
+                fq[f"{name}|rows"] = rows.numpy().astype(np.int32)
+                fq[f"{name}|post_rows"] = post[0][rows].numpy()
+                fq[f"{name}|ratio"] = np.asarray(ratio)
+        nll_book[name] = book
+        print(name, "hf_loss", hf_loss, book["nll"], flush=True)
+        del model, wrapper
+    np.savez_compressed(os.path.join(GOLD, "fake_quant_fullsize.npz"), **fq)
+    with open(os.path.join(GOLD, "wrapper_nll_fullsize.json"), "w") as f:
+        json.dump(nll_book, f, indent=1)
+
+
 def golden_degenerate():
     """The reference's unguarded 0/0: run its exact block on an all-zero selected set by driving
     the tiny wrapper with zeroed embeddings is not possible without editing it, so record the
@@ -227,8 +278,8 @@ def golden_initial():
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(8)
-    todo = sys.argv[1:] or ["importance", "degenerate", "wrappers", "channel", "initial"]
+    todo = sys.argv[1:] or ["importance", "degenerate", "wrappers", "channel", "initial", "fullsize"]
     for name in todo:
         {"importance": golden_importance, "degenerate": golden_degenerate, "wrappers": golden_wrappers,
-         "channel": golden_channel, "initial": golden_initial}[name]()
+         "channel": golden_channel, "initial": golden_initial, "fullsize": golden_fullsize}[name]()
     print("golden fixtures written to", GOLD)

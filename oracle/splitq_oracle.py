@@ -158,8 +158,13 @@ def quant_codes(x: torch.Tensor, m: torch.Tensor, L: int) -> torch.Tensor:
     return torch.round(scaled)
 
 
-def dequant_values(q: torch.Tensor, m: torch.Tensor, L: int) -> torch.Tensor:
-    """q / L * m  (pythia_model.py:186, qwen_layer_wise.py:68)."""
+def dequant_values(q: torch.Tensor, m: torch.Tensor, L: int, recip: bool = False) -> torch.Tensor:
+    """q / L * m  (pythia_model.py:186, qwen_layer_wise.py:68).  recip=True restates what CUDA ATen
+    computes for the same source line: a tensor divided by a Python scalar is multiplied by the fp32
+    reciprocal of the scalar there (aten/src/ATen/native/cuda/BinaryDivTrueKernel.cu), so the value
+    is (q * fl(1/L)) * m -- pinned against torch on a GPU by tests/test_cuda_aten_parity_gpu.py."""
+    if recip:
+        return q * torch.tensor(1.0, dtype=torch.float32).div(torch.tensor(float(L), dtype=torch.float32)) * m
     return q / float(L) * m
 
 
@@ -299,7 +304,10 @@ def row_codes(h_row: torch.Tensor, m: float, bits: int, scale_mode: int) -> np.n
     return q.to(torch.int8).numpy()
 
 
-def pack_payload(h: torch.Tensor, bits: np.ndarray, scale_mode: int) -> np.ndarray:
+HDR_DEQUANT_RECIP = 1  # header word 7, bit 0: the receiver dequantises with q * fl(1/L) (CUDA ATen flavour)
+
+
+def pack_payload(h: torch.Tensor, bits: np.ndarray, scale_mode: int, recip: bool = False) -> np.ndarray:
     """h: (S,D) fp32, bits: (S,) u8 in {2,4,8,32} -> uint8 payload for one window."""
     S, D = h.shape
     bits_off, rowoff_off, scales_off, codes_off = payload_layout(S, D, scale_mode)
@@ -307,7 +315,8 @@ def pack_payload(h: torch.Tensor, bits: np.ndarray, scale_mode: int) -> np.ndarr
     buf = np.zeros(total, dtype=np.uint8)
     n_scales = GROUP_SLOTS if scale_mode == SCALE_GROUP else S
     buf[:HEADER_BYTES] = np.frombuffer(
-        struct.pack("<8I", MAGIC, scale_mode, S, D, n_scales, codes_off, total, 0), dtype=np.uint8)
+        struct.pack("<8I", MAGIC, scale_mode, S, D, n_scales, codes_off, total, HDR_DEQUANT_RECIP if recip else 0),
+        dtype=np.uint8)
     buf[bits_off:bits_off + S] = bits
     rb = np.array([row_bytes(D, int(b)) for b in bits], dtype=np.int64)
     row_off16 = ((np.cumsum(rb) - rb) // 16).astype(np.uint32)
@@ -332,7 +341,7 @@ def unpack_payload(buf: np.ndarray) -> torch.Tensor:
     """Inverse of pack_payload: dequantised (S,D) fp32 hidden states.
     group mode with a zero class scale reproduces the reference's unguarded 0/0 -> NaN rows
     (pythia_model.py:176-186); token mode treats an all-zero row as zeros (our extension)."""
-    magic, scale_mode, S, D, n_scales, codes_off, total, _ = struct.unpack("<8I", buf[:HEADER_BYTES].tobytes())
+    magic, scale_mode, S, D, n_scales, codes_off, total, flags = struct.unpack("<8I", buf[:HEADER_BYTES].tobytes())
     assert magic == MAGIC and total == buf.size
     bits_off, rowoff_off, scales_off, _ = payload_layout(S, D, scale_mode)
     bits = buf[bits_off:bits_off + S]
@@ -351,14 +360,14 @@ def unpack_payload(buf: np.ndarray) -> torch.Tensor:
             if scale_mode == SCALE_GROUP and m == 0.0:
                 out[t] = float("nan")
             else:
-                out[t] = dequant_values(q, torch.tensor(m, dtype=torch.float32), L)
+                out[t] = dequant_values(q, torch.tensor(m, dtype=torch.float32), L, recip=bool(flags & HDR_DEQUANT_RECIP))
     return out
 
 
-def boundary_roundtrip(h: torch.Tensor, imp: torch.Tensor, ladder, scale_mode: int):
+def boundary_roundtrip(h: torch.Tensor, imp: torch.Tensor, ladder, scale_mode: int, recip: bool = False):
     """score-independent part of the path: select -> quantize/pack -> (transfer) -> dequantize."""
     bits = ladder_bits(imp, ladder)
-    payload = pack_payload(h, bits, scale_mode)
+    payload = pack_payload(h, bits, scale_mode, recip)
     return bits, payload, unpack_payload(payload)
 
 

@@ -25,7 +25,8 @@ rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dev = torch.device("cuda", rank % torch.cuda.device_count())
 torch.cuda.set_device(dev)
 dist.init_process_group("gloo")
-B, H, KVH, S, D, STEPS = 2, 4, 2, 384, 256, 7
+B, H, KVH, S, D, STEPS = 2, 4, 2, 384, 256, int(os.environ.get("SPLITQ_TEST_STEPS", "7"))
+FREE_RUNNING = os.environ.get("SPLITQ_TEST_FREE_RUNNING") == "1"
 ladder = splitq.ladder_from_fractions([(0.25, 2), (0.25, 4), (0.25, 8)], S)
 
 def inputs(r, step):
@@ -41,11 +42,25 @@ ipc = IpcPairExchange(ob.plans, rank, world)
 for p in ob.plans:
     p.transport = ipc
 got = []
-for step in range(STEPS):
-    plan = ob.step(*inputs(rank, step))
-    ob.side.synchronize()                      # this step's dequantise is done; keep a copy
-    got.append(plan.h_out.clone())
-ob.drain()
+if FREE_RUNNING:
+    # no host synchronisation between steps: the host runs ahead of both GPUs' streams, slots are
+    # reused at depth 2, and each result is copied out by stream-ordered work on the side stream
+    ins = [inputs(rank, step) for step in range(STEPS)]
+    keep = torch.zeros(STEPS, B, S, D, device=dev)
+    torch.cuda.synchronize()
+    dist.barrier()
+    for step in range(STEPS):
+        plan = ob.step(*ins[step])
+        with torch.cuda.stream(ob.side):
+            keep[step].copy_(plan.h_out)
+    ob.drain()
+    got = [keep[step] for step in range(STEPS)]
+else:
+    for step in range(STEPS):
+        plan = ob.step(*inputs(rank, step))
+        ob.side.synchronize()                      # this step's dequantise is done; keep a copy
+        got.append(plan.h_out.clone())
+    ob.drain()
 ipc.close()
 # what a single process computes for the PARTNER's windows
 ref = make_plan()
@@ -58,11 +73,15 @@ dist.destroy_process_group()
 '''
 
 
-def test_ipc_pair_exchange_two_ranks(tmp_path):
+@pytest.mark.parametrize("free_running", [False, True])
+def test_ipc_pair_exchange_two_ranks(tmp_path, free_running):
+    """free_running: 50 steps submitted without any host synchronisation (the way bench.py drives the
+    exchange), so the two ranks' counters, the depth-2 slot reuse and the copy-engine pulls overlap."""
     script = tmp_path / "worker.py"
     script.write_text(f"ROOT = {ROOT!r}\n" + WORKER)
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29533", WORLD_SIZE="2",
-               PYTORCH_CUDA_ALLOC_CONF="")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29534" if free_running else "29533", WORLD_SIZE="2",
+               PYTORCH_CUDA_ALLOC_CONF="", SPLITQ_TEST_STEPS="50" if free_running else "7",
+               SPLITQ_TEST_FREE_RUNNING="1" if free_running else "0")
     procs = [subprocess.Popen([sys.executable, str(script)], env=dict(env, RANK=str(r)), stdout=subprocess.PIPE,
                               stderr=subprocess.STDOUT, text=True) for r in range(2)]
     outs = []

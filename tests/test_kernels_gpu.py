@@ -178,6 +178,31 @@ def test_reference_fake_quant_fixtures_bit_exact(golden_dir):
     assert checked >= 30
 
 
+def test_reference_fullsize_fixtures_bit_exact(golden_dir):
+    """Same check at the window lengths BASELINE.json's configs name (Pythia-70M S=512 column-mean,
+    S=2048 last-row, Qwen2-0.5B S=512): the GPU select -> pack -> dequantise reproduces every row the
+    reference's own wrapper rewrote and leaves all other rows bit-identical."""
+    from test_oracle_golden import fullsize_cases
+    n = 0
+    for name, pre, imp, ratio, rows, post_rows in fullsize_cases(golden_dir):
+        S, D = pre.shape
+        ladder = splitq.ladder_for_ratio(ratio, S)
+        nbytes = splitq.payload_bytes(S, D, ladder, O.SCALE_GROUP)
+        bits, row_off = splitq.select_bits(imp.to(DEV), ladder, D)
+        payload = splitq.quant_pack(pre.to(DEV), bits, row_off, O.SCALE_GROUP, nbytes)
+        post = splitq.dequant(payload, S, D)[0].cpu().numpy()
+        assert np.array_equal(post[rows], post_rows), name            # -0.0 == +0.0 (see above)
+        nz = post_rows != 0
+        assert np.array_equal(post[rows].view(np.uint32)[nz], post_rows.view(np.uint32)[nz]), name
+        keep = np.ones(S, dtype=bool)
+        keep[rows] = False
+        assert np.array_equal(post[keep].view(np.uint32), pre.numpy()[keep].view(np.uint32)), name
+        want_payload = O.pack_payload(pre, O.ladder_bits(imp, ladder), O.SCALE_GROUP)
+        assert np.array_equal(payload[0].cpu().numpy(), want_payload), name
+        n += 1
+    assert n == 3
+
+
 def test_zero_block_reproduces_reference_nan_in_group_mode_only():
     S, D = 8, 16
     h = torch.zeros(1, S, D)
@@ -240,7 +265,7 @@ def test_transfer_same_device_copy():
 
 
 # ------------------------------------------------------------------------------------------
-# full-size properties (BASELINE.json config 3 shapes; oracle too slow here)
+# full size (BASELINE.json config 3 shapes): size-independent properties, then the payload bytes
 # ------------------------------------------------------------------------------------------
 def test_full_size_roundtrip_properties():
     B, H, S, D = 2, 14, 4096, 896
@@ -276,6 +301,13 @@ def test_full_size_roundtrip_properties():
     assert torch.equal(p2[:, lay[3]:], res.payload[:, lay[3]:])
     hdr = res.payload[0, :32].cpu().numpy().view(np.uint32)
     assert hdr[0] == O.MAGIC and hdr[2] == S and hdr[3] == D and hdr[6] == plan.nbytes
+    # and the bytes themselves, at full size: every window's payload equals the oracle's packing of the
+    # same hidden states under the kernel's own scores, and the dequantised states are bit-identical
+    for b in range(B):
+        want_bits, want_payload, want_h = O.boundary_roundtrip(h[b].cpu(), res.importance[b].cpu(), ladder, O.SCALE_TOKEN)
+        assert np.array_equal(bits[b].cpu().numpy(), want_bits)
+        assert np.array_equal(res.payload[b].cpu().numpy(), want_payload), b
+        assert np.array_equal(res.hidden[b].cpu().numpy().view(np.uint32), want_h.numpy().view(np.uint32)), b
 
 
 @pytest.mark.parametrize("mode", [O.SCALE_GROUP, O.SCALE_TOKEN])
@@ -337,6 +369,44 @@ def test_codes_bit_exact_near_rounding_boundaries():
             got = splitq.quant_pack(h.to(DEV), bits, off, mode, nbytes)[0].cpu().numpy()
             want = O.pack_payload(h[0], O.ladder_bits(imp[0], ladder), mode)
             assert np.array_equal(got, want), (bits_w, mode)
+
+
+def test_overlapped_boundary_free_running_no_host_syncs():
+    """The race surface of the software pipeline is slot reuse at depth 2 while the host runs ahead:
+    60 steps on distinct inputs are submitted back to back with NO host synchronisation; every step's
+    result is copied out by stream-ordered work on the side stream (as a consumer would read it) and
+    compared afterwards with a plain, fully synchronised plan."""
+    B, H, KVH, S, D, STEPS = 2, 4, 2, 256, 128, 60
+    gen = torch.Generator(device=DEV).manual_seed(33)
+    ladder = splitq.ladder_from_fractions([(0.25, 2), (0.25, 4), (0.25, 8)], S)
+    mk = lambda: splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=O.SCALE_TOKEN, KVH=KVH)  # noqa: E731
+    q = torch.randn(STEPS, B, H, S, 64, device=DEV, generator=gen)
+    k = torch.randn(STEPS, B, KVH, S, 64, device=DEV, generator=gen)
+    h = torch.randn(STEPS, B, S, D, device=DEV, generator=gen)
+    ref_plan = mk()
+    want_h = torch.empty(STEPS, B, S, D, device=DEV)
+    want_p = torch.empty(STEPS, B, ref_plan.nbytes, dtype=torch.uint8, device=DEV)
+    for i in range(STEPS):
+        r = ref_plan.run_fused(q[i], k[i], h[i])
+        want_h[i].copy_(r.hidden)
+        want_p[i].copy_(r.payload)
+    torch.cuda.synchronize()
+    for kw in ({}, {"pack_on_side": False}, {"main_priority": -3}):
+        ob = splitq.OverlappedBoundary(mk, depth=2, fused=True, **kw)
+        got_h = torch.zeros(STEPS, B, S, D, device=DEV)
+        got_p = torch.zeros(STEPS, B, ref_plan.nbytes, dtype=torch.uint8, device=DEV)
+        checksum = torch.zeros((), dtype=torch.int64, device=DEV)
+        for i in range(STEPS):
+            p = ob.step(q[i], k[i], h[i])
+            with torch.cuda.stream(ob.side):          # stream-ordered consumer; the host never waits
+                got_h[i].copy_(p.h_out)
+                got_p[i].copy_(p.payload_dst)
+                checksum += p.h_out.view(torch.int32).sum(dtype=torch.int64)
+        ob.join()
+        ob.drain()
+        assert torch.equal(got_p, want_p), kw
+        assert torch.equal(got_h.view(torch.int32), want_h.view(torch.int32)), kw
+        assert int(checksum) == int(want_h.view(torch.int32).sum(dtype=torch.int64)), kw
 
 
 def test_pipelined_front_ends_give_the_same_bytes_as_the_plain_plan():

@@ -43,6 +43,34 @@ def test_fake_quant_block_bit_exact(golden_dir):
         assert np.array_equal(post, g[key + "|post"]), key
 
 
+def fullsize_cases(golden_dir):
+    """(name, pre (S,D), imp (S,), ratio, rows the reference rewrote, their new values)"""
+    g = np.load(os.path.join(golden_dir, "fake_quant_fullsize.npz"))
+    for name in sorted({k.split("|")[0] for k in g.files}):
+        yield (name, torch.from_numpy(g[name + "|pre"]), torch.from_numpy(g[name + "|imp"]), float(g[name + "|ratio"]),
+               g[name + "|rows"], g[name + "|post_rows"])
+
+
+def test_fullsize_fake_quant_block_bit_exact(golden_dir):
+    """The reference wrappers at BASELINE.json's window lengths (Pythia-70M S=512 / S=2048,
+    Qwen2-0.5B S=512): the restatement and the payload round trip reproduce the rows the
+    reference's in-place int4 block rewrote, and leave every other row untouched."""
+    n = 0
+    for name, pre, imp, ratio, rows, post_rows in fullsize_cases(golden_dir):
+        S, D = pre.shape
+        assert (S, D) in ((512, 512), (2048, 512), (512, 896)), name
+        post = O.fake_quant_reference(pre.unsqueeze(0), imp, ratio)[0].numpy()
+        assert np.array_equal(post[rows], post_rows), name
+        keep = np.ones(S, dtype=bool)
+        keep[rows] = False
+        assert np.array_equal(post[keep], pre.numpy()[keep]), name
+        k = O.num_selected(ratio, S)
+        _, _, deq = O.boundary_roundtrip(pre, imp, [(k, 4)], O.SCALE_GROUP)
+        assert np.array_equal(deq.numpy(), post), name
+        n += 1
+    assert n == 3
+
+
 def test_payload_roundtrip_equals_reference_block(golden_dir):
     """pack -> unpack in group/int4 mode reproduces the reference's in-place fake quant bit for bit."""
     g = np.load(os.path.join(golden_dir, "fake_quant.npz"))
