@@ -27,6 +27,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -1097,16 +1098,22 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     p.q16 = (const uint4*)(w8 + wl.q0); p.k16 = (const uint4*)(w8 + wl.k0);
     p.q_part = (wl.q1 - wl.q0) / 16; p.k_part = (wl.k1 - wl.k0) / 16;
 
+    // one-time per-device set-up; the entry point is re-entrant (any thread, any stream), so the
+    // bookkeeping is under a lock -- the attribute calls themselves are idempotent
+    static std::mutex attr_mu;
     static bool attr_set[64] = {};
     int dev = 0, sms = 148;
     SPLITQ_CUDA(cudaGetDevice(&dev));
     SPLITQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    if (dev < 64 && !attr_set[dev]) {
+    {
+    std::lock_guard<std::mutex> attr_lock(attr_mu);
+    if (dev >= 64 || !attr_set[dev]) {
         SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         SPLITQ_CUDA(cudaFuncSetAttribute(fused_importance_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_set[dev] = true;
+        if (dev < 64) attr_set[dev] = true;
+    }
     }
     const long long per_bh = p.causal ? (long long)p.nb * (p.nb + 1) / 2 : (long long)p.nb * p.nb;
     const long long tiles = (long long)B * H * per_bh;

@@ -9,6 +9,7 @@ cited in include/splitq.h.
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from dataclasses import dataclass
 from typing import List, Optional, Sequence, Tuple
 
@@ -36,17 +37,25 @@ def _need_cuda_f32(t: torch.Tensor, name: str) -> torch.Tensor:
 
 
 class _Workspace:
-    """Grow-only scratch buffers per (device, tag) so steady-state calls never allocate."""
+    """Grow-only scratch buffers so steady-state calls never allocate.  Kernel scratch is live from
+    the launch until the kernel retires, so two calls may share a buffer only if they are ordered on
+    one stream: the module-level instance keys its buffers by (device, tag, CURRENT STREAM), and every
+    BoundaryPlan owns a private instance, so plans driven concurrently on different streams (or by
+    different threads) never meet in the same scratch."""
 
-    def __init__(self) -> None:
+    def __init__(self, per_stream: bool = True) -> None:
         self._bufs = {}
+        self._per_stream = per_stream
+        self._lock = threading.Lock()
 
     def get(self, device: torch.device, tag: str, nbytes: int) -> torch.Tensor:
-        key = (device.index, tag)
-        buf = self._bufs.get(key)
-        if buf is None or buf.numel() < nbytes:
-            buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
-            self._bufs[key] = buf
+        stream = torch.cuda.current_stream(device).cuda_stream if self._per_stream else 0
+        key = (device.index, tag, stream)
+        with self._lock:
+            buf = self._bufs.get(key)
+            if buf is None or buf.numel() < nbytes:
+                buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+                self._bufs[key] = buf
         return buf
 
 
@@ -81,7 +90,8 @@ def payload_bytes(S: int, D: int, ladder: Ladder, scale_mode: int) -> int:
 
 def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
                               want_last: bool = False, causal_hint: bool = False,
-                              out_col: Optional[torch.Tensor] = None, out_last: Optional[torch.Tensor] = None):
+                              out_col: Optional[torch.Tensor] = None, out_last: Optional[torch.Tensor] = None,
+                              workspace: Optional[_Workspace] = None):
     """A: (B,H,Sq,Sk) attention probabilities -> (col (B,Sk) or None, last (B,Sk) or None)."""
     A = _need_cuda_f32(A, "A")
     if A.dim() != 4:
@@ -93,7 +103,7 @@ def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]]
     if want_last and out_last is None:
         out_last = torch.empty(B, Sk, dtype=torch.float32, device=A.device)
     ws_bytes = lib.splitq_importance_colmean_workspace_bytes(B, H, Sq, Sk) if want_col else 0
-    ws = _WS.get(A.device, "colmean", ws_bytes) if ws_bytes else None
+    ws = (workspace or _WS).get(A.device, "colmean", ws_bytes) if ws_bytes else None
     hw = None
     if head_w is not None:
         hw = N.float_array([float(x) for x in head_w])
@@ -109,7 +119,7 @@ def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]]
 def importance_fused(q: torch.Tensor, k: torch.Tensor, scaling: float, causal: bool = True,
                      mode: int = N.FUSED_F16X3, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
                      want_last: bool = False, out_col: Optional[torch.Tensor] = None,
-                     out_last: Optional[torch.Tensor] = None):
+                     out_last: Optional[torch.Tensor] = None, workspace: Optional[_Workspace] = None):
     """q: (B,H,S,64), k: (B,KVH,S,64) post-RoPE fp32 CUDA tensors (any batch/head/seq strides, e.g.
     HF's `.view(...).transpose(1, 2)`) -> (col (B,S) or None, last (B,S) or None) without ever
     materialising the (S,S) attention matrix."""
@@ -126,8 +136,12 @@ def importance_fused(q: torch.Tensor, k: torch.Tensor, scaling: float, causal: b
     ws_bytes = lib.splitq_importance_fused_workspace_bytes(B, H, KVH, S, hd)
     if ws_bytes == 0:
         raise N.SplitqError(f"importance_fused: unsupported shape q={tuple(q.shape)} k={tuple(k.shape)} (head_dim 64 only)")
-    ws = _WS.get(q.device, "fused", ws_bytes)
-    hw = N.float_array([float(x) for x in head_w]) if head_w is not None else None
+    ws = (workspace or _WS).get(q.device, "fused", ws_bytes)
+    hw = None
+    if head_w is not None:
+        hw = N.float_array([float(x) for x in head_w])
+        if len(hw) != H:  # the C side reads exactly H host floats
+            raise N.SplitqError(f"head_w has {len(hw)} entries for {H} heads")
     qs = (C.c_longlong * 3)(q.stride(0), q.stride(1), q.stride(2))
     ks = (C.c_longlong * 3)(k.stride(0), k.stride(1), k.stride(2))
     with torch.cuda.device(q.device):
@@ -155,8 +169,26 @@ def select_bits(imp: torch.Tensor, ladder: Ladder, D: int, bits_out: Optional[to
     return bits_out, row_off_out
 
 
+def _check_pack_args(who: str, h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, payload: torch.Tensor,
+                     nbytes: Optional[int]) -> None:
+    """The C side trusts these pointers: a wrong dtype, device, layout or size is an out-of-bounds
+    access there, so it is refused here."""
+    B, S, _ = h.shape
+    for name, t, dt in (("bits", bits, torch.uint8), ("row_off", row_off, torch.int32)):
+        if not (isinstance(t, torch.Tensor) and t.device == h.device and t.dtype == dt and t.is_contiguous()
+                and tuple(t.shape) == (B, S)):
+            raise N.SplitqError(f"{who}: {name} must be a contiguous ({B},{S}) {dt} tensor on {h.device}")
+    if not (payload.device == h.device and payload.dtype == torch.uint8 and payload.dim() == 2
+            and payload.shape[0] == B and payload.stride(1) == 1 and payload.stride(0) % 16 == 0):
+        raise N.SplitqError(f"{who}: payload must be a ({B}, nbytes) uint8 tensor on {h.device} with a row stride "
+                            "that is a multiple of 16")
+    if nbytes is not None and payload.shape[1] < nbytes:
+        raise N.SplitqError(f"{who}: payload rows hold {payload.shape[1]} bytes, {nbytes} needed")
+
+
 def quant_pack(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, scale_mode: int, nbytes: int,
-               payload: Optional[torch.Tensor] = None, cuda_aten_dequant: bool = False) -> torch.Tensor:
+               payload: Optional[torch.Tensor] = None, cuda_aten_dequant: bool = False,
+               workspace: Optional[_Workspace] = None) -> torch.Tensor:
     """h: (B,S,D) -> payload uint8 (B, nbytes).  `nbytes` = payload_bytes(S, D, ladder, scale_mode).
     cuda_aten_dequant marks the payload so that the receiver dequantises with q * fl(1/L) -- what the
     reference's `quantized / 7 * max_val` evaluates to when it runs on a GPU -- instead of the
@@ -167,9 +199,10 @@ def quant_pack(h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, scale
     B, S, D = h.shape
     if payload is None:
         payload = torch.empty(B, nbytes, dtype=torch.uint8, device=h.device)
+    _check_pack_args("quant_pack", h, bits, row_off, payload, nbytes)
     lib = N.load()
     ws_bytes = lib.splitq_quant_pack_workspace_bytes(B, S, D, scale_mode)
-    ws = _WS.get(h.device, "quant", ws_bytes) if ws_bytes else None
+    ws = (workspace or _WS).get(h.device, "quant", ws_bytes) if ws_bytes else None
     with torch.cuda.device(h.device):
         N.check(lib.splitq_quant_pack(_ptr(h), B, S, D, _ptr(bits), _ptr(row_off),
                                       scale_mode | (N.FLAG_DEQUANT_RECIP if cuda_aten_dequant else 0), _ptr(payload),
@@ -188,6 +221,7 @@ def quant_pack_group_noalloc(h: torch.Tensor, bits: torch.Tensor, row_off: torch
     if not (h.is_cuda and h.dtype == torch.float32 and h.is_contiguous() and h.dim() == 3):
         raise N.SplitqError("quant_pack_group_noalloc: h must be a contiguous (B,S,D) float32 CUDA tensor")
     B, S, D = h.shape
+    _check_pack_args("quant_pack_group_noalloc", h, bits, row_off, payload, None)
     with torch.cuda.device(h.device):
         N.check(N.load().splitq_quant_pack_group_noalloc(_ptr(h), B, S, D, _ptr(bits), _ptr(row_off), _ptr(payload),
                                                          payload.stride(0), _stream(h)))
@@ -283,15 +317,16 @@ class BoundaryPlan:
         self.payload_src = torch.empty(B, self.nbytes, dtype=torch.uint8, device=self.src)
         self.payload_dst = torch.empty(B, self.nbytes, dtype=torch.uint8, device=self.dst)
         self.h_out = torch.empty(B, S, D, dtype=torch.float32, device=self.dst)
-        # warm the grow-only workspaces
-        lib = N.load()
-        _WS.get(self.src, "colmean", lib.splitq_importance_colmean_workspace_bytes(B, H, S, S))
-        _WS.get(self.src, "quant", lib.splitq_quant_pack_workspace_bytes(B, S, D, scale_mode))
+        # private scratch (not shared with any other plan or stream); the small one is sized now, the
+        # scoring scratch (materialised or fused, whichever this plan is driven with) on first use
+        self.ws = _Workspace(per_stream=False)
+        self.ws.get(self.src, "quant", N.load().splitq_quant_pack_workspace_bytes(B, S, D, scale_mode))
+        self._dst_done = None  # two-device plans: the downstream device has finished reading payload_dst
 
     def score(self, A: torch.Tensor) -> torch.Tensor:
         last = self.method == "last_row"
         importance_from_attention(A, want_col=not last, want_last=last, causal_hint=self.causal_hint,
-                                  out_col=self.imp, out_last=self.imp)
+                                  out_col=self.imp, out_last=self.imp, workspace=self.ws)
         return self.imp
 
     def score_fused(self, q: torch.Tensor, k: torch.Tensor, scaling: Optional[float] = None) -> torch.Tensor:
@@ -299,17 +334,21 @@ class BoundaryPlan:
         last = self.method == "last_row"
         scaling = q.shape[-1] ** -0.5 if scaling is None else scaling
         importance_fused(q, k, scaling, causal=True, mode=self.fused_mode, want_col=not last, want_last=last,
-                         out_col=self.imp, out_last=self.imp)
+                         out_col=self.imp, out_last=self.imp, workspace=self.ws)
         return self.imp
 
     def send(self, h: torch.Tensor) -> torch.Tensor:
         select_bits(self.imp, self.ladder, self.D, self.bits, self.row_off)
-        quant_pack(h, self.bits, self.row_off, self.scale_mode, self.nbytes, self.payload_src)
+        quant_pack(h, self.bits, self.row_off, self.scale_mode, self.nbytes, self.payload_src, workspace=self.ws)
         return self.payload_src
 
     def hop(self) -> torch.Tensor:
         if self.transport is not None:  # e.g. transport.PairExchange between ranks
             return self.transport.send(self.payload_src, self.payload_dst)
+        if self.dst != self.src and self._dst_done is not None:
+            # the copy is enqueued on the SOURCE device's stream but overwrites a buffer that the
+            # DESTINATION device's stream may still be dequantising from (the previous pass)
+            torch.cuda.current_stream(self.src).wait_event(self._dst_done)
         transfer(self.payload_dst, self.payload_src)
         if self.dst != self.src:
             ev = torch.cuda.Event()
@@ -318,7 +357,11 @@ class BoundaryPlan:
         return self.payload_dst
 
     def receive(self) -> torch.Tensor:
-        return dequant(self.payload_dst, self.S, self.D, self.h_out)
+        out = dequant(self.payload_dst, self.S, self.D, self.h_out)
+        if self.dst != self.src:
+            self._dst_done = torch.cuda.Event()
+            self._dst_done.record(torch.cuda.current_stream(self.dst))
+        return out
 
     def run(self, A: torch.Tensor, h: torch.Tensor) -> BoundaryResult:
         self.score(A)
@@ -512,6 +555,8 @@ class OverlappedBoundary:
                 self._pack(p, inputs[-1])
             p.hop()
             p.receive()
+            if p._dst_done is not None:  # two-device plan: the dequantise ran on the other device's stream
+                self.side.wait_event(p._dst_done)
             p._xfer_done = torch.cuda.Event()
             p._xfer_done.record(self.side)
             if side_event is not None:

@@ -159,14 +159,31 @@ class _LayerWiseModel:
         self.last_payload_bytes = B * nbytes
         return payload
 
+    def payload_like(self, rows: int, S: int, ratio: float) -> torch.Tensor:
+        """Receive buffer for what boundary_send(hidden (rows,S,D), ., ratio) produces on the other
+        side of a GPU pair: the size depends only on (S, D, ladder, scale mode)."""
+        D = self._down.config.hidden_size
+        nbytes = boundary.payload_bytes(S, D, self.ladder(ratio, S), self.scale_mode)
+        return torch.empty(rows, nbytes, dtype=torch.uint8, device=self.down_device)
+
+    def hidden_like(self, rows: int, S: int) -> torch.Tensor:
+        return torch.empty(rows, S, self._down.config.hidden_size, dtype=torch.float32, device=self.down_device)
+
     def boundary_hop(self, payload):
         if self.down_device == payload.device:
             return payload
         dst = torch.empty(payload.shape, dtype=torch.uint8, device=self.down_device)
+        # `dst` comes from the downstream device's caching allocator and may be a block that an
+        # earlier, still queued dequantise on that device reads; the copy is enqueued on the UPSTREAM
+        # device's stream, which knows nothing of that work -- so order it behind it explicitly
+        up, down = torch.cuda.current_stream(payload.device), torch.cuda.current_stream(self.down_device)
+        free = torch.cuda.Event()
+        free.record(down)
+        up.wait_event(free)
         boundary.transfer(dst, payload)
         ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(payload.device))
-        torch.cuda.current_stream(self.down_device).wait_event(ev)
+        ev.record(up)
+        down.wait_event(ev)
         return dst
 
     def downstream(self, ids_shape, target, layer_of_interest, payload=None, hidden=None, per_sequence=False):

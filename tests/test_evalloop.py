@@ -18,6 +18,13 @@ def test_closed_form_schedule_equals_reference_loop(n, max_len, stride):
     assert evalloop.window_schedule(n, max_len, stride) == O.window_schedule(n, max_len, stride)
 
 
+def free_port() -> int:
+    import socket
+    with socket.socket() as sock:
+        sock.bind(("127.0.0.1", 0))
+        return sock.getsockname()[1]
+
+
 class StubWrapper:
     """Deterministic stand-in: NLL depends on the window's tokens, the split layer and the ratio."""
     device = down_device = torch.device("cpu")
@@ -31,6 +38,12 @@ class StubWrapper:
 
     def boundary_hop(self, payload):
         return payload
+
+    def payload_like(self, rows, S, ratio):
+        return torch.empty(())
+
+    def hidden_like(self, rows, S):
+        return torch.empty(())
 
     def downstream(self, shape, target, loi, payload=None, hidden=None):
         x = payload if payload is not None else hidden
@@ -60,7 +73,7 @@ def test_two_rank_gloo_equals_single_process(tmp_path):
     ids = torch.randint(0, 1000, (1, 1500), generator=torch.Generator().manual_seed(3))
     single = evalloop.evaluate(PARAMS, StubWrapper(), ids, stub_importance, 256, log=lambda *a: None)
     out = str(tmp_path) + "/"
-    mp.spawn(_worker, args=(2, 29611, out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, free_port(), out), nprocs=2, join=True)
     total, n_tokens, windows = pickle.load(open(out + "res.pkl", "rb"))
     assert n_tokens == single.n_tokens == 1500 - len(evalloop.window_schedule(1500, 256, 32))
     assert windows == single.windows == len(evalloop.window_schedule(1500, 256, 32))
@@ -72,6 +85,39 @@ def test_two_rank_gloo_equals_single_process(tmp_path):
     assert ppl[0][0][0] == pytest.approx(math.exp(total[0][0][0] / n_tokens))
     # ratio 0 is method independent, as in the reference's own logs
     assert total[0][0][0] == total[1][0][0]
+
+
+def _pairs_worker(rank, world, port, out, n_tokens):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.distributed.init_process_group("gloo", rank=rank, world_size=world)
+    ids = torch.randint(0, 1000, (1, n_tokens), generator=torch.Generator().manual_seed(3))
+    res = evalloop.evaluate(PARAMS, StubWrapper(), ids, stub_importance, 256, out_prefix=out, log=lambda *a: None,
+                            pairs=True, checkpoint_every=2, file_names=evalloop.FILE_NAMES["pythia"])
+    with open(out + f"res{rank}.pkl", "wb") as f:
+        pickle.dump((res.total_nll, res.n_tokens, res.windows, res.hop_bytes), f)
+    torch.distributed.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_tokens", [(2, 1500), (4, 1500), (3, 700), (4, 256 + 5 * 32)])
+def test_gpu_pair_layout_over_gloo_equals_single_process(tmp_path, world, n_tokens):
+    """pairs=True: rank 2p = upstream half, rank 2p+1 = downstream half, payloads and ratio-0 hidden
+    states cross by send/recv, pair p of P owns windows k = p (mod P); an odd last rank idles but
+    still joins the collectives (checkpoint_every=2 makes the periodic all-reduce fire while the
+    shards hold different window counts -- the gate depends on the global index only).  Totals
+    equal the single-process run bit for bit on every rank."""
+    ids = torch.randint(0, 1000, (1, n_tokens), generator=torch.Generator().manual_seed(3))
+    single = evalloop.evaluate(PARAMS, StubWrapper(), ids, stub_importance, 256, log=lambda *a: None)
+    out = str(tmp_path) + "/"
+    mp.spawn(_pairs_worker, args=(world, free_port(), out, n_tokens), nprocs=world, join=True)
+    for rank in range(world):
+        total, n_tok, windows, hop = pickle.load(open(out + f"res{rank}.pkl", "rb"))
+        assert n_tok == single.n_tokens and windows == single.windows
+        assert torch.allclose(torch.tensor(total), torch.tensor(single.total_nll), rtol=1e-12, atol=0)
+        is_up = rank % 2 == 0 and rank < 2 * (world // 2)
+        assert (hop > 0) == is_up
+    # the Pythia script's own file names (last_row_exp.py:122-124,142)
+    assert pickle.load(open(out + "n_tokens_pythia_70m.pkl", "rb")) == single.n_tokens
+    assert os.path.exists(out + "total_nll_pythia_70m.pkl") and os.path.exists(out + "avg_ppl_results_pythia_70m.pkl")
 
 
 @pytest.mark.gpu
@@ -129,7 +175,7 @@ def _pair_worker(rank, world, port, out):
 @pytest.mark.parametrize("world", [2, 3])
 def test_pair_exchange_over_gloo(tmp_path, world):
     """rank r swaps payloads with r^1; an unpaired last rank keeps its own (local copy)."""
-    mp.spawn(_pair_worker, args=(world, 29620 + world, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_pair_worker, args=(world, free_port(), str(tmp_path)), nprocs=world, join=True)
 
 
 @pytest.mark.gpu
@@ -171,3 +217,82 @@ def test_batching_all_method_ratio_variants_changes_nothing(family):
     b = evalloop.evaluate(params, w, ids, fn, 128, log=lambda *x: None, batch_combos=True)
     assert a.n_tokens == b.n_tokens
     assert torch.allclose(torch.tensor(a.total_nll), torch.tensor(b.total_nll), rtol=1e-5)
+
+
+@pytest.mark.gpu
+def test_channel_wise_driver_matches_wrapper_calls(tmp_path):
+    """evaluate_channel == the reference's channel_wise.py loop structure (one wrapper.channel_wise call
+    per (window, method, layer)), and writes its three pickle files."""
+    from splitq import compat
+    from splitq.models import QwenPointFiveBModel
+    cfg = dict(compat.QWEN2_TINY, hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=256,
+               max_position_embeddings=1024)
+    w = QwenPointFiveBModel.from_config("cuda:0", cfg=cfg, seed=0)
+    methods, layers = ["channel_8", "channel_4", "channel_1_mean", "channel_1_max"], [0, 1]
+    ids_all = torch.randint(0, 512, (1, 512 + 2 * 32), generator=torch.Generator().manual_seed(9))
+    out = str(tmp_path) + "/"
+    res = evalloop.evaluate_channel(layers, methods, w, ids_all, out_prefix=out, log=lambda *a: None)
+    total = [[0.0] * len(methods) for _ in layers]
+    ntok = 0
+    for begin, end, trg in O.window_schedule(ids_all.shape[1], 512, 32):
+        ids = ids_all[:, begin:end].to("cuda:0")
+        tgt, nlt = O.window_targets(ids, trg)
+        for m, method in enumerate(methods):
+            for l, loi in enumerate(layers):
+                total[l][m] += w.channel_wise(ids, tgt, loi, method).item() * nlt
+        ntok += nlt
+    assert res.n_tokens == ntok and res.windows == 3
+    assert torch.allclose(torch.tensor(res.total_nll), torch.tensor(total), rtol=1e-5)
+    assert pickle.load(open(out + "n_tokens_channel.pkl", "rb")) == ntok
+    ppl = pickle.load(open(out + "ppl_channel.pkl", "rb"))
+    assert ppl[1][2] == pytest.approx(math.exp(total[1][2] / ntok), rel=1e-5)
+    assert os.path.exists(out + "total_nll_channel.pkl")
+
+
+PAIR_WORKER = r'''
+import json, os, sys
+import torch
+sys.path.insert(0, os.path.join(ROOT, "llm-inference-in-distributed-edge-networks_b200"))
+from splitq.main import run
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", rank))
+params = json.loads(os.environ["SPLITQ_PARAMS"])
+res = run("pythia", params, int(os.environ["SPLITQ_TOKENS"]), f"cuda:{rank}", pairs=True, out_prefix=os.environ["SPLITQ_OUT"])
+if rank == 0:
+    json.dump({"total": res.total_nll, "n": res.n_tokens, "w": res.windows}, open(os.environ["SPLITQ_OUT"] + "pair.json", "w"))
+torch.distributed.destroy_process_group()
+'''
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch_combos", [False, True])
+def test_gpu_pair_eval_equals_single_gpu_eval(tmp_path, batch_combos):
+    """SURVEY 8e on real devices: upstream half on GPU 0 (rank 0), downstream half on GPU 1 (rank 1),
+    payloads over NCCL send/recv -- the NLL sums equal the one-GPU run bit for bit (same kernels, same
+    inputs; only where the two halves execute differs) and the Pythia file names are written."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import json
+    import subprocess
+    import sys
+    from splitq.main import run
+    params = {"ratios": [0, 0.5, 1], "layers_of_interest": [2, 5], "methods": ["regular_importance", "last_row"],
+              "max_length": 256, "batch_combos": batch_combos}
+    n = 256 + 4 * 32
+    single = run("pythia", params, n, "cuda:0")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "pair_worker.py"
+    script.write_text(f"ROOT = {root!r}\n" + PAIR_WORKER)
+    out = str(tmp_path) + "/"
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), WORLD_SIZE="2",
+               SPLITQ_PARAMS=json.dumps(params), SPLITQ_TOKENS=str(n), SPLITQ_OUT=out)
+    procs = [subprocess.Popen([sys.executable, str(script)], env=dict(env, RANK=str(r), LOCAL_RANK=str(r)),
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-3000:]
+    got = json.load(open(out + "pair.json"))
+    assert got["n"] == single.n_tokens and got["w"] == single.windows
+    assert torch.equal(torch.tensor(got["total"]), torch.tensor(single.total_nll))
+    assert os.path.exists(out + "avg_ppl_results_pythia_70m.pkl")

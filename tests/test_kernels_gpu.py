@@ -409,6 +409,89 @@ def test_overlapped_boundary_free_running_no_host_syncs():
         assert int(checksum) == int(want_h.view(torch.int32).sum(dtype=torch.int64)), kw
 
 
+def test_two_plans_on_two_streams_do_not_share_scratch():
+    """Two BoundaryPlans driven concurrently on two streams (group mode, so quantise/pack uses its
+    class-maximum scratch, and fused scoring, which uses the large K2 scratch): every plan owns its
+    workspace, so both results equal the serial ones.  Also the module-level functions, whose default
+    workspace is keyed by the current stream."""
+    B, H, KVH, S, D = 3, 4, 2, 512, 256
+    gen = torch.Generator(device=DEV).manual_seed(41)
+    ladder = splitq.ladder_for_ratio(0.5, S)
+    mk = lambda: splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=O.SCALE_GROUP, KVH=KVH)  # noqa: E731
+    data = [(torch.randn(B, H, S, 64, device=DEV, generator=gen), torch.randn(B, KVH, S, 64, device=DEV, generator=gen),
+             torch.randn(B, S, D, device=DEV, generator=gen) * (1 + 10 * i)) for i in range(2)]
+    serial = mk()
+    want = []
+    for q, k, h in data:
+        r = serial.run_fused(q, k, h)
+        want.append((r.payload.clone(), r.hidden.clone()))
+    torch.cuda.synchronize()
+    plans, streams = [mk(), mk()], [torch.cuda.Stream(), torch.cuda.Stream()]
+    assert plans[0].ws is not plans[1].ws
+    for rep in range(20):
+        for pl, st, (q, k, h) in zip(plans, streams, data):
+            with torch.cuda.stream(st):
+                pl.run_fused(q, k, h)
+    torch.cuda.synchronize()
+    for pl, (wp, wh) in zip(plans, want):
+        assert torch.equal(pl.payload_dst, wp) and torch.equal(pl.h_out.view(torch.int32), wh.view(torch.int32))
+    # module-level entry points on two streams: default scratch is per (device, tag, stream)
+    outs = []
+    for st, (q, k, h) in zip(streams, data):
+        with torch.cuda.stream(st):
+            for rep in range(10):
+                col, _ = splitq.importance_fused(q, k, 0.125)
+                bits, off = splitq.select_bits(col, ladder, D)
+                payload = splitq.quant_pack(h, bits, off, O.SCALE_GROUP, serial.nbytes)
+            outs.append(payload)
+    torch.cuda.synchronize()
+    for payload, (wp, _) in zip(outs, want):
+        assert torch.equal(payload, wp)
+
+
+def test_python_layer_rejects_mismatched_buffers():
+    S, D = 64, 32
+    h = torch.randn(1, S, D, device=DEV)
+    imp = torch.rand(1, S, device=DEV)
+    ladder = [(16, 4)]
+    bits, off = splitq.select_bits(imp, ladder, D)
+    nbytes = splitq.payload_bytes(S, D, ladder, O.SCALE_TOKEN)
+    with pytest.raises(N.SplitqError):
+        splitq.quant_pack(h, bits.to(torch.int32), off, O.SCALE_TOKEN, nbytes)
+    with pytest.raises(N.SplitqError):
+        splitq.quant_pack(h, bits, off[:, : S // 2].contiguous(), O.SCALE_TOKEN, nbytes)
+    with pytest.raises(N.SplitqError):
+        splitq.quant_pack(h, bits, off, O.SCALE_TOKEN, nbytes, payload=torch.empty(1, nbytes - 16, dtype=torch.uint8, device=DEV))
+    q = torch.randn(1, 4, S, 64, device=DEV)
+    with pytest.raises(N.SplitqError):
+        splitq.importance_fused(q, q, 0.125, head_w=[1.0, 2.0])
+
+
+def test_dequant_refuses_truncated_or_inconsistent_payloads():
+    """A payload that crossed a process/device boundary is not trusted: wrong codes_offset, a row
+    that ends past the declared size, or a declared size beyond the stride give NaN rows, not an
+    out-of-bounds read."""
+    S, D = 32, 64
+    h = torch.randn(1, S, D, device=DEV)
+    imp = torch.rand(1, S, device=DEV)
+    ladder = [(8, 2), (8, 4), (8, 8)]
+    nbytes = splitq.payload_bytes(S, D, ladder, O.SCALE_TOKEN)
+    bits, off = splitq.select_bits(imp, ladder, D)
+    good = splitq.quant_pack(h, bits, off, O.SCALE_TOKEN, nbytes)
+    assert torch.isfinite(splitq.dequant(good, S, D)).all()
+    for word, value in ((5, 16), (6, nbytes - 64), (6, nbytes + 4096)):
+        bad = good.clone()
+        hdr = bad[0, :32].view(torch.int32)
+        hdr[word] = value
+        out = splitq.dequant(bad, S, D)
+        assert torch.isnan(out).any(), (word, value)
+    rows = good.clone()
+    lay = O.payload_layout(S, D, O.SCALE_TOKEN)
+    rows[0, lay[1]:lay[1] + 4].view(torch.int32)[0] = 1 << 20  # row offset of token 0 far outside
+    out = splitq.dequant(rows, S, D)
+    assert torch.isnan(out[0, 0]).all() and torch.isfinite(out[0, 1:]).all()
+
+
 def test_pipelined_front_ends_give_the_same_bytes_as_the_plain_plan():
     """OverlappedBoundary (side-stream hop + dequantise) and HostPipeline (H2D / kernels / D2H on
     three streams) are schedules, not arithmetic: outputs must equal BoundaryPlan.run bit for bit."""

@@ -154,3 +154,58 @@ def test_two_device_split_equals_single_device(book):
         b = two.activation_quantization(ids, ids.clone(), imp, ratio, 2)
         assert b.device.index == 1
         assert a.item() == pytest.approx(b.item(), rel=1e-6)
+
+
+@pytest.mark.gpu
+def test_two_device_split_back_to_back_with_a_busy_downstream_device(book):
+    """The hop writes into the downstream device's memory from the upstream device's stream.  Many
+    (ratio, importance) variants are queued back to back with no host sync while the downstream
+    device is kept busy, so a copy that did not wait for the previous dequantise would overwrite a
+    payload that is still being read; every NLL must equal the single-device one."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    name = "pythia_70m"
+    one = build(name, "cuda:0")
+    two = build(name, "cuda:0", split_devices=("cuda:0", "cuda:1"))
+    ids = torch.tensor([book[name]["ids"]], device="cuda:0")
+    gen = torch.Generator(device="cuda:0").manual_seed(3)
+    imps = [torch.rand(ids.shape[1], device="cuda:0", generator=gen) for _ in range(6)]
+    ratios = [0.25, 0.5, 0.75, 1.0]
+    want = [one.activation_quantization(ids, ids.clone(), imp, r, 2) for imp in imps for r in ratios]
+    busy = torch.randn(4096, 4096, device="cuda:1")
+    got = []
+    for imp in imps:
+        for r in ratios:
+            for _ in range(4):
+                busy = busy @ busy * 1e-4          # queue work on the downstream device's stream
+            got.append(two.activation_quantization(ids, ids.clone(), imp, r, 2))
+    torch.cuda.synchronize("cuda:0")
+    torch.cuda.synchronize("cuda:1")
+    for a, b in zip(want, got):
+        assert a.item() == pytest.approx(b.item(), rel=1e-6)
+
+
+@pytest.mark.gpu
+def test_two_device_overlapped_boundary_matches_one_device():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import splitq_oracle as O
+    B, H, KVH, S, D, STEPS = 2, 4, 2, 256, 128, 30
+    gen = torch.Generator(device="cuda:0").manual_seed(8)
+    ladder = splitq.ladder_from_fractions([(0.25, 2), (0.25, 4), (0.25, 8)], S)
+    q = torch.randn(STEPS, B, H, S, 64, device="cuda:0", generator=gen)
+    k = torch.randn(STEPS, B, KVH, S, 64, device="cuda:0", generator=gen)
+    h = torch.randn(STEPS, B, S, D, device="cuda:0", generator=gen)
+    ref = splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=O.SCALE_TOKEN, KVH=KVH)
+    want = torch.stack([ref.run_fused(q[i], k[i], h[i]).hidden.clone() for i in range(STEPS)])
+    mk = lambda: splitq.BoundaryPlan(B, H, S, D, ladder, scale_mode=O.SCALE_TOKEN, KVH=KVH,  # noqa: E731
+                                     src_device="cuda:0", dst_device="cuda:1")
+    ob = splitq.OverlappedBoundary(mk, depth=2, fused=True)
+    got = torch.zeros(STEPS, B, S, D, device="cuda:1")
+    for i in range(STEPS):
+        p = ob.step(q[i], k[i], h[i])
+        with torch.cuda.device("cuda:1"):            # cuda:1's current stream: where a two-device plan dequantises
+            got[i].copy_(p.h_out)
+    ob.drain()
+    torch.cuda.synchronize("cuda:1")
+    assert torch.equal(got.cpu().view(torch.int32), want.cpu().view(torch.int32))
