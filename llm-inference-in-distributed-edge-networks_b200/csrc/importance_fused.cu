@@ -27,6 +27,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <mutex>
 
 #include "common.cuh"
@@ -38,7 +39,10 @@ constexpr int kTile = 128;
 constexpr int kHd = 64;
 constexpr uint32_t kPartBytes = 128 * 128;           // 128 rows x 64 fp16: one swizzle-128B slab (h0 or h1 part)
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // h0 + h1
-constexpr int kStages = 4;                           // streamed tiles in flight; one barrier pair and one TMA issue per tile
+#ifndef SPLITQ_K2_STAGES
+#define SPLITQ_K2_STAGES 4
+#endif
+constexpr int kStages = SPLITQ_K2_STAGES;            // streamed tiles in flight; one barrier pair and one TMA issue per tile
 // SPLITQ_K2_A_SMEM = 1: the fixed operand stays in shared memory (SS-mode MMA, brought in by TMA like
 // the streamed one) instead of tensor memory; the 128 TMEM columns this frees hold a FOURTH
 // accumulator, and the loader warps have nothing to do.
@@ -71,7 +75,8 @@ constexpr uint32_t kTmemABuf = 64;                    // columns per fixed-opera
 constexpr uint32_t kASmemOff = kStages * kOperandBytes;              // two fixed-operand buffers (kASmem only)
 constexpr uint32_t kBarOff = kASmemOff + (kASmem ? 2 * kOperandBytes : 0);
 constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
-constexpr uint32_t kSmemBytes = kLseOff + 4 * kEpiGroups * 2 * kTile * 4;  // lse: per epilogue warp 2 buffers x 128 floats
+constexpr uint32_t kFlagOff = kLseOff + 4 * kEpiGroups * 2 * kTile * 4;     // lse: per epilogue warp 2 buffers x 128 floats
+constexpr uint32_t kSmemBytes = kFlagOff + 256;                              // 3 floats per warp: launch-wide facts
 // (the dynamic smem base must be 1024-aligned; checked in the kernel)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -182,6 +187,9 @@ __device__ __forceinline__ float ex2_ordered(float x) {
     return y;
 }
 #endif
+#ifndef SPLITQ_K2_GROUP_DELAY
+#define SPLITQ_K2_GROUP_DELAY 0
+#endif
 #ifndef SPLITQ_K2_EXP_BATCH
 #define SPLITQ_K2_EXP_BATCH 16
 #endif
@@ -196,11 +204,14 @@ constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) <<
 struct Params {
     int B, H, KVH, S, nb;
     int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
-    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads, bit3: print cycle accounting, bit4: loaders skip their global loads
-    float cs;          // scaling * log2(e)
+    int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads, bit4: loaders skip their global loads, bit5: never take the FAST epilogue
+    int nq_blk, nk_blk;  // entries of bound2 / eblk that belong to Q blocks (B*H*nb) and to K blocks (B*KVH*nb)
     int tiles;         // tiles of one pass = B * H * tiles_per_bh
     float2* ml;        // (kSlots,B,H,S) pass-1 partial (max, sum) per result slot, pre-set to (-inf, 0)
     float* lse2;       // (B,H,S) log2-domain log-sum-exp (lse_combine_kernel)
+    float* w2;         // (B,H,S) 2^-lse2 (FAST epilogue of pass 2)
+    const float* bound2;  // per operand block: largest squared row norm (Q rows already carry scaling * log2 e)
+    const int* eblk;      // per operand block: exponent e of the power-of-two pre-scale 2^-e (0 unless |x| >= 2^15)
     float* part_col;   // (kSlots,B,H,S) partial sum_i p[i][j] per result slot, pre-set to 0
     float* part_last;  // (B,H,S) p[S-1][j]
     const uint4 *q16, *k16;  // dense (n,S,64) fp16 h0 part; the h1 part follows at +q_part / +k_part uint4
@@ -320,14 +331,14 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
 __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
-// log2-domain lse of queries q0..q0+3 of one (b,h) row block; queries past S read +inf (-> p = 0)
-__device__ __forceinline__ float4 load_lse4(const float* __restrict__ row0, int q0, int S, bool vec) {
+// per-query values (log2-domain lse, or w = 2^-lse) of queries q0..q0+3 of one (b,h); queries past S read `fill` (-> p = 0)
+__device__ __forceinline__ float4 load_lse4(const float* __restrict__ row0, int q0, int S, bool vec, float fill) {
     if (vec && q0 + 3 < S) return __ldg(reinterpret_cast<const float4*>(row0 + q0));
     float4 r;
-    r.x = q0 + 0 < S ? __ldg(row0 + q0 + 0) : INFINITY;
-    r.y = q0 + 1 < S ? __ldg(row0 + q0 + 1) : INFINITY;
-    r.z = q0 + 2 < S ? __ldg(row0 + q0 + 2) : INFINITY;
-    r.w = q0 + 3 < S ? __ldg(row0 + q0 + 3) : INFINITY;
+    r.x = q0 + 0 < S ? __ldg(row0 + q0 + 0) : fill;
+    r.y = q0 + 1 < S ? __ldg(row0 + q0 + 1) : fill;
+    r.z = q0 + 2 < S ? __ldg(row0 + q0 + 2) : fill;
+    r.w = q0 + 3 < S ? __ldg(row0 + q0 + 3) : fill;
     return r;
 }
 // One column of this thread's TMEM lane (the last query's logit for pass 2's last-row importance)
@@ -343,6 +354,89 @@ __device__ __forceinline__ void tc_ld1_issue(uint32_t taddr, float& v) {
 //
 // pass 1, NC columns (= keys cr0..cr0+NC-1) of one query row: online log-sum-exp in the log2
 // domain.  EDGE: key c is valid iff c <= jmax (this row) ; jlo / jhi = the smallest / largest jmax in the warp.
+// FAST variants: the operand split has proven |logit| < kFastBound for every (query, key) pair of the
+// launch (largest query norm x largest key norm; the logits arrive in the log2 domain because the
+// softmax scale is folded into Q), so exp2 can neither overflow nor lose the row's largest terms and
+// needs no running maximum: pass 1 is a plain sum of exp2(v) -- MUFU + FADD per element -- and pass 2
+// multiplies by w = 2^-lse of the query instead of subtracting lse first -- MUFU + FFMA.  With half the
+// issue slots per element one warp alone keeps the MUFU pipe busy, so the two epilogue warps of a
+// sub-partition no longer depend on being inside their exp2 code at the same time.
+constexpr float kFastBound = 100.f;
+// The FAST loops leave most issue slots free while the MUFU pipe (16 exp2 / clk / SM) is the busiest
+// unit, so kPoly of every 16 exponentials are evaluated on the FMA pipe instead: round-to-nearest range
+// reduction by the 1.5 * 2^23 trick (valid for |x| < 2^22; here |x| < 100), a degree-5 polynomial for
+// 2^r on [-0.5, 0.5] (relative error 1.8e-7 in fp32, the same as ex2.approx) and an integer add of
+// the exponent.
+#ifndef SPLITQ_K2_POLY
+#define SPLITQ_K2_POLY 0
+#endif
+constexpr int kPoly = SPLITQ_K2_POLY;
+__device__ __forceinline__ float ex2_poly(float x) {
+    const float t = x + 12582912.f;
+    const float r = x - (t - 12582912.f);
+    float p = 0.001326472731307149f;
+    p = fmaf(p, r, 0.009671512991189957f);
+    p = fmaf(p, r, 0.05550733581185341f);
+    p = fmaf(p, r, 0.24022242426872253f);
+    p = fmaf(p, r, 0.6931470036506653f);
+    p = fmaf(p, r, 1.0f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+// element j of a batch of 16 goes to the FMA pipe if it closes one of kPoly equal strides
+__device__ __forceinline__ constexpr bool on_fma_pipe(int j) { return ((j & 15) + 1) * kPoly / 16 != (j & 15) * kPoly / 16; }
+__device__ __forceinline__ float ex2_mixed(float x, int j) { return on_fma_pipe(j) ? ex2_poly(x) : ex2_ordered(x); }
+template <int NC, bool EDGE>
+__device__ __forceinline__ void pass1_fast(const float (&v)[NC], int cr0, int jmax, int jlo, int jhi, float& l) {
+    constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int i0 = 0; i0 < NC; i0 += EB) {
+        if (EDGE && cr0 + i0 > jhi) continue;            // nothing valid for any row of the warp
+        float e[EB];
+#pragma unroll
+        for (int j = 0; j < EB; ++j) e[j] = ex2_mixed(v[i0 + j], j);
+        if (EDGE && cr0 + i0 + EB - 1 > jlo) {           // the boundary crosses this batch
+#pragma unroll
+            for (int j = 0; j < EB; ++j) e[j] = (cr0 + i0 + j > jmax) ? 0.f : e[j];
+        }
+#pragma unroll
+        for (int j = 0; j < EB; j += 4) {
+            s0 += e[j + 0];
+            s1 += e[j + 1];
+            s2 += e[j + 2];
+            s3 += e[j + 3];
+        }
+    }
+    l += (s0 + s1) + (s2 + s3);
+}
+// ws = shared address of the NC per-query weights w = 2^-lse (queries >= S carry w = 0)
+template <int NC, bool DIAG>
+__device__ __forceinline__ void pass2_fast(const float (&v)[NC], uint32_t ws, int cr0, int r, int w0, float& colsum) {
+    constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int i0 = 0; i0 < NC; i0 += EB) {
+        if (DIAG && cr0 + i0 + EB <= w0) continue;       // all queries of the batch precede every key of the warp
+        float e[EB];
+#pragma unroll
+        for (int j = 0; j < EB; ++j) e[j] = ex2_mixed(v[i0 + j], j);
+        if (DIAG && cr0 + i0 < w0 + 31) {                // the diagonal crosses this batch
+#pragma unroll
+            for (int j = 0; j < EB; ++j) e[j] = (cr0 + i0 + j < r) ? 0.f : e[j];
+        }
+#pragma unroll
+        for (int j = 0; j < EB; j += 4) {
+            const float4 w4 = lds128(ws + 4u * (i0 + j));
+            s0 = fmaf(e[j + 0], w4.x, s0);
+            s1 = fmaf(e[j + 1], w4.y, s1);
+            s2 = fmaf(e[j + 2], w4.z, s2);
+            s3 = fmaf(e[j + 3], w4.w, s3);
+        }
+    }
+    colsum += (s0 + s1) + (s2 + s3);
+}
+// General variants (any magnitude): cs = 2^(block exponents) rescales a tile whose operand blocks
+// were pre-scaled into fp16 range (1 otherwise).
 template <int NC, bool EDGE>
 __device__ __forceinline__ void pass1_body(float (&v)[NC], int cr0, int jmax, int jlo, int jhi, float cs, float& m, float& l) {
     constexpr int EB = NC < kExpBatch ? NC : kExpBatch;
@@ -459,10 +553,46 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // launch-wide facts from the operand split (every CTA reduces the small per-block arrays itself):
+    // the largest squared row norms of Q' = Q * scaling * log2(e) and of K bound every logit of the
+    // launch by Cauchy-Schwarz; any non-zero block exponent means some block was pre-scaled
+    {
+        float q2 = 0.f, k2 = 0.f;
+        int emax = 0;
+        for (int i = threadIdx.x; i < p.nq_blk + p.nk_blk; i += kThreads) {
+            const float b2 = __ldg(p.bound2 + i);
+            if (i < p.nq_blk) q2 = fmaxf(q2, b2 == b2 ? b2 : INFINITY);
+            else k2 = fmaxf(k2, b2 == b2 ? b2 : INFINITY);
+            emax = max(emax, __ldg(p.eblk + i));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            q2 = fmaxf(q2, __shfl_xor_sync(0xffffffffu, q2, o));
+            k2 = fmaxf(k2, __shfl_xor_sync(0xffffffffu, k2, o));
+            emax = max(emax, __shfl_xor_sync(0xffffffffu, emax, o));
+        }
+        if (lane == 0) {
+            float* f = reinterpret_cast<float*>(gen + kFlagOff) + 3 * warp;
+            f[0] = q2; f[1] = k2; f[2] = __int_as_float(emax);
+        }
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    bool fast, scaled;
+    {
+        float q2 = 0.f, k2 = 0.f;
+        int emax = 0;
+        const float* f = reinterpret_cast<const float*>(gen + kFlagOff);
+        for (int w = 0; w < kThreads / 32; ++w) {
+            q2 = fmaxf(q2, f[3 * w]); k2 = fmaxf(k2, f[3 * w + 1]); emax = max(emax, __float_as_int(f[3 * w + 2]));
+        }
+        scaled = emax != 0;
+        // the norm caps keep the absolute fp16 floor of one operand (2^-25 per element) times the other
+        // operand's norm far below the 1e-6 a logit may be off by
+        fast = !scaled && q2 < 16384.f && k2 < 16384.f && q2 * k2 < kFastBound * kFastBound && !(DBG && (p.dbg & 32));
+    }
 
     const CUtensorMap* str_map = PASS == 1 ? &mapK : &mapQ;  // streamed operand, h0 and h1 parts in dim 3
     const CUtensorMap* fix_map = PASS == 1 ? &mapQ : &mapK;  // fixed operand (kASmem: by TMA as well)
@@ -534,7 +664,6 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 const uint32_t mi = (uint32_t)warp - 1u;
                 uint32_t n_tile = 0;
                 uint32_t stage = 0, sphase = 0, acc = 0, aphase = 0;
-                long long w_afull = 0, w_tempty = 0, w_full = 0, c_start = DBG ? clock64() : 0;  // DBG bit 3
                 SegIter<PASS> si;
                 si.init(p, 0);
                 Seg it;
@@ -542,10 +671,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
                     const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;           // TMEM columns
                     const uint32_t as_h0 = ring_s + kASmemOff + ab * kOperandBytes, as_h1 = as_h0 + kPartBytes;  // kASmem
-                    const bool acct = DBG && (p.dbg & 8);
-                    long long c0 = acct ? clock64() : 0;
                     mbar_wait_t<DBG>(bar_afull + 8 * ab, abphase);
-                    if (acct) w_afull += clock64() - c0;
                     tc_fence_after();
                     for (int t = it.ta; t < it.tb; ++t, ++n_tile) {
                         if (kMmaWarps > 1 && (n_tile & 1u) != mi) {  // the other warp's tile
@@ -559,11 +685,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                             const uint32_t k_other = mi ? (n_tile >> 1) : (n_tile >> 1) - 1u;
                             mbar_wait_t<DBG>(bar_turn + 8 * (mi ^ 1u), k_other & 1u);
                         }
-                        c0 = acct ? clock64() : 0;
                         mbar_wait_t<DBG>(bar_tempty + 8 * acc, aphase ^ 1);
-                        const long long c1 = acct ? clock64() : 0;
                         mbar_wait_t<DBG>(bar_full + 8 * stage, sphase);
-                        if (acct) { w_tempty += c1 - c0; w_full += clock64() - c1; }
                         if (kMmaWarps > 1) {
                             if (elect_one()) mbar_arrive(bar_turn + 8 * mi);
                             __syncwarp();
@@ -601,9 +724,6 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     if (elect_one()) tc_commit(bar_aempty + 8 * ab);      // fixed-operand buffer reusable
                     __syncwarp();
                 }
-                if (DBG && (p.dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
-                    printf("K2 pass %d cta %d MMA warp: waited %lld cycles for the fixed operand, %lld for a free accumulator, "
-                           "%lld for streamed tiles, of %lld\n", PASS, blockIdx.x, w_afull, w_tempty, w_full, clock64() - c_start);
             }
         }
     } else if (wg == kEpiGroups + 1) {
@@ -647,9 +767,12 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         // Every warp runs on its own: no block or group barrier anywhere, only the accumulator
         // mbarriers.  The loop is software-pipelined across tiles AND items: while the exp2 loop
         // runs on one 64-column half, the tcgen05.ld of the next half (or of the next tile's first
-        // half) is in flight, and the next tile's lse values (pass 2; each warp stages all 128 of
-        // them for itself) are on their way from L2.  When the sequence moves to another item the
-        // per-row partial results are stored to this (piece, group) slot.
+        // half) is in flight, and the next tile's per-query values (pass 2; each warp stages all 128
+        // of them for itself) are on their way from L2.  When the sequence moves to another item the
+        // per-row partial results are stored to this (piece, group) slot.  The loop exists twice:
+        // FAST (bounded logits, see pass1_fast) and the general form; the choice is launch-wide.
+        auto epilogue = [&](auto fast_tag) {
+        constexpr bool FAST = decltype(fast_tag)::value;
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
         const int grp = wg - 1;                     // this group takes tiles grp, grp + kEpiGroups, ...
         const int row = q4 * 32 + lane;
@@ -657,20 +780,21 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const uint32_t lse_w = base + kLseOff + (uint32_t)(warp - 4) * (2u * kTile * 4u);  // two 128-float buffers per warp
         const int S = p.S, dbg = DBG ? p.dbg : 0;
         const bool causal = p.causal != 0;
-        const float cs = p.cs;
-        const float* __restrict__ lse2 = p.lse2;
+        // pass 2 stages one value per query of the tile: w = 2^-lse (FAST; 0 past S) or lse (+inf past S)
+        const float* __restrict__ qval = FAST ? p.w2 : p.lse2;
+        const float qfill = FAST ? 0.f : INFINITY;
         const bool lse_vec = (S & 3) == 0;
         const int last_tile = (S - 1) / kTile, last_col = (S - 1) % kTile;
         const size_t rows = (size_t)p.B * p.H * S;
+        const int nb = p.nb;
 
         SegIter<PASS> nx;                           // runs one tile ahead of the tile being processed
         nx.init(p, 0);
         const int first_bh = nx.bh, first_blk = nx.blk;
         const int first_part = nx.t != nx.t0(nx.blk);  // the range starts inside an item
         nx.advance(grp);
-        uint32_t gn = (uint32_t)grp;                // number of the tile inside the CTA's range
         int st_bh = -1, st_blk = 0;                 // item whose partial results are in registers
-        float m = -INFINITY, l = 0.f;               // pass 1
+        float m = FAST ? 0.f : -INFINITY, l = 0.f;  // pass 1
         float colsum = 0.f, lastp = 0.f;            // pass 2
         bool saw_last = false;
 
@@ -686,23 +810,35 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 if (saw_last) p.part_last[o] = lastp;
             }
         };
+        // general form only: 2^(exponents) of the two operand blocks of a tile, 1 unless a block was
+        // pre-scaled into fp16 range (eblk: Q blocks first, then K blocks)
+        auto tile_scale = [&](int bh, int blk, int t) -> float {
+            if (FAST || !scaled) return 1.0f;
+            const int kv = (bh / p.H) * p.KVH + (bh % p.H) / group;
+            const int qb = PASS == 1 ? blk : t, kb = PASS == 1 ? t : blk;
+            const int e = __ldg(p.eblk + (size_t)bh * nb + qb) + __ldg(p.eblk + (size_t)p.B * p.H * nb + (size_t)kv * nb + kb);
+            return __int_as_float((127 + min(max(e, -126), 127)) << 23);
+        };
 
         float va[kChunk], vb[kChunk];               // chunk c of a tile sits in va (c even) or vb (c odd)
         if (dbg & 4) {
 #pragma unroll
             for (int i = 0; i < kChunk; ++i) va[i] = vb[i] = (float)(row + i) * 0.01f;
         }
-        uint32_t lb = 0;                            // lse buffer of the current tile
-        long long clk_math = 0, clk_loop = DBG ? clock64() : 0;
-        long long clk_seg[1 + 2 * kChunks] = {};    // DBG bit 3: loop head, then per chunk: before / after its body
-        long long clk_late = 0, clk_ldw = 0;
-        int n_late = 0;
-        const bool acct = DBG && (p.dbg & 8);
-        uint32_t acc_i = (uint32_t)grp % kAcc, acc_ph = 0;  // accumulator (gn % kAcc) and barrier phase of the current tile
+        uint32_t lb = 0;                            // per-query value buffer of the current tile
+        uint32_t acc_i = (uint32_t)grp % kAcc, acc_ph = 0;  // accumulator (tile number % kAcc) and barrier phase of the current tile
         bool have = nx.valid();
+#if SPLITQ_K2_GROUP_DELAY > 0
+        // phase offset between the epilogue groups: two warps that share a sub-partition's MUFU pipe keep
+        // whatever offset they start with (see benchmarks/experiments/README.md)
+        if (grp > 0) {
+            const long long t0 = clock64();
+            while (clock64() - t0 < (long long)SPLITQ_K2_GROUP_DELAY * grp) {}
+        }
+#endif
         if (have) {
             if (PASS == 2) {
-                sts128(lse_w + 16u * lane, load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec));
+                sts128(lse_w + 16u * lane, load_lse4(qval + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec, qfill));
                 __syncwarp();
             }
             mbar_wait_t<DBG>(bar_tfull + 8 * acc_i, acc_ph);
@@ -711,13 +847,12 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             tc_ld_wait();
         }
         while (have) {
-            long long tseg = acct ? clock64() : 0;
-            // ---- the tile being processed: number gn = (bh, blk, t), where nx stands before it moves on
+            // ---- the tile being processed: (bh, blk, t), where nx stands before it moves on
             const int bh = nx.bh, blk = nx.blk, t = nx.t;
             const uint32_t a = acc_i;
             const uint32_t cur_tmem = tmem_lane + a * kTile;
             // ---- look one tile ahead: is its accumulator ready (asked early, the answer takes ~100
-            // cycles), and start fetching its lse values
+            // cycles), and start fetching its per-query values
             uint32_t na = a + (uint32_t)(kEpiGroups % kAcc), nph = acc_ph;
             if (na >= (uint32_t)kAcc) { na -= (uint32_t)kAcc; nph ^= 1u; }
             if (kEpiGroups >= kAcc) nph ^= 1u;
@@ -725,14 +860,15 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const bool has_next = nx.valid();
             bool ready = has_next && mbar_test(bar_tfull + 8 * na, nph);
             float4 lse_nx = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (PASS == 2 && has_next) lse_nx = load_lse4(lse2 + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec);
+            if (PASS == 2 && has_next) lse_nx = load_lse4(qval + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec, qfill);
             // ---- entering a new item: store what the registers hold
             if (bh != st_bh || blk != st_blk) {
                 flush();
-                m = -INFINITY; l = 0.f; colsum = 0.f; lastp = 0.f; saw_last = false;
+                m = FAST ? 0.f : -INFINITY; l = 0.f; colsum = 0.f; lastp = 0.f; saw_last = false;
                 st_bh = bh;
                 st_blk = blk;
             }
+            const float cs = tile_scale(bh, blk, t);
             const bool diag = causal && t == blk;   // the causal boundary runs through this tile
             const bool has_last = PASS == 2 && last_tile == t;
             saw_last = saw_last || has_last;
@@ -744,7 +880,6 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const bool edge1 = diag || s_hi < kTile - 1;
             float lastv = 0.f;
             if (has_last && !(dbg & 4)) tc_ld1_issue(cur_tmem + (uint32_t)last_col, lastv);  // lands with the next wait
-            if (acct) { const long long now = clock64(); clk_seg[0] += now - tseg; tseg = now; }
 #pragma unroll
             for (int c = 0; c < kChunks; ++c) {
                 float (&cur)[kChunk] = (c & 1) ? vb : va;
@@ -760,21 +895,30 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
                     }
                 }
-                const long long tm0 = (DBG && (dbg & 8)) ? clock64() : 0;
-                if (acct) clk_seg[1 + 2 * c] += tm0 - tseg;
                 if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
                 else if (PASS == 1) {
-                    if (edge1) pass1_body<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
-                    else pass1_body<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                    if (FAST) {
+                        if (edge1) pass1_fast<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, l);
+                        else pass1_fast<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, l);
+                    } else {
+                        if (edge1) pass1_body<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                        else pass1_body<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                    }
                 } else {
-                    if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
-                    else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
+                    if (FAST) {
+                        if (diag) pass2_fast<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, colsum);
+                        else pass2_fast<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, colsum);
+                    } else {
+                        if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
+                        else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
+                    }
                 }
-                if (acct) { tseg = clock64(); clk_math += tseg - tm0; }
                 if (c + 1 < kChunks) {
                     tc_ld_wait();
-                    if (c == 0 && has_last)           // p[S-1][key]: the last query is never masked
-                        lastp = ex2(fmaf(lastv, cs, -lds32(lse_t + 4u * (uint32_t)last_col)));
+                    if (c == 0 && has_last) {         // p[S-1][key]: the last query is never masked
+                        const float qv = lds32(lse_t + 4u * (uint32_t)last_col);
+                        lastp = FAST ? ex2(lastv) * qv : ex2(fmaf(lastv, cs, -qv));
+                    }
                     if (c + 2 == kChunks) {           // the last chunk is in registers: accumulator drained
                         tc_fence_before();
                         __syncwarp();
@@ -782,34 +926,23 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     }
                 } else if (has_next) {
                     if (!ready) {
-                        const long long w0 = acct ? clock64() : 0;
                         mbar_wait_t<DBG>(bar_tfull + 8 * na, nph);
-                        if (acct) { clk_late += clock64() - w0; ++n_late; }
                         tc_fence_after();
                         if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
                     }
-                    const long long w1 = acct ? clock64() : 0;
                     tc_ld_wait();                     // next tile's first chunk landed
-                    if (acct) clk_ldw += clock64() - w1;
-                    __syncwarp();                     // the lse values staged by the other lanes are visible
+                    __syncwarp();                     // the per-query values staged by the other lanes are visible
                     lb ^= 1u;
-                    gn += kEpiGroups;
                     acc_i = na;
                     acc_ph = nph;
                 }
-                if (acct) { const long long now = clock64(); clk_seg[2 + 2 * c] += now - tseg; tseg = now; }
             }
             have = has_next;
         }
         flush();
-        if (DBG && (dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))  // bit 3: cycle accounting
-            printf("K2 pass %d cta %d warp %d: %lld cycles in the math bodies of %lld in the tile loop, %d tiles; loop head %lld, "
-                   "before/after body 0: %lld / %lld, before/after the last body: %lld / %lld\n", PASS, blockIdx.x, warp, clk_math,
-                   clock64() - clk_loop, (int)(gn / kEpiGroups), clk_seg[0], clk_seg[1], clk_seg[2], clk_seg[2 * kChunks - 1],
-                   clk_seg[2 * kChunks]);
-        if (DBG && (dbg & 8) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
-            printf("K2 pass %d cta %d warp %d: next accumulator not ready after the last body %d times (%lld cycles waited), "
-                   "%lld cycles in the wait for its first TMEM load\n", PASS, blockIdx.x, warp, n_late, clk_late, clk_ldw);
+        };
+        if (fast) epilogue(std::true_type{});
+        else epilogue(std::false_type{});
     }
 
     tc_fence_before();
@@ -821,47 +954,114 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
 }
 
 // ---- operand preparation: fp32 -> fp16 h0 = fp16(x) and h1 = fp16(x - h0), gathered from arbitrary
-// (b,h,s) strides into dense (n, S, 64) fp16 arrays (one 128-byte row per token) ----
+// (b,h,s) strides into dense (n, S, 64) fp16 arrays (one 128-byte row per token).  One CTA = one
+// 128-row block of one head of Q (blockIdx.y < BH) or of K.  Q is multiplied by scaling * log2(e)
+// first, so the tensor-core products are log2-domain logits.  Per block the kernel also records
+//   bound2: the largest squared row norm (of the values as they enter the products' true magnitude),
+//           from which the passes bound every logit of the launch (FAST epilogue), and
+//   eblk:   e such that the block was multiplied by 2^-e before the fp16 conversion: operands beyond
+//           the fp16 range (or far below it) lose nothing but a power of two, which the epilogue
+//           multiplies back per tile (e = 0 for any ordinary activation).  Inside a block that is not
+//           pre-scaled, elements below 2^-3 carry an absolute error of up to 2^-25 instead of a
+//           relative one of 2^-23 (the low fp16 part is subnormal there).
+struct SplitArgs {
+    const float *q, *k;
+    long long qs[3], ks[3];   // element strides of (b, head, s)
+    int H, KVH, S, nb, BH;
+    int vecq, veck;
+    float cs;                 // scaling * log2(e), folded into Q
+    uint2 *q0, *q1, *k0, *k1; // h0 / h1 parts
+    float2* ml;               // result slots preset by the Q blocks: (kSlots, rows) (max, sum) = (-inf, 0)
+    float* part_col;          // (kSlots, rows) = 0
+    size_t rows;
+    float* bound2;            // (BH + BKV) * nb
+    int* eblk;                // (BH + BKV) * nb
+};
 __global__ void __launch_bounds__(256)
-split_f16_kernel(const float* __restrict__ x, long long sb, long long sh, long long ss, int heads, int S,
-                 uint2* __restrict__ h0, uint2* __restrict__ h1, int vec, float2* __restrict__ ml,
-                 float* __restrict__ part_col, size_t rows) {
-    // grid.y = b * heads + h (one division per CTA); grid.x strides over the S*16 float4 of that
-    // head, 4 per thread with 256-thread spacing so every warp access is contiguous
-    const int bh = blockIdx.y;
+split_f16_kernel(const SplitArgs a) {
+    __shared__ float s_red[2][8];
+    const int y = blockIdx.y;
+    const bool isq = y < a.BH;
+    const int bh = isq ? y : y - a.BH;
+    const int heads = isq ? a.H : a.KVH;
     const int b = bh / heads, h = bh - b * heads;
-    const float* src0 = x + b * sb + h * sh;
-    const int n4 = S * (kHd / 4);
-    uint2* o0 = h0 + (size_t)bh * n4;
-    uint2* o1 = h1 + (size_t)bh * n4;
-    constexpr int UN = 4;
-    const int i0 = blockIdx.x * (256 * UN) + threadIdx.x;
+    const long long* st = isq ? a.qs : a.ks;
+    const float* src0 = (isq ? a.q : a.k) + b * st[0] + h * st[1];
+    const bool vec = isq ? a.vecq : a.veck;
+    const float pre = isq ? a.cs : 1.0f;
+    const int row0 = blockIdx.x * kTile;
+    constexpr int UN = kTile * (kHd / 4) / 256;  // 8 float4 per thread; 16 consecutive threads share a row
     float4 v[UN];
+    uint32_t amax = 0u;
+    float rmax = 0.f;
 #pragma unroll
     for (int u = 0; u < UN; ++u) {
-        const int i = i0 + u * 256;
-        if (i < n4) {
-            const float* src = src0 + (long long)(i >> 4) * ss + (i & 15) * 4;
+        const int i = threadIdx.x + 256 * u;
+        const int r = row0 + (i >> 4);
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < a.S) {
+            const float* src = src0 + (long long)r * st[2] + (i & 15) * 4;
             if (vec) v[u] = __ldg(reinterpret_cast<const float4*>(src));
             else v[u] = make_float4(__ldg(src), __ldg(src + 1), __ldg(src + 2), __ldg(src + 3));
         }
+        v[u].x *= pre; v[u].y *= pre; v[u].z *= pre; v[u].w *= pre;
     }
 #pragma unroll
     for (int u = 0; u < UN; ++u) {
-        const int i = i0 + u * 256;
-        if (i < n4) {
-            const __half2 a01 = __floats2half2_rn(v[u].x, v[u].y), a23 = __floats2half2_rn(v[u].z, v[u].w);
+        amax = max(amax, __float_as_uint(v[u].x) & 0x7fffffffu);
+        amax = max(amax, __float_as_uint(v[u].y) & 0x7fffffffu);
+        amax = max(amax, __float_as_uint(v[u].z) & 0x7fffffffu);
+        amax = max(amax, __float_as_uint(v[u].w) & 0x7fffffffu);
+        float ss = fmaf(v[u].x, v[u].x, fmaf(v[u].y, v[u].y, fmaf(v[u].z, v[u].z, v[u].w * v[u].w)));
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);  // the 16 lanes of one row
+        rmax = fmaxf(rmax, ss == ss ? ss : INFINITY);
+    }
+    amax = __reduce_max_sync(0xffffffffu, amax);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rmax = fmaxf(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        s_red[0][warp] = __uint_as_float(amax);
+        s_red[1][warp] = rmax;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        amax = max(amax, __float_as_uint(s_red[0][w]));
+        rmax = fmaxf(rmax, s_red[1][w]);
+    }
+    // a block whose maximum lies in [2^-10, 2^15) stays as it is (every ordinary activation); otherwise
+    // 2^-e brings the block maximum into [2^14, 2^15): down from beyond the fp16 range, or up from so far
+    // below it that the fp16 parts would be subnormal (e < 0)
+    const int ex = (int)(amax >> 23) - 127;
+    const int e = (ex >= 15 || (ex < -10 && amax != 0u)) ? ex - 14 : 0;
+    const float sc = __int_as_float((127 - e) << 23);
+    if (threadIdx.x == 0) {
+        a.bound2[(size_t)y * a.nb + blockIdx.x] = rmax;
+        a.eblk[(size_t)y * a.nb + blockIdx.x] = e;
+    }
+    const size_t n4 = (size_t)a.S * (kHd / 4);
+    uint2* o0 = (isq ? a.q0 : a.k0) + (size_t)bh * n4 + (size_t)row0 * (kHd / 4);
+    uint2* o1 = (isq ? a.q1 : a.k1) + (size_t)bh * n4 + (size_t)row0 * (kHd / 4);
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+        const int i = threadIdx.x + 256 * u;
+        const int r = row0 + (i >> 4);
+        if (r < a.S) {
+            const float x0 = v[u].x * sc, x1 = v[u].y * sc, x2 = v[u].z * sc, x3 = v[u].w * sc;
+            const __half2 a01 = __floats2half2_rn(x0, x1), a23 = __floats2half2_rn(x2, x3);
             const float2 f01 = __half22float2(a01), f23 = __half22float2(a23);
-            const __half2 l01 = __floats2half2_rn(v[u].x - f01.x, v[u].y - f01.y);
-            const __half2 l23 = __floats2half2_rn(v[u].z - f23.x, v[u].w - f23.y);
+            const __half2 l01 = __floats2half2_rn(x0 - f01.x, x1 - f01.y);
+            const __half2 l23 = __floats2half2_rn(x2 - f23.x, x3 - f23.y);
             o0[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a01), *reinterpret_cast<const uint32_t*>(&a23));
             o1[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
-            if (ml && (i & 15) == 0) {  // the Q launch also presets the result slots of its (b,h,s) row
-                const size_t r = (size_t)bh * S + (i >> 4);
+            if (isq && (i & 15) == 0) {  // the Q blocks also preset the result slots of their (b,h,s) rows
+                const size_t rr = (size_t)bh * a.S + r;
 #pragma unroll
                 for (int sl = 0; sl < kSlots; ++sl) {
-                    ml[sl * rows + r] = make_float2(-INFINITY, 0.f);
-                    part_col[sl * rows + r] = 0.f;
+                    a.ml[sl * a.rows + rr] = make_float2(-INFINITY, 0.f);
+                    a.part_col[sl * a.rows + rr] = 0.f;
                 }
             }
         }
@@ -871,7 +1071,7 @@ split_f16_kernel(const float* __restrict__ x, long long sb, long long sh, long l
 // pass 1 leaves up to kSlots (max, sum) pairs per row (two pieces of a cut item x two epilogue
 // groups; unused slots hold (-inf, 0)); merge them in slot order into the log2-domain lse
 __global__ void __launch_bounds__(256)
-lse_combine_kernel(const float2* __restrict__ ml, size_t n, float* __restrict__ lse2) {
+lse_combine_kernel(const float2* __restrict__ ml, size_t n, float* __restrict__ lse2, float* __restrict__ w2) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float2 v[kSlots];
@@ -885,7 +1085,9 @@ lse_combine_kernel(const float2* __restrict__ ml, size_t n, float* __restrict__ 
     float sum = 0.f;
 #pragma unroll
     for (int sl = 0; sl < kSlots; ++sl) sum += v[sl].x > -INFINITY ? v[sl].y * exp2f(v[sl].x - mm) : 0.f;
-    lse2[i] = mm + log2f(sum);
+    const float lse = mm + log2f(sum);
+    lse2[i] = lse;
+    w2[i] = exp2f(-lse);  // only read by the FAST epilogue, whose bound keeps it a normal number
 }
 
 struct HeadW {
@@ -1004,15 +1206,17 @@ static int make_map(CUtensorMap* map, void* base, int S, long long n, size_t par
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
 
 struct WsLayout {
-    size_t q0, q1, k0, k1, lse, pcol, plast, ml, total;  // fp16 h0 / h1 parts of Q and K, then per-(b,h,s) floats
+    size_t q0, q1, k0, k1, lse, pcol, plast, ml, w2, bound2, eblk, total;  // fp16 h0 / h1 parts of Q and K, per-(b,h,s) floats, per-block facts
 };
 static WsLayout ws_layout(int B, int H, int KVH, int S) {
     WsLayout w;
     const size_t q = align256((size_t)B * H * S * kHd * 2), k = align256((size_t)B * KVH * S * kHd * 2);
     const size_t v = align256((size_t)B * H * S * 4);
+    const size_t blk = align256((size_t)B * (H + KVH) * cdiv(S, kTile) * 4);
     w.q0 = 0; w.q1 = q; w.k0 = 2 * q; w.k1 = 2 * q + k;
     w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + kSlots * v; w.ml = w.plast + v;
-    w.total = w.ml + 2 * kSlots * v;
+    w.w2 = w.ml + 2 * kSlots * v; w.bound2 = w.w2 + v; w.eblk = w.bound2 + blk;
+    w.total = w.eblk + blk;
     return w;
 }
 
@@ -1038,7 +1242,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
                    "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
     SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
                    "materialised path splitq_importance_colmean", hd);
-    const int dbg = (mode >> 4) & 31;  // undocumented timing-experiment bits
+    const int dbg = (mode >> 4) & 63;  // undocumented timing-experiment bits
     mode &= 15;
     SPLITQ_REQUIRE(mode == SPLITQ_FUSED_F16X3 || mode == SPLITQ_FUSED_F16X1, SPLITQ_ERR_ARG,
                    "importance_fused: unknown mode %d", mode);
@@ -1065,18 +1269,23 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
         return SPLITQ_OK;
     }
 
-    {   // operand split
+    const int nb = cdiv(S, kTile);
+    {   // operand split: one launch for Q and K
         auto vec_ok = [](const float* p, const long long* s) {
             return aligned16(p) && s[0] % 4 == 0 && s[1] % 4 == 0 && s[2] % 4 == 0;
         };
-        SPLITQ_REQUIRE((long long)B * H <= 65535, SPLITQ_ERR_ARG, "importance_fused: B*H=%lld > 65535", (long long)B * H);
-        const unsigned gx = (unsigned)cdiv((long long)S * (kHd / 4), 256 * 4);
-        split_f16_kernel<<<dim3(gx, B * H), 256, 0, st>>>(Q, q_strides_host[0], q_strides_host[1], q_strides_host[2], H, S,
-                                                       (uint2*)(w8 + wl.q0), (uint2*)(w8 + wl.q1), vec_ok(Q, q_strides_host),
-                                                       (float2*)(w8 + wl.ml), (float*)(w8 + wl.pcol), (size_t)B * H * S);
-        split_f16_kernel<<<dim3(gx, B * KVH), 256, 0, st>>>(K, k_strides_host[0], k_strides_host[1], k_strides_host[2], KVH, S,
-                                                         (uint2*)(w8 + wl.k0), (uint2*)(w8 + wl.k1), vec_ok(K, k_strides_host),
-                                                         nullptr, nullptr, 0);
+        SPLITQ_REQUIRE((long long)B * (H + KVH) <= 65535, SPLITQ_ERR_ARG, "importance_fused: B*(H+KVH)=%lld > 65535",
+                       (long long)B * (H + KVH));
+        SplitArgs a;
+        a.q = Q; a.k = K;
+        for (int i = 0; i < 3; ++i) { a.qs[i] = q_strides_host[i]; a.ks[i] = k_strides_host[i]; }
+        a.H = H; a.KVH = KVH; a.S = S; a.nb = nb; a.BH = B * H;
+        a.vecq = vec_ok(Q, q_strides_host); a.veck = vec_ok(K, k_strides_host);
+        a.cs = scaling * 1.4426950408889634f;
+        a.q0 = (uint2*)(w8 + wl.q0); a.q1 = (uint2*)(w8 + wl.q1); a.k0 = (uint2*)(w8 + wl.k0); a.k1 = (uint2*)(w8 + wl.k1);
+        a.ml = (float2*)(w8 + wl.ml); a.part_col = (float*)(w8 + wl.pcol); a.rows = (size_t)B * H * S;
+        a.bound2 = (float*)(w8 + wl.bound2); a.eblk = (int*)(w8 + wl.eblk);
+        split_f16_kernel<<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
         SPLITQ_LAUNCH_CHECK("split_f16_kernel");
     }
 
@@ -1086,11 +1295,12 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     if (int rc = make_map(&mk, w8 + wl.k0, S, (long long)B * KVH, wl.k1 - wl.k0, parts)) return rc;
 
     Params p;
-    p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = cdiv(S, kTile);
+    p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = nb;
+    p.nq_blk = B * H * nb; p.nk_blk = B * KVH * nb;
+    p.w2 = (float*)(w8 + wl.w2); p.bound2 = (const float*)(w8 + wl.bound2); p.eblk = (const int*)(w8 + wl.eblk);
     p.causal = causal ? 1 : 0;
     p.x3 = mode == SPLITQ_FUSED_F16X3;
     p.dbg = dbg;
-    p.cs = scaling * 1.4426950408889634f;
     p.lse2 = (float*)(w8 + wl.lse);
     p.ml = (float2*)(w8 + wl.ml);
     p.part_col = (float*)(w8 + wl.pcol);
@@ -1125,7 +1335,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     if (dbg) fused_importance_kernel<1, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     else fused_importance_kernel<1, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 1)");
-    lse_combine_kernel<<<(unsigned)cdiv((long long)rows, 256), 256, 0, st>>>(p.ml, rows, p.lse2);
+    lse_combine_kernel<<<(unsigned)cdiv((long long)rows, 256), 256, 0, st>>>(p.ml, rows, p.lse2, p.w2);
     if (dbg) fused_importance_kernel<2, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     else fused_importance_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
     SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 2)");

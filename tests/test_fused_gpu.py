@@ -101,16 +101,62 @@ def test_last_row_only_uses_the_gemv_path_and_matches(B, H, KVH, S):
     assert max_rel(both_last.cpu(), want_last) <= 1e-5
 
 
-def test_fused_out_of_fp16_range_fails_loudly():
-    """The tensor-core products run on fp16 operands: |q|,|k| >= 65504 overflow there.  The
-    documented behaviour is non-finite scores (loud) in both modes, never a silently wrong ranking."""
+GENERAL_PATH = 32 << 4  # undocumented mode bit: never take the bounded-logit (FAST) epilogue
+
+
+def test_fused_beyond_fp16_range_is_prescaled_not_nan():
+    """The tensor-core products run on fp16 operands.  A 128-row block whose largest |x| reaches 2^15 is
+    multiplied by a power of two before the conversion and the epilogue multiplies it back per tile,
+    so activations beyond 65504 score correctly instead of overflowing to NaN."""
     gen = torch.Generator().manual_seed(1)
     q, k = make_qk(gen, 1, 2, 2, 256, 1.0)
     q[0, 0, 5, 3] = 1.0e5
-    col, _ = splitq.importance_fused(q.to(DEV), k.to(DEV), 1e-6)
-    assert torch.isnan(col).any()
+    k[0, 1, 200, 7] = -3.0e6
+    col, last = splitq.importance_fused(q.to(DEV), k.to(DEV), 1e-6, want_last=True)
+    A = O.attention_probs(q, k, 1e-6, True)
+    want_col, want_last = O.importance_regular(A), O.importance_last_row(A)
+    assert torch.isfinite(col).all()
+    assert max_rel(col[0].cpu(), want_col) <= 1e-5
+    assert max_rel(last[0].cpu(), want_last) <= 1e-5
     col1, _ = splitq.importance_fused(q.to(DEV), k.to(DEV), 1e-6, mode=N.FUSED_F16X1)
-    assert not torch.isfinite(col1).all()
+    assert torch.isfinite(col1).all() and max_rel(col1[0].cpu(), want_col) <= 2e-2
+    # non-finite inputs stay loud
+    q[0, 1, 7, 0] = float("inf")
+    bad, _ = splitq.importance_fused(q.to(DEV), k.to(DEV), 1e-6)
+    assert not torch.isfinite(bad).all()
+
+
+@pytest.mark.parametrize("B,H,KVH,S,sigma", [(1, 4, 2, 512, 1.0), (2, 6, 3, 333, 1.2), (1, 14, 2, 1024, 2.0)])
+def test_fused_general_epilogue_forced(B, H, KVH, S, sigma):
+    """Inputs whose norms prove |logit| < 100 take the epilogue without a running maximum; the general
+    epilogue (online maximum, per-tile scale) is forced here on the same inputs and must agree with
+    the oracle and, to rounding, with the bounded path."""
+    gen = torch.Generator().manual_seed(S + H)
+    q, k = make_qk(gen, B, H, KVH, S, sigma)
+    want_col, want_last = oracle_scores(q, k, True)
+    col_g, last_g = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_last=True, mode=N.FUSED_F16X3 | GENERAL_PATH)
+    col_f, last_f = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_last=True)
+    for got_c, got_l in ((col_g, last_g), (col_f, last_f)):
+        assert max_rel(got_c.cpu(), want_col) <= 1e-5
+        assert max_rel(got_l.cpu(), want_last) <= 1e-5
+    assert max_rel(col_g, col_f) <= 2e-6
+
+
+@pytest.mark.parametrize("q_sigma,k_sigma", [(0.1, 20.0), (100.0, 0.02), (3.0, 3.0)])
+def test_fused_large_norms_take_the_general_epilogue(q_sigma, k_sigma):
+    """Operand norms beyond the caps of the bounded-logit path (|k| = 160, or |q * scaling * log2 e| =
+    144, or their product above 100): the general epilogue runs by itself.  Against fp64; the
+    (3, 3) case has logits of standard deviation 9 (|s| up to ~45), where an fp32 matmul is itself
+    only good to ~1e-5 on the smallest probabilities, hence the looser bar there."""
+    B, H, KVH, S = 1, 4, 2, 768
+    gen = torch.Generator(device=DEV).manual_seed(int(q_sigma * 10))
+    q = torch.randn(B, H, S, 64, device=DEV, generator=gen) * q_sigma
+    k = torch.randn(B, KVH, S, 64, device=DEV, generator=gen) * k_sigma
+    want_col, want_last = fp64_scores(q, k)
+    col, last = splitq.importance_fused(q, k, 0.125, want_last=True)
+    tol = 1e-5 if q_sigma * k_sigma < 4 else 1e-4
+    assert max_rel(col, want_col.float()) <= tol
+    assert max_rel(last, want_last.float()) <= tol
 
 
 @pytest.mark.parametrize("S", [127, 129, 255, 257, 640])
