@@ -116,6 +116,24 @@ int splitq_select_bits(const float* imp, int B, int S, int D, const int* ladder_
                        const int* ladder_bits_host, int n_ladder, uint8_t* bits_out,
                        uint32_t* row_off_out, splitq_stream_t stream);
 
+/* Same selection with ONE rung of `bits` bits whose size differs per window.  Replaces the two
+ * token-set rules of the reference's first experiment (Experiments/Pythia-70M/pythia_model.py):
+ *   k_host != NULL              window b quantises its k_host[b] least important tokens -- the rule of
+ *                               batched_quantization_helper (:141-142, `ordering[:int(0.1*ratio*len)]`);
+ *   mass_threshold_host != NULL "top-rho", batched_top_rho_quantization (:93-109): walking the tokens
+ *                               from the most important down, keep them while the importance mass
+ *                               taken so far is below mass_threshold_host[b] (the reference uses
+ *                               1 - 0.1*ratio) and quantise all the others.  (The reference then slices
+ *                               with a token id where a rank is meant; the intended rule is built.)
+ *                               Masses are summed as 2^-47 fixed-point integers of the scores clamped
+ *                               to [0, 1], so the kept count is independent of summation order.
+ * Exactly one of the two host arrays is given (B entries).  k_out (device, B ints, nullable) receives
+ * the number of quantised tokens per window.  Payloads of such windows differ in size: size the
+ * payload buffer for the all-raw case, splitq_payload_bytes(S, D, NULL, NULL, 0, mode). */
+int splitq_select_bits_per_window(const float* imp, int B, int S, int D, int bits, const int* k_host,
+                                  const double* mass_threshold_host, uint8_t* bits_out,
+                                  uint32_t* row_off_out, int* k_out, splitq_stream_t stream);
+
 /* ---- absmax + quantise + bit-pack (K3) -------------------------------------------------
  * Replaces the scale/clamp/round block (pythia_model.py:176-184, qwen_layer_wise.py:60-66)
  * and emits what the reference never materialises: integer codes packed into one payload.
@@ -182,6 +200,14 @@ size_t splitq_channel_workspace_bytes(int B, int S, int D);
 int splitq_channel_fake_quant(const float* h, int B, int S, int D, int method, float* stats_out,
                               float* h_out, int8_t* codes_out, void* ws, size_t ws_bytes,
                               splitq_stream_t stream);
+
+/* ---- layer-distance analytics -----------------------------------------------------------
+ * Replaces the triple Python loop of Notebooks/distributions_distance_across_layers.ipynb (cells 12,
+ * 13, 16: KL in bits with a p != 0 guard, Jensen-Shannon divergence, every layer pair i < j, every
+ * sample): dist (L,N,S) fp32 importance distributions of L layers over N samples ->
+ * js_out (L,L,N) fp64, entry [i][j][n] = JS(dist[i][n], dist[j][n]) for i < j (other entries are
+ * left untouched).  fp64 arithmetic, fixed reduction order. */
+int splitq_layer_js(const float* dist, int L, int N, int S, double* js_out, splitq_stream_t stream);
 
 /* ---- transfer --------------------------------------------------------------------------
  * The device hop the reference only simulates (in-place quant->dequant,

@@ -7,17 +7,41 @@
 // preserving integer image of the fp32 scores (4 histogram passes, no sort), resolves ties in
 // favour of the lower token index with a block scan, and emits the per-token width map plus the
 // exclusive prefix sum of row sizes that the pack kernel uses as row offsets.
+//
+// What keeps the pass chain short (it is pure latency: S floats per window):
+//   * the four histograms of every rung live in shared memory side by side and are cleared once,
+//     so a pass is "atomics, barrier, one warp per rung scans 256 bins, barrier";
+//   * pass 0 is the same for every rung (no prefix yet): one histogram, one warp-aggregated
+//     atomic per key (importance scores share a handful of exponents, plain atomics would
+//     serialise); later passes touch only the keys inside a rung's pivot bin -- a whole warp
+//     skips them with one vote;
+//   * the tie scan is skipped when the last histogram shows that every key equal to a pivot is
+//     selected anyway (always, unless scores repeat exactly at a rung boundary).
+//
+// Second mode ("top-rho", Experiments/Pythia-70M/pythia_model.py:93-109 `batched_top_rho_
+// quantization`): keep the fewest most-important tokens whose importance mass reaches a
+// threshold and quantise the rest.  The kept count comes from the same radix machinery run from
+// the top with a mass histogram beside the count histogram; masses are 2^-47 fixed-point
+// integers (values clamped to [0, 1]), so the sums -- and the count -- do not depend on the order of
+// the atomics and equal the oracle's integer arithmetic exactly.
 #include "common.cuh"
 
 namespace splitq {
 
 constexpr int kSelThreads = 1024;
+constexpr int kSelMaxWindows = 32;  // windows per launch of the per-window modes (kernel-parameter space)
 
 struct Ladder {
     int n;
     int thresh[SPLITQ_MAX_LADDER];       // cumulative token counts
     int bits[SPLITQ_MAX_LADDER];
     uint32_t rb16[SPLITQ_MAX_LADDER + 1];  // row bytes / 16 per rung; last = raw fp32
+};
+// per-window overrides of the single rung's count (mode 1) or the mass threshold it is derived from (mode 2)
+struct PerWindow {
+    int mode;                             // 0: ladder as given; 1: k[w] tokens; 2: top-rho with threshold mass[w]
+    int k[kSelMaxWindows];
+    unsigned long long mass[kSelMaxWindows];  // ceil(threshold * 2^47)
 };
 
 // fp32 -> uint32 such that a < b  <=>  key(a) < key(b); -0.0 and +0.0 map to the same key
@@ -26,134 +50,257 @@ __device__ __forceinline__ uint32_t order_key(float f) {
     if (u == 0x80000000u) u = 0u;
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
+__device__ __forceinline__ float key_value(uint32_t k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+// importance mass of one token as a 2^-47 fixed-point integer: values are clamped to [0, 1] (NaN -> 0)
+__device__ __forceinline__ unsigned long long mass_of(float v) {
+    v = fminf(fmaxf(v, 0.f), 1.f);                      // fmaxf(NaN, 0) = 0
+    return (unsigned long long)(v * 140737488355328.0f);  // exact: a power-of-two scaling, then truncation
+}
 
-struct U4 {
-    uint32_t v[4];
-};
-
-// exclusive prefix sum of four counters over the whole CTA (thread order)
-__device__ __forceinline__ U4 block_exclusive_scan4(U4 x, U4* warp_tot /* smem[32] */) {
+// exclusive prefix sum of one counter over the whole CTA (thread order); `total` gets the block sum
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* warp_tot /* smem[32] */, uint32_t* total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    U4 inc = x;
+    uint32_t inc = x;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc.v[c], o);
-            if (lane >= o) inc.v[c] += t;
-        }
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
     }
     if (lane == 31) warp_tot[warp] = inc;
     __syncthreads();
-    if (warp == 0) {
-        U4 t = warp_tot[lane];
-        U4 ti = t;
+    uint32_t w = warp_tot[lane];  // every warp scans the 32 warp totals itself: no second barrier
+    uint32_t wi = w;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint32_t u = __shfl_up_sync(0xffffffffu, ti.v[c], o);
-                if (lane >= o) ti.v[c] += u;
-            }
-        }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) ti.v[c] -= t.v[c];
-        warp_tot[lane] = ti;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+        if (lane >= o) wi += t;
     }
-    __syncthreads();
-    U4 base = warp_tot[warp];
-    U4 out;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) out.v[c] = base.v[c] + inc.v[c] - x.v[c];
+    const uint32_t base = __shfl_sync(0xffffffffu, wi - w, warp);
+    if (total) *total = __shfl_sync(0xffffffffu, wi, 31);
     __syncthreads();  // warp_tot may be reused by the caller
-    return out;
+    return base + inc - x;
+}
+
+struct SelShared {
+    uint32_t hist[4][SPLITQ_MAX_LADDER][256];   // [pass][rung][digit]; pass 0 uses rung slot 0 for all rungs
+    uint32_t tcnt[4][256];                      // top-rho: key counts per digit, per pass
+    unsigned long long tmass[4][256];           // top-rho: fixed-point mass per digit, per pass
+    uint32_t prefix[SPLITQ_MAX_LADDER], rem[SPLITQ_MAX_LADDER];
+    uint32_t warp_tot[32];
+    uint32_t t_prefix, t_nhi, t_done, t_keep;
+    unsigned long long t_mhi;
+};
+
+// one warp: find the digit of `hist` (256 bins, ascending) that holds rank `rem`; returns through lane-uniform refs
+__device__ __forceinline__ void scan_bins_ascending(const uint32_t* hist, uint32_t rem, int lane, uint32_t& digit,
+                                                    uint32_t& rem_out) {
+    uint32_t loc[8], sum = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        loc[q] = hist[lane * 8 + q];
+        sum += loc[q];
+    }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    uint32_t before = inc - sum;
+    const bool mine = before <= rem && rem < inc;
+    uint32_t d = 0, r = 0;
+    if (mine) {
+        int q = 0;
+        while (before + loc[q] <= rem) before += loc[q++];
+        d = (uint32_t)(lane * 8 + q);
+        r = rem - before;
+    }
+    const uint32_t who = __ballot_sync(0xffffffffu, mine);
+    const int src = who ? __ffs(who) - 1 : 0;
+    digit = __shfl_sync(0xffffffffu, d, src);
+    rem_out = __shfl_sync(0xffffffffu, r, src);
 }
 
 template <int ITEMS>
 __global__ void __launch_bounds__(kSelThreads)
-select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, uint8_t* __restrict__ bits_out,
-                   uint32_t* __restrict__ row_off_out) {
-    __shared__ uint32_t hist[SPLITQ_MAX_LADDER][256];
-    __shared__ uint32_t s_prefix[SPLITQ_MAX_LADDER];
-    __shared__ uint32_t s_rem[SPLITQ_MAX_LADDER];
-    __shared__ U4 warp_tot[32];
-
+select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWindow pw, uint8_t* __restrict__ bits_out,
+                   uint32_t* __restrict__ row_off_out, int* __restrict__ k_out) {
+    __shared__ SelShared sh;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t wbase = (size_t)blockIdx.x * S;
     imp += wbase;
 
     uint32_t key[ITEMS];
+    if (ITEMS % 4 == 0 && (S & 3) == 0 && (reinterpret_cast<uintptr_t>(imp) & 15u) == 0) {
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-        const int idx = tid * ITEMS + i;
-        key[i] = idx < S ? order_key(imp[idx]) : 0xffffffffu;
+        for (int i = 0; i < ITEMS; i += 4) {
+            const int idx = tid * ITEMS + i;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (idx < S) v = __ldg(reinterpret_cast<const float4*>(imp + idx));
+            key[i + 0] = idx + 0 < S ? order_key(v.x) : 0xffffffffu;
+            key[i + 1] = idx + 1 < S ? order_key(v.y) : 0xffffffffu;
+            key[i + 2] = idx + 2 < S ? order_key(v.z) : 0xffffffffu;
+            key[i + 3] = idx + 3 < S ? order_key(v.w) : 0xffffffffu;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const int idx = tid * ITEMS + i;
+            key[i] = idx < S ? order_key(__ldg(imp + idx)) : 0xffffffffu;
+        }
     }
+    {   // clear every histogram once
+        uint32_t* z = &sh.hist[0][0][0];
+        constexpr int nz = (int)((sizeof(sh.hist) + sizeof(sh.tcnt) + sizeof(sh.tmass)) / 4);
+        static_assert(offsetof(SelShared, tcnt) == sizeof(sh.hist) && offsetof(SelShared, tmass) == sizeof(sh.hist) + sizeof(sh.tcnt),
+                      "histograms must be contiguous");
+        for (int i = tid; i < nz; i += kSelThreads) z[i] = 0u;
+        if (tid == 0) { sh.t_prefix = 0u; sh.t_nhi = 0u; sh.t_done = 0u; sh.t_keep = 0u; sh.t_mhi = 0ull; }
+    }
+    __syncthreads();
+
+    int thresh[SPLITQ_MAX_LADDER];
+#pragma unroll
+    for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) thresh[c] = c < lad.n ? lad.thresh[c] : 0;
+    if (pw.mode == 1) thresh[0] = pw.k[blockIdx.x];
+
+    // ---- top-rho: how many of the most important tokens reach the mass threshold T -----------------
+    if (pw.mode == 2) {
+        const unsigned long long T = pw.mass[blockIdx.x];
+        for (int pass = 0; pass < 4; ++pass) {
+            const int shift = 24 - 8 * pass;
+            const uint32_t himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+            const uint32_t pre = sh.t_prefix;
+            if (!sh.t_done) {
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i) {
+                    if (tid * ITEMS + i < S && (key[i] & himask) == pre) {
+                        const uint32_t digit = (key[i] >> shift) & 255u;
+                        atomicAdd(&sh.tcnt[pass][digit], 1u);
+                        const unsigned long long m = mass_of(key_value(key[i]));
+                        if (m) atomicAdd(&sh.tmass[pass][digit], m);
+                    }
+                }
+            }
+            __syncthreads();
+            if (warp == 0 && !sh.t_done) {
+                // descending order: lane l owns bins 255-8l .. 248-8l
+                uint32_t cl[8], csum = 0;
+                unsigned long long ml[8], msum = 0;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int bin = 255 - (lane * 8 + q);
+                    cl[q] = sh.tcnt[pass][bin];
+                    ml[q] = sh.tmass[pass][bin];
+                    csum += cl[q];
+                    msum += ml[q];
+                }
+                uint32_t cinc = csum;
+                unsigned long long minc = msum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t ct = __shfl_up_sync(0xffffffffu, cinc, o);
+                    const unsigned long long mt = __shfl_up_sync(0xffffffffu, minc, o);
+                    if (lane >= o) { cinc += ct; minc += mt; }
+                }
+                const unsigned long long mhi = sh.t_mhi;
+                unsigned long long mbefore = mhi + (minc - msum);
+                uint32_t cbefore = cinc - csum;
+                const bool mine = mbefore < T && T <= mhi + minc;   // the running mass reaches T inside my bins
+                const uint32_t who = __ballot_sync(0xffffffffu, mine);
+                if (who == 0u) {
+                    if (lane == 0) {  // T == 0: nothing is kept; otherwise the whole distribution is lighter than T
+                        sh.t_keep = T == 0ull ? 0u : (uint32_t)S;
+                        sh.t_done = 1u;
+                    }
+                } else if (mine) {
+                    int q = 0;
+                    while (mbefore + ml[q] < T) { mbefore += ml[q]; cbefore += cl[q]; ++q; }
+                    const uint32_t digit = (uint32_t)(255 - (lane * 8 + q));
+                    sh.t_prefix = pre | (digit << shift);
+                    sh.t_mhi = mbefore;
+                    sh.t_nhi += cbefore;
+                    if (pass == 3) {  // cl[q] keys equal to the pivot, each of mass w > 0 (their bin moved the sum)
+                        const unsigned long long w = ml[q] / cl[q];
+                        const unsigned long long need = (T - mbefore + w - 1ull) / w;
+                        sh.t_keep = sh.t_nhi + (uint32_t)(need < cl[q] ? need : cl[q]);
+                        sh.t_done = 1u;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        thresh[0] = S - (int)sh.t_keep;
+    }
+    if (k_out && tid == 0) k_out[blockIdx.x] = thresh[0];
     if (tid < SPLITQ_MAX_LADDER) {
-        s_prefix[tid] = 0u;
-        s_rem[tid] = (tid < lad.n && lad.thresh[tid] > 0) ? (uint32_t)(lad.thresh[tid] - 1) : 0u;
+        sh.prefix[tid] = 0u;
+        sh.rem[tid] = thresh[tid] > 0 ? (uint32_t)(thresh[tid] - 1) : 0u;
     }
 
     // ---- 4 passes of 8-bit MSB radix select, all rungs at once --------------------------------
-    for (int pass = 0; pass < 4; ++pass) {
-        const int shift = 24 - 8 * pass;
-        const uint32_t himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-        for (int i = tid; i < SPLITQ_MAX_LADDER * 256; i += kSelThreads) (&hist[0][0])[i] = 0u;
-        __syncthreads();
+    // pass 0: no rung has a prefix yet -> one histogram for all, one warp-aggregated atomic per key
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) {
-            const uint32_t digit = (key[i] >> shift) & 255u;
-            for (int c = 0; c < lad.n; ++c) {
-                const bool in = (key[i] & himask) == s_prefix[c];
-                // warp-aggregated shared atomics: scores cluster in a few exponent buckets
+    for (int i = 0; i < ITEMS; ++i) {
+        const uint32_t digit = key[i] >> 24;
+        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        if (lane == (__ffs(peers) - 1)) atomicAdd(&sh.hist[0][0][digit], __popc(peers));
+    }
+    __syncthreads();
+    if (warp < lad.n) {
+        uint32_t digit, rem;
+        scan_bins_ascending(sh.hist[0][0], sh.rem[warp], lane, digit, rem);
+        if (lane == 0) { sh.prefix[warp] = digit << 24; sh.rem[warp] = rem; }
+    }
+    __syncthreads();
+    for (int pass = 1; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        const uint32_t himask = 0xffffffffu << (shift + 8);
+        for (int c = 0; c < lad.n; ++c) {
+            const uint32_t pre = sh.prefix[c];
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) {
+                const bool in = (key[i] & himask) == pre;
+                if (!__any_sync(0xffffffffu, in)) continue;
+                const uint32_t digit = (key[i] >> shift) & 255u;
                 const uint32_t peers = __match_any_sync(0xffffffffu, in ? digit : 0xffffffffu);
-                if (in && lane == (__ffs(peers) - 1)) atomicAdd(&hist[c][digit], __popc(peers));
+                if (in && lane == (__ffs(peers) - 1)) atomicAdd(&sh.hist[pass][c][digit], __popc(peers));
             }
         }
         __syncthreads();
         if (warp < lad.n) {
-            const int c = warp;
-            uint32_t loc[8], sum = 0;
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                loc[q] = hist[c][lane * 8 + q];
-                sum += loc[q];
-            }
-            uint32_t inc = sum;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += t;
-            }
-            const uint32_t rem = s_rem[c];
-            uint32_t before = inc - sum;
-            const bool mine = before <= rem && rem < inc;
-            __syncwarp();
-            if (mine) {
-                int q = 0;
-                while (before + loc[q] <= rem) before += loc[q++];
-                s_prefix[c] |= (uint32_t)(lane * 8 + q) << shift;
-                s_rem[c] = rem - before;
-            }
+            uint32_t digit, rem;
+            scan_bins_ascending(sh.hist[pass][warp], sh.rem[warp], lane, digit, rem);
+            if (lane == 0) { sh.prefix[warp] |= digit << shift; sh.rem[warp] = rem; }
         }
         __syncthreads();
     }
 
-    // ---- ties: equal-to-pivot elements are taken in index order ---------------------------------
-    uint32_t pivot[SPLITQ_MAX_LADDER], need[SPLITQ_MAX_LADDER];
+    // ---- ties: equal-to-pivot keys are taken in index order.  The last histogram knows how many keys
+    // equal each pivot; if all of them are wanted there is nothing to break.
+    uint32_t pivot[SPLITQ_MAX_LADDER], need[SPLITQ_MAX_LADDER], eq_base[SPLITQ_MAX_LADDER];
+    bool ties = false;
 #pragma unroll
     for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) {
-        pivot[c] = s_prefix[c];
-        need[c] = (c < lad.n && lad.thresh[c] > 0) ? s_rem[c] + 1u : 0u;
+        pivot[c] = sh.prefix[c];
+        need[c] = (c < lad.n && thresh[c] > 0) ? sh.rem[c] + 1u : 0u;
+        eq_base[c] = 0u;
+        if (need[c] > 0u && sh.hist[3][c][pivot[c] & 255u] != need[c]) ties = true;
     }
-    U4 cnt = {{0u, 0u, 0u, 0u}};
+    if (ties) {  // block-uniform
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
+        for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) {
+            uint32_t cnt = 0;
 #pragma unroll
-        for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) cnt.v[c] += (key[i] == pivot[c]) ? 1u : 0u;
-    U4 eq_base = block_exclusive_scan4(cnt, warp_tot);
+            for (int i = 0; i < ITEMS; ++i) cnt += (key[i] == pivot[c]) ? 1u : 0u;
+            eq_base[c] = block_exclusive_scan(cnt, sh.warp_tot, nullptr);
+        }
+    }
 
     uint8_t cls[ITEMS];
-    U4 mine = {{0u, 0u, 0u, 0u}};  // v[3] = row bytes / 16 of this thread's tokens
+    uint32_t mine = 0;  // row bytes / 16 of this thread's tokens
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         int k = lad.n;
@@ -161,16 +308,15 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, uint8_t* __
         for (int c = SPLITQ_MAX_LADDER - 1; c >= 0; --c) {
             if (c < lad.n) {
                 const bool eq = key[i] == pivot[c];
-                const bool sel = need[c] > 0u && (key[i] < pivot[c] || (eq && eq_base.v[c] < need[c]));
-                if (eq) eq_base.v[c]++;
+                const bool sel = need[c] > 0u && (key[i] < pivot[c] || (eq && eq_base[c] < need[c]));
+                if (eq) eq_base[c]++;
                 if (sel) k = c;
             }
         }
         cls[i] = (uint8_t)k;
-        if (tid * ITEMS + i < S) mine.v[3] += lad.rb16[k];
+        if (tid * ITEMS + i < S) mine += lad.rb16[k];
     }
-    U4 off = block_exclusive_scan4(mine, warp_tot);
-    uint32_t o16 = off.v[3];
+    uint32_t o16 = block_exclusive_scan(mine, sh.warp_tot, nullptr);
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         const int idx = tid * ITEMS + i;
@@ -187,6 +333,39 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, uint8_t* __
 
 using namespace splitq;
 
+static int launch_select(const float* imp, int nwin, int S, const Ladder& lad, const PerWindow& pw, uint8_t* bits_out,
+                         uint32_t* row_off_out, int* k_out, cudaStream_t st) {
+#define SPLITQ_SEL(ITEMS) \
+    select_bits_kernel<ITEMS><<<nwin, kSelThreads, 0, st>>>(imp, S, lad, pw, bits_out, row_off_out, k_out)
+    if (S <= 1 * kSelThreads) SPLITQ_SEL(1);
+    else if (S <= 2 * kSelThreads) SPLITQ_SEL(2);
+    else if (S <= 4 * kSelThreads) SPLITQ_SEL(4);
+    else if (S <= 8 * kSelThreads) SPLITQ_SEL(8);
+    else if (S <= 16 * kSelThreads) SPLITQ_SEL(16);
+    else SPLITQ_SEL(32);
+#undef SPLITQ_SEL
+    SPLITQ_LAUNCH_CHECK("select_bits_kernel");
+    return SPLITQ_OK;
+}
+
+static void fill_ladder(Ladder& lad, int D, const int* k, const int* bits, int n) {
+    lad.n = n;
+    int cum = 0;
+    for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) {
+        if (c < n) {
+            cum += k[c];
+            lad.thresh[c] = cum;
+            lad.bits[c] = bits[c];
+            lad.rb16[c] = row_bytes(D, bits[c]) / 16u;
+        } else {
+            lad.thresh[c] = 0;
+            lad.bits[c] = SPLITQ_BITS_RAW;
+            lad.rb16[c] = 0;
+        }
+    }
+    lad.rb16[n] = row_bytes(D, SPLITQ_BITS_RAW) / 16u;
+}
+
 extern "C" int splitq_select_bits(const float* imp, int B, int S, int D, const int* ladder_k_host,
                                   const int* ladder_bits_host, int n_ladder, uint8_t* bits_out,
                                   uint32_t* row_off_out, splitq_stream_t stream) {
@@ -197,31 +376,50 @@ extern "C" int splitq_select_bits(const float* imp, int B, int S, int D, const i
     if (int rc = validate_ladder(S, ladder_k_host, ladder_bits_host, n_ladder)) return rc;
     if (int rc = check_arch()) return rc;
     Ladder lad;
-    lad.n = n_ladder;
-    int cum = 0;
-    for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) {
-        if (c < n_ladder) {
-            cum += ladder_k_host[c];
-            lad.thresh[c] = cum;
-            lad.bits[c] = ladder_bits_host[c];
-            lad.rb16[c] = row_bytes(D, ladder_bits_host[c]) / 16u;
-        } else {
-            lad.thresh[c] = 0;
-            lad.bits[c] = SPLITQ_BITS_RAW;
-            lad.rb16[c] = 0;
+    fill_ladder(lad, D, ladder_k_host, ladder_bits_host, n_ladder);
+    PerWindow pw;
+    pw.mode = 0;
+    return launch_select(imp, B, S, lad, pw, bits_out, row_off_out, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int splitq_select_bits_per_window(const float* imp, int B, int S, int D, int bits, const int* k_host,
+                                             const double* mass_threshold_host, uint8_t* bits_out,
+                                             uint32_t* row_off_out, int* k_out, splitq_stream_t stream) {
+    SPLITQ_REQUIRE(imp && bits_out && row_off_out, SPLITQ_ERR_ARG, "select_bits_per_window: NULL buffer");
+    SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0, SPLITQ_ERR_ARG, "select_bits_per_window: bad shape B=%d S=%d D=%d", B, S, D);
+    SPLITQ_REQUIRE(S <= SPLITQ_MAX_SELECT_S, SPLITQ_ERR_ARG, "select_bits_per_window: S=%d > %d", S, SPLITQ_MAX_SELECT_S);
+    SPLITQ_REQUIRE((k_host != nullptr) != (mass_threshold_host != nullptr), SPLITQ_ERR_ARG,
+                   "select_bits_per_window: give either per-window counts or per-window mass thresholds");
+    SPLITQ_REQUIRE(bits == 2 || bits == 4 || bits == 8, SPLITQ_ERR_ARG, "select_bits_per_window: width %d not in {2,4,8}", bits);
+    if (int rc = check_arch()) return rc;
+    const int one_k = 0;
+    Ladder lad;
+    fill_ladder(lad, D, &one_k, &bits, 1);
+    for (int w0 = 0; w0 < B; w0 += kSelMaxWindows) {
+        const int n = B - w0 < kSelMaxWindows ? B - w0 : kSelMaxWindows;
+        PerWindow pw;
+        pw.mode = k_host ? 1 : 2;
+        for (int i = 0; i < n; ++i) {
+            pw.k[i] = 0;
+            pw.mass[i] = 0ull;
+            if (k_host) {
+                SPLITQ_REQUIRE(k_host[w0 + i] >= 0 && k_host[w0 + i] <= S, SPLITQ_ERR_ARG,
+                               "select_bits_per_window: count %d of window %d not in [0,%d]", k_host[w0 + i], w0 + i, S);
+                pw.k[i] = k_host[w0 + i];
+            } else {
+                const double t = mass_threshold_host[w0 + i];
+                SPLITQ_REQUIRE(t == t && t <= 32768.0, SPLITQ_ERR_ARG,
+                               "select_bits_per_window: mass threshold of window %d is not a number <= 32768", w0 + i);
+                // ceil(t * 2^47) in exact integer arithmetic on the double's value
+                const double scaled = t <= 0.0 ? 0.0 : t * 140737488355328.0;
+                unsigned long long q = (unsigned long long)scaled;
+                if ((double)q < scaled) ++q;
+                pw.mass[i] = q;
+            }
         }
+        if (int rc = launch_select(imp + (size_t)w0 * S, n, S, lad, pw, bits_out + (size_t)w0 * S,
+                                   row_off_out + (size_t)w0 * S, k_out ? k_out + w0 : nullptr, (cudaStream_t)stream))
+            return rc;
     }
-    lad.rb16[n_ladder] = row_bytes(D, SPLITQ_BITS_RAW) / 16u;
-    cudaStream_t st = (cudaStream_t)stream;
-#define SPLITQ_SEL(ITEMS) \
-    select_bits_kernel<ITEMS><<<B, kSelThreads, 0, st>>>(imp, S, lad, bits_out, row_off_out)
-    if (S <= 1 * kSelThreads) SPLITQ_SEL(1);
-    else if (S <= 2 * kSelThreads) SPLITQ_SEL(2);
-    else if (S <= 4 * kSelThreads) SPLITQ_SEL(4);
-    else if (S <= 8 * kSelThreads) SPLITQ_SEL(8);
-    else if (S <= 16 * kSelThreads) SPLITQ_SEL(16);
-    else SPLITQ_SEL(32);
-#undef SPLITQ_SEL
-    SPLITQ_LAUNCH_CHECK("select_bits_kernel");
     return SPLITQ_OK;
 }

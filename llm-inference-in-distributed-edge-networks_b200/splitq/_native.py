@@ -38,6 +38,7 @@ SIGNATURES = {
     "splitq_importance_fused": (_i, [_vp, _llp, _vp, _llp, _i, _i, _i, _i, _i, C.c_float, _i, _i, _fp, _vp, _vp, _vp,
                                      _sz, _vp]),
     "splitq_select_bits": (_i, [_vp, _i, _i, _i, _ip, _ip, _i, _vp, _vp, _vp]),
+    "splitq_select_bits_per_window": (_i, [_vp, _i, _i, _i, _i, _ip, C.POINTER(C.c_double), _vp, _vp, _vp, _vp]),
     "splitq_payload_bytes": (_sz, [_i, _i, _ip, _ip, _i, _i]),
     "splitq_quant_pack_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "splitq_quant_pack": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _sz, _vp, _sz, _vp]),
@@ -46,6 +47,7 @@ SIGNATURES = {
     "splitq_dequant_norm": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, C.c_float, _vp, _vp, _vp, _vp, _vp, _vp]),
     "splitq_channel_workspace_bytes": (_sz, [_i, _i, _i]),
     "splitq_channel_fake_quant": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "splitq_layer_js": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "splitq_transfer_peer": (_i, [_vp, _i, _vp, _i, _sz, _vp]),
     "splitq_ipc_export": (_i, [_vp, _vp, C.POINTER(C.c_size_t)]),
     "splitq_ipc_open": (_i, [_vp, _sz, C.POINTER(C.c_void_p)]),

@@ -26,8 +26,21 @@ def jensen_shannon(p: torch.Tensor, q: torch.Tensor) -> torch.Tensor:
 
 def layer_distance_matrix(dist: torch.Tensor) -> torch.Tensor:
     """dist: (L, N, S) importance distributions of L layers over N samples -> (L, L) matrix whose
-    upper triangle holds the sample-averaged JS divergence and the rest NaN (notebook cell 16)."""
+    upper triangle holds the sample-averaged JS divergence and the rest NaN (notebook cell 16).
+    fp32 CUDA input (what the scoring kernels produce) goes through one kernel launch
+    (splitq_layer_js); anything else through the torch formulas below."""
     L = dist.shape[0]
+    if dist.is_cuda and dist.dtype == torch.float32 and dist.dim() == 3:
+        import ctypes as C
+
+        from . import _native as N_
+        d = dist.contiguous()
+        _, Ns, S = d.shape
+        js = torch.full((L, L, Ns), float("nan"), dtype=torch.float64, device=d.device)
+        with torch.cuda.device(d.device):
+            N_.check(N_.load().splitq_layer_js(C.c_void_p(d.data_ptr()), L, Ns, S, C.c_void_p(js.data_ptr()),
+                                               C.c_void_p(torch.cuda.current_stream(d.device).cuda_stream)))
+        return js.mean(dim=-1)
     out = torch.full((L, L), float("nan"), dtype=torch.float64, device=dist.device)
     d = dist.double()
     for i in range(L):

@@ -169,6 +169,33 @@ def select_bits(imp: torch.Tensor, ladder: Ladder, D: int, bits_out: Optional[to
     return bits_out, row_off_out
 
 
+def select_bits_per_window(imp: torch.Tensor, bits: int, D: int, counts: Optional[Sequence[int]] = None,
+                           mass_thresholds: Optional[Sequence[float]] = None, want_counts: bool = False):
+    """One rung of `bits` bits whose size differs per window of imp (B,S): either `counts[b]` least
+    important tokens (batched_quantization_helper's rule), or "top-rho": everything outside the
+    fewest most-important tokens whose importance mass reaches mass_thresholds[b]
+    (batched_top_rho_quantization, pythia_model.py:93-109).  -> (bits u8 (B,S), row_off (B,S)
+    [, quantised-token counts int32 (B,) on the device])."""
+    imp = _need_cuda_f32(imp, "importance")
+    if imp.dim() == 1:
+        imp = imp.unsqueeze(0)
+    B, S = imp.shape
+    if (counts is None) == (mass_thresholds is None):
+        raise N.SplitqError("select_bits_per_window: give either counts or mass_thresholds")
+    n = len(counts if counts is not None else mass_thresholds)
+    if n != B:
+        raise N.SplitqError(f"select_bits_per_window: {n} per-window values for {B} windows")
+    bits_out = torch.empty(B, S, dtype=torch.uint8, device=imp.device)
+    row_off_out = torch.empty(B, S, dtype=torch.int32, device=imp.device)
+    k_out = torch.empty(B, dtype=torch.int32, device=imp.device) if want_counts else None
+    ks = N.int_array([int(c) for c in counts]) if counts is not None else None
+    ms = (C.c_double * B)(*[float(t) for t in mass_thresholds]) if mass_thresholds is not None else None
+    with torch.cuda.device(imp.device):
+        N.check(N.load().splitq_select_bits_per_window(_ptr(imp), B, S, D, int(bits), ks, ms, _ptr(bits_out),
+                                                       _ptr(row_off_out), _ptr(k_out), _stream(imp)))
+    return (bits_out, row_off_out, k_out) if want_counts else (bits_out, row_off_out)
+
+
 def _check_pack_args(who: str, h: torch.Tensor, bits: torch.Tensor, row_off: torch.Tensor, payload: torch.Tensor,
                      nbytes: Optional[int]) -> None:
     """The C side trusts these pointers: a wrong dtype, device, layout or size is an out-of-bounds

@@ -290,6 +290,67 @@ class Pythia70Model(_LayerWiseModel):
         mlp_out = layer.post_mlp_dropout(layer.mlp(layer.post_attention_layernorm(attn_out)))
         return mlp_out + attn_out
 
+    # ---- the first experiment's batched entry points (initial_exp.py:112-131) --------------------
+    # The batch holds one copy of the window per entry of self.ratios and the RATIO VALUE is the batch
+    # row it acts on (pythia_model.py:59, `hidden_states[ratio, token, :]`), so the ratios are the
+    # integers 0 .. B-1.  In the reference both methods die in `simulate_quantization` (a @staticmethod
+    # declared with `self`, pythia_model.py:57 vs :112,:143), whose per-token affine qint8 would leave
+    # two levels per token; the token-set rules are rebuilt here as intended, over this library's
+    # quantiser (self.bits, self.scale_mode) and the real boundary (pack -> hop -> dequantise).
+    def _batched_boundary(self, batched_input_tokens, target, quant_layer, select):
+        with torch.no_grad():
+            hidden = self.upstream(batched_input_tokens, quant_layer)
+            B, S, D = hidden.shape
+            target = target.to(hidden.device)
+            if target.size(0) != B:
+                target = target.expand(B, -1)
+            shape = (B, S)
+            if select is None:
+                nll = self.downstream(shape, target, quant_layer, hidden=hidden, per_sequence=True)
+            else:
+                bits, row_off = select(B, S, D)
+                nbytes = boundary.payload_bytes(S, D, [], self.scale_mode)  # rows differ per window: size for all-raw
+                payload = boundary.quant_pack(hidden, bits, row_off, self.scale_mode, nbytes)
+                self.last_payload_bytes = B * nbytes
+                nll = self.downstream(shape, target, quant_layer, payload=self.boundary_hop(payload), per_sequence=True)
+            return [nll[int(r)] for r in self.ratios]
+
+    def batched_quantization_helper(self, batched_input_tokens, ordering, target, quant_layer=2, do_quant=True):
+        """pythia_model.py:116-145: batch row `ratio` has the first int(0.1 * ratio * len(ordering)) tokens
+        of `ordering` (ascending importance, from extract_attentions) quantised after layer
+        `quant_layer`; returns one NLL per entry of self.ratios."""
+        if not do_quant:
+            return self._batched_boundary(batched_input_tokens, target, quant_layer, None)
+        order = torch.as_tensor(ordering, dtype=torch.long)
+        n = order.numel()
+
+        def select(B, S, D):
+            rank = torch.empty(S, dtype=torch.float32)
+            rank[order] = torch.arange(n, dtype=torch.float32)  # rank as importance: the k lowest ranks = ordering[:k]
+            counts = [0] * B
+            for r in self.ratios:
+                counts[int(r)] = int(0.1 * r * n)
+            imp = rank.to(self.device).unsqueeze(0).expand(B, S).contiguous()
+            return boundary.select_bits_per_window(imp, self.bits, D, counts=counts)
+        return self._batched_boundary(batched_input_tokens, target, quant_layer, select)
+
+    def batched_top_rho_quantization(self, batched_input_tokens, distribution, target, quant_layer=2, do_quant=True):
+        """pythia_model.py:71-114 ("upto ratio"): batch row `ratio` keeps the fewest most-important tokens
+        whose importance (`distribution`, the layer's column-mean scores) sums to >= 1 - 0.1 * ratio and
+        has all the others quantised after layer `quant_layer`; returns one NLL per entry of self.ratios.
+        The threshold search runs inside the selection kernel (no host sort, no sync)."""
+        if not do_quant:
+            return self._batched_boundary(batched_input_tokens, target, quant_layer, None)
+        dist = torch.as_tensor(distribution, dtype=torch.float32).to(self.device).reshape(-1)
+
+        def select(B, S, D):
+            thresholds = [float(S + 1)] * B  # rows no ratio points at keep every token
+            for r in self.ratios:
+                thresholds[int(r)] = 1 - 0.1 * r
+            return boundary.select_bits_per_window(dist.unsqueeze(0).expand(B, S).contiguous(), self.bits, D,
+                                                   mass_thresholds=thresholds)
+        return self._batched_boundary(batched_input_tokens, target, quant_layer, select)
+
     def calculate_batched_nll(self, hidden_states, target):
         """pythia_model.py:36-54: one NLL per entry of self.ratios, ratio used as batch index."""
         with torch.no_grad():

@@ -5,7 +5,8 @@ orderings from the column-mean importance of a layer, of layers 0-2 averaged ("a
 of their element-wise maximum ("maximum aggregation"), or returns the raw layer-2 distribution
 ("upto ratio"); `batched_top_rho_quantization` (pythia_model.py:93-109) keeps the fewest tokens
 whose importance mass reaches 1 - 0.1*ratio and quantises the rest.  The importance vectors come
-from K1 (or K2); the bookkeeping on (S,) vectors below is plain torch on the GPU.
+from K1 (or K2); the top-rho threshold is a mode of the selection kernel
+(splitq_select_bits_per_window), the orderings are torch argsorts of the kernel's scores.
 """
 from __future__ import annotations
 
@@ -42,18 +43,33 @@ def extract_attentions(attention_weights, interesting_layers) -> Dict[object, np
     return out
 
 
+def top_rho_thresholds(ratios: Sequence[float]) -> List[float]:
+    """pythia_model.py:95: the mass the kept (unquantised) tokens must reach for each ratio."""
+    return [1 - 0.1 * float(r) for r in ratios]
+
+
+def top_rho_select(distribution: torch.Tensor, ratios: Sequence[float], D: int, bits: int = 4, want_counts: bool = False):
+    """K3a's cumulative-mass mode for a batch: row b of `distribution` (B,S) -- or the one (S,)
+    distribution shared by all rows -- keeps the fewest most-important tokens whose importance sums to
+    >= 1 - 0.1*ratios[b] and quantises the rest to `bits` bits (the intended semantics of
+    batched_top_rho_quantization, pythia_model.py:93-109; its own slice mixes token ids and ranks,
+    SURVEY 8f-2).  Everything stays on the device: -> (bits, row_off[, quantised counts])."""
+    from .boundary import select_bits_per_window
+    if distribution.dim() == 1:
+        distribution = distribution.unsqueeze(0).expand(len(ratios), -1)
+    return select_bits_per_window(distribution.contiguous(), bits, D, mass_thresholds=top_rho_thresholds(ratios),
+                                  want_counts=want_counts)
+
+
 def top_rho_keep_count(distribution: torch.Tensor, ratio: float) -> int:
-    """Fewest most-important tokens whose importance sums to >= 1 - 0.1*ratio
-    (pythia_model.py:93-106: sort descending, accumulate until the threshold is met)."""
-    threshold = 1 - 0.1 * ratio
-    vals = torch.sort(distribution.double(), descending=True).values
-    before = torch.cumsum(vals, dim=0) - vals  # running total before each token is taken
-    return int((before < threshold).sum().item())  # the loop takes a token while total < threshold
+    """Fewest most-important tokens whose importance sums to >= 1 - 0.1*ratio (pythia_model.py:93-106),
+    computed by the selection kernel; reads one integer back from the device."""
+    _, _, k = top_rho_select(distribution.reshape(1, -1), [ratio], D=4, want_counts=True)
+    return distribution.numel() - int(k.item())
 
 
 def top_rho_ladder(distribution: torch.Tensor, ratio: float, bits: int = 4) -> List[Tuple[int, int]]:
-    """Ladder for select_bits: everything outside the kept top-rho set is quantised (the intended
-    semantics of batched_top_rho_quantization; its own slice mixes token ids and ranks)."""
+    """Ladder for select_bits: everything outside the kept top-rho set is quantised."""
     S = distribution.numel()
     k = S - top_rho_keep_count(distribution, ratio)
     return [(k, bits)] if k > 0 else []

@@ -411,6 +411,36 @@ def layer_distance_matrix_np(dist: np.ndarray) -> np.ndarray:
     return out
 
 
+MASS_ONE = 1 << 47  # fixed-point unit of the top-rho mass sums
+
+
+def mass_threshold_fixed(threshold: float) -> int:
+    """ceil(threshold * 2^47) as an integer (0 for thresholds <= 0)."""
+    if threshold <= 0:
+        return 0
+    scaled = float(threshold) * float(MASS_ONE)
+    q = int(scaled)
+    return q + 1 if q < scaled else q
+
+
+def top_rho_keep_count_fixed(distribution: np.ndarray, threshold: float) -> int:
+    """The intended rule of batched_top_rho_quantization (pythia_model.py:93-106) -- walk the tokens
+    from the most important down and take one while the mass taken so far is below the threshold
+    (the reference's threshold is 1 - 0.1*ratio) -- in the exact arithmetic the kernel uses: each
+    score, clamped to [0, 1], counts as the integer floor(score * 2^47), so the result does not
+    depend on the order of summation."""
+    v = np.asarray(distribution, dtype=np.float32)
+    mass = np.floor(np.clip(np.nan_to_num(v, nan=0.0), 0.0, 1.0).astype(np.float64) * float(MASS_ONE)).astype(np.uint64)
+    order = np.argsort(-v.astype(np.float64), kind="stable")
+    T, total, n = mass_threshold_fixed(threshold), 0, 0
+    for i in order:
+        if total >= T:
+            break
+        total += int(mass[i])
+        n += 1
+    return n
+
+
 def top_rho_keep_count(distribution: np.ndarray, ratio: float) -> int:
     """pythia_model.py:93-106: iterate the descending distribution until the running total reaches
     1 - 0.1*ratio; returns how many tokens were taken."""
