@@ -24,6 +24,8 @@
 // the top with a mass histogram beside the count histogram; masses are 2^-47 fixed-point
 // integers (values clamped to [0, 1]), so the sums -- and the count -- do not depend on the order of
 // the atomics and equal the oracle's integer arithmetic exactly.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace splitq {
@@ -84,10 +86,18 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* w
 }
 
 struct SelShared {
-    uint32_t hist[4][SPLITQ_MAX_LADDER][256];   // [pass][rung][digit]; pass 0 uses rung slot 0 for all rungs
+    // Two ways to count, each where it is cheap (cycle counts from a timing build, S = 4096):
+    //   pass 0 -- scores share a handful of exponents, so atomics would pile onto a few bins; a warp
+    //   finds its few distinct digits with match.any (cost grows with the number of distinct values:
+    //   ~2 k cycles here) and one leader lane per digit adds the count to the warp's OWN histogram with
+    //   a plain store; the 32 warp histograms are summed column-wise afterwards (counts fit 16 bits);
+    //   passes 1-3 -- the digits inside a pivot bin are spread over all 256 values, where match.any costs
+    //   ~300 cycles per call (13 k cycles for pass 1 alone) and plain shared atomics hardly collide.
+    uint16_t whist[32][256];                    // pass 0: [warp][digit]
+    uint32_t hist[4][SPLITQ_MAX_LADDER][256];   // [pass][rung][digit], cleared once; pass 0 uses rung slot 0 for all
     uint32_t tcnt[4][256];                      // top-rho: key counts per digit, per pass
     unsigned long long tmass[4][256];           // top-rho: fixed-point mass per digit, per pass
-    uint32_t prefix[SPLITQ_MAX_LADDER], rem[SPLITQ_MAX_LADDER];
+    uint32_t prefix[SPLITQ_MAX_LADDER], rem[SPLITQ_MAX_LADDER], eqcnt[SPLITQ_MAX_LADDER];
     uint32_t warp_tot[32];
     uint32_t t_prefix, t_nhi, t_done, t_keep;
     unsigned long long t_mhi;
@@ -127,7 +137,15 @@ template <int ITEMS>
 __global__ void __launch_bounds__(kSelThreads)
 select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWindow pw, uint8_t* __restrict__ bits_out,
                    uint32_t* __restrict__ row_off_out, int* __restrict__ k_out) {
-    __shared__ SelShared sh;
+#ifdef SPLITQ_SEL_TIMING
+    long long tk[12]; int nt = 0;
+#define SEL_TICK() do { __syncthreads(); tk[nt++] = clock64(); } while (0)
+#else
+#define SEL_TICK() do {} while (0)
+#endif
+    SEL_TICK();
+    extern __shared__ __align__(16) uint8_t sel_smem[];
+    SelShared& sh = *reinterpret_cast<SelShared*>(sel_smem);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t wbase = (size_t)blockIdx.x * S;
     imp += wbase;
@@ -151,16 +169,17 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
             key[i] = idx < S ? order_key(__ldg(imp + idx)) : 0xffffffffu;
         }
     }
-    {   // clear every histogram once
+    {   // clear the atomically filled histograms once (the top-rho ones only when they are used)
         uint32_t* z = &sh.hist[0][0][0];
-        constexpr int nz = (int)((sizeof(sh.hist) + sizeof(sh.tcnt) + sizeof(sh.tmass)) / 4);
-        static_assert(offsetof(SelShared, tcnt) == sizeof(sh.hist) && offsetof(SelShared, tmass) == sizeof(sh.hist) + sizeof(sh.tcnt),
-                      "histograms must be contiguous");
+        const int nz = (int)((sizeof(sh.hist) + (pw.mode == 2 ? sizeof(sh.tcnt) + sizeof(sh.tmass) : 0)) / 4);
+        static_assert(offsetof(SelShared, tcnt) == offsetof(SelShared, hist) + sizeof(sh.hist) &&
+                      offsetof(SelShared, tmass) == offsetof(SelShared, tcnt) + sizeof(sh.tcnt), "histograms must be contiguous");
         for (int i = tid; i < nz; i += kSelThreads) z[i] = 0u;
         if (tid == 0) { sh.t_prefix = 0u; sh.t_nhi = 0u; sh.t_done = 0u; sh.t_keep = 0u; sh.t_mhi = 0ull; }
+        if (pw.mode == 2) __syncthreads();
     }
-    __syncthreads();
 
+    SEL_TICK();  // keys loaded
     int thresh[SPLITQ_MAX_LADDER];
 #pragma unroll
     for (int c = 0; c < SPLITQ_MAX_LADDER; ++c) thresh[c] = c < lad.n ? lad.thresh[c] : 0;
@@ -241,43 +260,59 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
     }
 
     // ---- 4 passes of 8-bit MSB radix select, all rungs at once --------------------------------
-    // pass 0: no rung has a prefix yet -> one histogram for all, one warp-aggregated atomic per key
+    {   // pass 0: no rung has a prefix yet -> one histogram for all rungs, counted per warp
+        uint16_t* mine = sh.whist[warp];
+        uint32_t* z = reinterpret_cast<uint32_t*>(mine);
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-        const uint32_t digit = key[i] >> 24;
-        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
-        if (lane == (__ffs(peers) - 1)) atomicAdd(&sh.hist[0][0][digit], __popc(peers));
+        for (int i = 0; i < 4; ++i) z[lane + 32 * i] = 0u;
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const uint32_t digit = key[i] >> 24;
+            const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+            if (lane == (__ffs(peers) - 1)) mine[digit] = (uint16_t)(mine[digit] + __popc(peers));
+            __syncwarp();
+        }
+        __syncthreads();
+        SEL_TICK();
+        if (tid < 256) {
+            uint32_t sum = 0;
+#pragma unroll 8
+            for (int w = 0; w < 32; ++w) sum += sh.whist[w][tid];
+            sh.hist[0][0][tid] = sum;
+        }
+        __syncthreads();
+        if (warp < lad.n) {
+            uint32_t digit, rem;
+            scan_bins_ascending(sh.hist[0][0], sh.rem[warp], lane, digit, rem);
+            if (lane == 0) { sh.prefix[warp] = digit << 24; sh.rem[warp] = rem; }
+        }
+        __syncthreads();
     }
-    __syncthreads();
-    if (warp < lad.n) {
-        uint32_t digit, rem;
-        scan_bins_ascending(sh.hist[0][0], sh.rem[warp], lane, digit, rem);
-        if (lane == 0) { sh.prefix[warp] = digit << 24; sh.rem[warp] = rem; }
-    }
-    __syncthreads();
     for (int pass = 1; pass < 4; ++pass) {
         const int shift = 24 - 8 * pass;
         const uint32_t himask = 0xffffffffu << (shift + 8);
         for (int c = 0; c < lad.n; ++c) {
             const uint32_t pre = sh.prefix[c];
 #pragma unroll
-            for (int i = 0; i < ITEMS; ++i) {
-                const bool in = (key[i] & himask) == pre;
-                if (!__any_sync(0xffffffffu, in)) continue;
-                const uint32_t digit = (key[i] >> shift) & 255u;
-                const uint32_t peers = __match_any_sync(0xffffffffu, in ? digit : 0xffffffffu);
-                if (in && lane == (__ffs(peers) - 1)) atomicAdd(&sh.hist[pass][c][digit], __popc(peers));
-            }
+            for (int i = 0; i < ITEMS; ++i)
+                if ((key[i] & himask) == pre) atomicAdd(&sh.hist[pass][c][(key[i] >> shift) & 255u], 1u);
         }
         __syncthreads();
+        SEL_TICK();
         if (warp < lad.n) {
             uint32_t digit, rem;
             scan_bins_ascending(sh.hist[pass][warp], sh.rem[warp], lane, digit, rem);
-            if (lane == 0) { sh.prefix[warp] |= digit << shift; sh.rem[warp] = rem; }
+            if (lane == 0) {
+                sh.prefix[warp] |= digit << shift;
+                sh.rem[warp] = rem;
+                if (pass == 3) sh.eqcnt[warp] = sh.hist[3][warp][digit];  // keys equal to the pivot
+            }
         }
         __syncthreads();
     }
 
+    SEL_TICK();  // passes done
     // ---- ties: equal-to-pivot keys are taken in index order.  The last histogram knows how many keys
     // equal each pivot; if all of them are wanted there is nothing to break.
     uint32_t pivot[SPLITQ_MAX_LADDER], need[SPLITQ_MAX_LADDER], eq_base[SPLITQ_MAX_LADDER];
@@ -287,7 +322,7 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
         pivot[c] = sh.prefix[c];
         need[c] = (c < lad.n && thresh[c] > 0) ? sh.rem[c] + 1u : 0u;
         eq_base[c] = 0u;
-        if (need[c] > 0u && sh.hist[3][c][pivot[c] & 255u] != need[c]) ties = true;
+        if (need[c] > 0u && sh.eqcnt[c] != need[c]) ties = true;
     }
     if (ties) {  // block-uniform
 #pragma unroll
@@ -316,17 +351,49 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
         cls[i] = (uint8_t)k;
         if (tid * ITEMS + i < S) mine += lad.rb16[k];
     }
+    SEL_TICK();  // classified
     uint32_t o16 = block_exclusive_scan(mine, sh.warp_tot, nullptr);
+    SEL_TICK();  // offsets scanned
+    if (ITEMS % 4 == 0 && (S & 3) == 0 && ((wbase & 3) == 0) &&
+        ((reinterpret_cast<uintptr_t>(bits_out) & 3u) | (reinterpret_cast<uintptr_t>(row_off_out) & 15u)) == 0) {
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-        const int idx = tid * ITEMS + i;
-        if (idx < S) {
-            const int k = cls[i];
-            bits_out[wbase + idx] = (uint8_t)(k < lad.n ? lad.bits[k] : SPLITQ_BITS_RAW);
-            row_off_out[wbase + idx] = o16;
-            o16 += lad.rb16[k];
+        for (int i = 0; i < ITEMS; i += 4) {
+            const int idx = tid * ITEMS + i;
+            uint32_t b4 = 0;
+            uint4 o4;
+            uint32_t* o = &o4.x;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int k = cls[i + j];
+                b4 |= (uint32_t)(k < lad.n ? lad.bits[k] : SPLITQ_BITS_RAW) << (8 * j);
+                o[j] = o16;
+                o16 += lad.rb16[k];
+            }
+            if (idx < S) {
+                *reinterpret_cast<uint32_t*>(bits_out + wbase + idx) = b4;
+                *reinterpret_cast<uint4*>(row_off_out + wbase + idx) = o4;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const int idx = tid * ITEMS + i;
+            if (idx < S) {
+                const int k = cls[i];
+                bits_out[wbase + idx] = (uint8_t)(k < lad.n ? lad.bits[k] : SPLITQ_BITS_RAW);
+                row_off_out[wbase + idx] = o16;
+                o16 += lad.rb16[k];
+            }
         }
     }
+#ifdef SPLITQ_SEL_TIMING
+    SEL_TICK();
+    if (blockIdx.x == 0 && tid == 0) {
+        printf("select_bits timing (cycles since start):");
+        for (int i = 1; i < nt; ++i) printf(" %lld", tk[i] - tk[0]);
+        printf("\n");
+    }
+#endif
 }
 
 }  // namespace splitq
@@ -336,7 +403,18 @@ using namespace splitq;
 static int launch_select(const float* imp, int nwin, int S, const Ladder& lad, const PerWindow& pw, uint8_t* bits_out,
                          uint32_t* row_off_out, int* k_out, cudaStream_t st) {
 #define SPLITQ_SEL(ITEMS) \
-    select_bits_kernel<ITEMS><<<nwin, kSelThreads, 0, st>>>(imp, S, lad, pw, bits_out, row_off_out, k_out)
+    do {                                                                                                  \
+        static std::once_flag once[64];                                                                   \
+        int dev = 0;                                                                                      \
+        SPLITQ_CUDA(cudaGetDevice(&dev));                                                                 \
+        cudaError_t attr_err = cudaSuccess;                                                               \
+        std::call_once(once[dev & 63], [&] {                                                              \
+            attr_err = cudaFuncSetAttribute(select_bits_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                            (int)sizeof(SelShared));                                      \
+        });                                                                                               \
+        SPLITQ_CUDA(attr_err);                                                                            \
+        select_bits_kernel<ITEMS><<<nwin, kSelThreads, sizeof(SelShared), st>>>(imp, S, lad, pw, bits_out, row_off_out, k_out); \
+    } while (0)
     if (S <= 1 * kSelThreads) SPLITQ_SEL(1);
     else if (S <= 2 * kSelThreads) SPLITQ_SEL(2);
     else if (S <= 4 * kSelThreads) SPLITQ_SEL(4);
