@@ -271,12 +271,17 @@ def main() -> None:
                     help="payload hop between paired ranks in the device-resident loop: NCCL send/recv, or a "
                          "copy-engine pull over CUDA IPC ordered by stream memory operations (auto = ipc, "
                          "falling back to nccl if the mapping cannot be set up)")
-    ap.add_argument("--main-priority", type=int, default=-3,
-                    help="CUDA priority of the scoring stream (negative = above the side stream's default 0: the "
-                         "persistent scoring kernels then get SMs ahead of queued pack / dequantise CTAs)")
+    ap.add_argument("--main-priority", type=int, default=1,
+                    help="> 0 (default): score on the caller's stream.  <= 0: score on a separate stream of that CUDA "
+                         "priority (negative = above the side stream's 0); measured in round 2: the per-step join of "
+                         "that stream with the caller's costs 30 us of idle scoring stream per step on one GPU and "
+                         "100 us across GPUs, more than the priority gains (profiles/r2_d_stream_variants.txt)")
     ap.add_argument("--pack-on-main", action="store_true",
                     help="keep select + quantise/pack on the scoring stream (default: on the side stream with hop + dequantise)")
     ap.add_argument("--batch-windows", type=int, default=0, help="windows per step (0 = workload default)")
+    ap.add_argument("--depth", type=int, default=0,
+                    help="buffer sets of the software pipeline (0 = 2 on one GPU, 3 across GPUs: the third set lets the "
+                         "NVLink pull of step i run under the scoring of step i+1 instead of between two scorings)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -332,8 +337,9 @@ def main() -> None:
         return pl
 
     # software pipeline over steps: hop + dequantise of step i on a side stream under the scoring of i+1
-    ob = splitq.OverlappedBoundary(make_plan, depth=2, fused=fused, pack_on_side=not args.pack_on_main,
-                                   main_priority=args.main_priority)
+    depth = args.depth or (2 if world == 1 else 3)
+    ob = splitq.OverlappedBoundary(make_plan, depth=depth, fused=fused, pack_on_side=not args.pack_on_main,
+                                   main_priority=None if args.main_priority > 0 else args.main_priority)
     dev_inputs = (q, k, h) if fused else (A, h)
     ipc, transfer_name = None, "nccl pair exchange" if world > 1 else "device-to-device copy"
     if world > 1 and args.transfer in ("auto", "ipc"):
@@ -352,15 +358,21 @@ def main() -> None:
     def step(timed_events=None, side_event=None):
         ob.step(*dev_inputs, score_events=timed_events, side_event=side_event)
 
+    sampler = ClockSampler(local)  # NVML set-up takes milliseconds and differs per rank: keep it out of the start line
     for _ in range(args.warmup):
         step()
     ob.drain()
     if dist is not None:
         dist.barrier()
         torch.cuda.synchronize()
-
-    sampler = ClockSampler(local)
     sampler.start()
+    if dist is not None:
+        # device-side start line: the ranks leave the host barrier up to milliseconds apart, and a rank that
+        # starts early only waits for its partner's first payload (round 1: one such wait halved the 8-GPU
+        # number of a 16 ms timed region).  This all-reduce is queued on the scoring stream right before the
+        # start event, so every rank's GPU begins step 0 when the slowest rank's host has got here.
+        start_line = torch.zeros(1, device=device)
+        dist.all_reduce(start_line)
     k_events = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     side_events = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     host_t = [0.0] * (args.steps + 1)
