@@ -145,6 +145,50 @@ def synth_qk(cfg, B, device, seed):
     return q, k
 
 
+def side_kernel_rooflines(splitq, N, cfg, B, S, D, ladder, h, device):
+    """HBM rooflines of the kernels that run beside the scoring (SURVEY 8d algorithmic bytes): each is
+    timed ALONE here, after the step loop, with CUDA events on its stream, median of 20 launches, the
+    126 MB L2 flushed before every launch (in the step they share the GPU with the scoring kernel, so
+    their in-step times say nothing about the kernels themselves)."""
+    import statistics as st
+    peak, peak_src = load_peaks()
+    mode = cfg["scale_mode"]
+    nbytes = splitq.payload_bytes(S, D, ladder, mode)
+    gen = torch.Generator(device=device).manual_seed(99)
+    imp = torch.rand(B, S, device=device, generator=gen)
+    bits, off = splitq.select_bits(imp, ladder, D)
+    payload = torch.empty(B, nbytes, dtype=torch.uint8, device=device)
+    payload2 = torch.empty_like(payload)
+    out = torch.empty(B, S, D, device=device)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    splitq.quant_pack(h, bits, off, mode, nbytes, payload)
+    group_extra = 0 if mode == N.SCALE_TOKEN else 4 * sum(k for k, _ in ladder) * D * B  # group mode re-reads the selected rows
+    cases = [
+        ("select_bits", lambda: splitq.select_bits(imp, ladder, D, bits, off), 4 * B * S + 5 * B * S, "latency (S floats per window, one CTA each)"),
+        ("quant_pack", lambda: splitq.quant_pack(h, bits, off, mode, nbytes, payload),
+         4 * B * S * D + 5 * B * S + B * nbytes + group_extra, "hbm"),
+        ("transfer_copy", lambda: splitq.transfer(payload2, payload), 2 * B * nbytes, "hbm (device copy standing in for the hop at N = 1)"),
+        ("dequant", lambda: splitq.dequant(payload, S, D, out), B * nbytes + 4 * B * S * D, "hbm"),
+    ]
+    res = {"peak": peak, "peak_source": peak_src, "unit": "GB/s",
+           "method": "each kernel alone, CUDA events, median of 20, L2 flushed before every launch"}
+    for name, fn, alg, bound in cases:
+        ts = []
+        for i in range(23):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(a.elapsed_time(b))
+        ms = st.median(ts)
+        res[name] = {"bound": bound, "kernel_us": 1e3 * ms, "algorithmic_bytes": alg, "achieved": alg / ms / 1e6,
+                     "frac": alg / ms / 1e6 / peak, "frac_of_8tbs_spec": alg / ms / 1e6 / 8000.0}
+    return res
+
+
 def cpu_pass(O, cfg, ladder, fused, inputs):
     """One pass of the reference's CPU path over ONE window (oracle restatement, vectorised ATen)."""
     if fused:
@@ -222,6 +266,75 @@ def run_reference_eval(args):
                       "split_forward_tokens_per_s": args.steps * S * combos / dt}))
 
 
+def run_eval(args):
+    """--eval-family F (product arm): BASELINE.json's second metric, split-inference eval tokens/sec.  The
+    reference's sliding-window sweep (methods x split layers x ratios per window) through splitq.evalloop:
+    on one GPU both halves run there; on N >= 2 GPUs in the GPU-PAIR layout of SURVEY 8e -- rank 2p runs
+    scoring + the upstream half + select/quantise/pack on its GPU, rank 2p+1 dequantise + the downstream
+    half + loss on its own, payloads cross by NCCL send/recv, pair p of N/2 owns windows k = p (mod N/2),
+    NLL sums are all-reduced.  --steps = windows per pair (after --warmup windows per pair, untimed)."""
+    import splitq  # noqa: F401
+    from splitq import compat, evalloop
+    from splitq.models import Pythia70Model, QwenPointFiveBModel
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    sw = dict(EVAL_SWEEPS[args.eval_family])
+    family = sw.pop("family")
+    pairs = world >= 2
+    shards = world // 2 if pairs else 1
+    S, stride = sw["max_length"], sw["stride"]
+    if family == "qwen2":
+        cfg, wrapper = compat.QWEN2_05B, None
+        wrapper = QwenPointFiveBModel.from_config(dev, cfg=cfg, seed=0)
+    else:
+        cfg = compat.PYTHIA_70M
+        wrapper = Pythia70Model.from_config(dev, sw["ratios"], cfg=cfg, seed=0)
+    fn = evalloop.make_importance_fn(wrapper, sw["methods"], "fused", layers=sw["layers_of_interest"])
+
+    def sweep(windows):
+        n = S + (windows - 1) * stride
+        ids = torch.randint(0, cfg["vocab_size"], (1, n), generator=torch.Generator().manual_seed(1234))
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = evalloop.evaluate(sw, wrapper, ids, fn, S, reduce_device=dev if dist is not None else None,
+                                log=lambda *a: None, batch_combos=True, pairs=pairs)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = t.item()
+        return res, dt
+
+    sweep(max(1, args.warmup) * shards)
+    windows = args.steps * shards
+    res, dt = sweep(windows)
+    combos = len(sw["methods"]) * len(sw["layers_of_interest"]) * len(sw["ratios"])
+    if rank == 0:
+        print(json.dumps({
+            "metric": "eval window tokens/sec (split-inference sweep)", "value": windows * S / dt, "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"eval-{args.eval_family}", "model": family, "S": S, "stride": stride,
+                       "combos_per_window": combos, "windows": windows, "windows_scored": res.windows,
+                       "layout": (f"{shards} GPU pair(s): upstream half on rank 2p, downstream half on rank 2p+1, payload over "
+                                  "NCCL send/recv" if pairs else "both halves on one GPU"),
+                       "batching": "all (method, ratio > 0) variants of a split layer as one downstream batch"},
+            "split_forward_tokens_per_s": windows * S * combos / dt, "scored_tokens": res.n_tokens}))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def run_reference(args, cfg, name):
     """--impl reference: the reference's CPU implementation of the same path, all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -286,7 +399,8 @@ def main() -> None:
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--eval-family", default=None, choices=["qwen", "pythia"],
-                    help="with --impl reference: time the CPU port of the eval-loop sweep over --steps windows instead")
+                    help="time the sliding-window eval sweep instead of the boundary path: --steps windows (per GPU pair); "
+                         "with --impl reference the CPU port of the reference loop")
     args = ap.parse_args()
     cfg = WORKLOADS[args.workload]
     if args.impl == "reference" and args.eval_family:
@@ -294,6 +408,9 @@ def main() -> None:
         return
     if args.impl == "reference":
         run_reference(args, cfg, args.workload)
+        return
+    if args.eval_family:
+        run_eval(args)
         return
     args.warmup = max(args.warmup, 3)
 
@@ -450,6 +567,7 @@ def main() -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms, e2e_s, score_ms = t.tolist()
 
+    aux = side_kernel_rooflines(splitq, N, cfg, B, S, D, ladder, h, device) if rank == 0 else None
     if rank == 0:
         peaks = {}
         path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -480,10 +598,14 @@ def main() -> None:
             dense_equiv = 4.0 * B * H * S * S * 64
             achieved = issued / (score_ms * 1e-3) / 1e12
             mufu_ms = tiles * 128 * 128 / (16.0 * 148 * 1.965e9) * 1e3   # 16 ex2/clk/SM at the max SM clock
+            burst = peaks.get("bf16_tflops", 1590.0)
             roofline = {
-                "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + operand split + finalize",
+                "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + operand split + lse merge + finalize",
                 "achieved": achieved, "peak": peak_mix, "unit": "TFLOP/s", "frac": achieved / peak_mix,
-                "traffic": (captured_traffic("r1_h_ncu_full_k2_summary.csv", "fused_importance_kernel")
+                "frac_of_sustained_peak": achieved / peak_mix, "frac_of_burst_peak": achieved / burst,
+                "which_peak_applies": "sustained: the kernel runs back to back inside the step loop and the SM clock sits "
+                                      "near 1.65 GHz under sw_power_cap while it does (ncu: cycles / duration)",
+                "traffic": (captured_traffic("r2_b_ncu_full_k2_summary.csv", "fused_importance_kernel")
                             if args.workload == DEFAULT_WORKLOAD and B == cfg["B_fused"] and x3 else None),
                 "traffic_note": "DRAM bytes of the two tensor-core passes (ncu); operands are re-read from L2, not HBM",
                 "peak_source": (f"MEASURED_PEAKS.json {bf16_key}" if peaks else "fallback 1590 (B200_PROFILING.md)") +
@@ -523,6 +645,7 @@ def main() -> None:
                        "pipelining": ("hop + dequantise" if args.pack_on_main else "select + quantise/pack + hop + dequantise") +
                                      " of step i on a side stream, overlapping the scoring of step i+1"},
             "roofline": roofline,
+            "roofline_aux": aux,
             "e2e": {"value": world * B * S * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
                     "api": "splitq.HostPipeline.submit/drain (pinned host buffers, 3 streams, depth 2)"},
