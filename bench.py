@@ -147,42 +147,48 @@ def synth_qk(cfg, B, device, seed):
 
 def side_kernel_rooflines(splitq, N, cfg, B, S, D, ladder, h, device):
     """HBM rooflines of the kernels that run beside the scoring (SURVEY 8d algorithmic bytes): each is
-    timed ALONE here, after the step loop, with CUDA events on its stream, median of 20 launches, the
-    126 MB L2 flushed before every launch (in the step they share the GPU with the scoring kernel, so
-    their in-step times say nothing about the kernels themselves)."""
+    timed ALONE here, after the step loop (in the step they share the GPU with the scoring kernel, so
+    their in-step times say nothing about the kernels themselves): CUDA events around 8 back-to-back
+    launches that rotate through 4 separate buffer sets (640 MB, so no launch finds its data in the
+    126 MB L2), median of 7 such groups, time per launch."""
     import statistics as st
     peak, peak_src = load_peaks()
     mode = cfg["scale_mode"]
     nbytes = splitq.payload_bytes(S, D, ladder, mode)
     gen = torch.Generator(device=device).manual_seed(99)
-    imp = torch.rand(B, S, device=device, generator=gen)
-    bits, off = splitq.select_bits(imp, ladder, D)
-    payload = torch.empty(B, nbytes, dtype=torch.uint8, device=device)
-    payload2 = torch.empty_like(payload)
-    out = torch.empty(B, S, D, device=device)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
-    splitq.quant_pack(h, bits, off, mode, nbytes, payload)
+    SETS, REP = 4, 8
+    hs = [h] + [torch.randn(B, S, D, device=device, generator=gen) for _ in range(SETS - 1)]
+    imps = [torch.rand(B, S, device=device, generator=gen) for _ in range(SETS)]
+    maps = [splitq.select_bits(imp, ladder, D) for imp in imps]
+    payloads = [torch.empty(B, nbytes, dtype=torch.uint8, device=device) for _ in range(SETS)]
+    payloads2 = [torch.empty(B, nbytes, dtype=torch.uint8, device=device) for _ in range(SETS)]
+    outs = [torch.empty(B, S, D, device=device) for _ in range(SETS)]
+    for i in range(SETS):
+        splitq.quant_pack(hs[i], maps[i][0], maps[i][1], mode, nbytes, payloads[i])
     group_extra = 0 if mode == N.SCALE_TOKEN else 4 * sum(k for k, _ in ladder) * D * B  # group mode re-reads the selected rows
     cases = [
-        ("select_bits", lambda: splitq.select_bits(imp, ladder, D, bits, off), 4 * B * S + 5 * B * S, "latency (S floats per window, one CTA each)"),
-        ("quant_pack", lambda: splitq.quant_pack(h, bits, off, mode, nbytes, payload),
+        ("select_bits", lambda i: splitq.select_bits(imps[i], ladder, D, maps[i][0], maps[i][1]), 4 * B * S + 5 * B * S,
+         "latency (S floats per window, one CTA each)"),
+        ("quant_pack", lambda i: splitq.quant_pack(hs[i], maps[i][0], maps[i][1], mode, nbytes, payloads[i]),
          4 * B * S * D + 5 * B * S + B * nbytes + group_extra, "hbm"),
-        ("transfer_copy", lambda: splitq.transfer(payload2, payload), 2 * B * nbytes, "hbm (device copy standing in for the hop at N = 1)"),
-        ("dequant", lambda: splitq.dequant(payload, S, D, out), B * nbytes + 4 * B * S * D, "hbm"),
+        ("transfer_copy", lambda i: splitq.transfer(payloads2[i], payloads[i]), 2 * B * nbytes,
+         "hbm (device copy standing in for the hop at N = 1)"),
+        ("dequant", lambda i: splitq.dequant(payloads[i], S, D, outs[i]), B * nbytes + 4 * B * S * D, "hbm"),
     ]
     res = {"peak": peak, "peak_source": peak_src, "unit": "GB/s",
-           "method": "each kernel alone, CUDA events, median of 20, L2 flushed before every launch"}
+           "method": f"each kernel alone: CUDA events around {REP} back-to-back launches rotating through {SETS} buffer sets "
+                     "(working set 640 MB >> L2), median of 7 groups, per launch"}
     for name, fn, alg, bound in cases:
         ts = []
-        for i in range(23):
-            flush.zero_()
+        for rep in range(9):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            fn()
+            for j in range(REP):
+                fn(j % SETS)
             b.record()
             torch.cuda.synchronize()
-            if i >= 3:
-                ts.append(a.elapsed_time(b))
+            if rep >= 2:
+                ts.append(a.elapsed_time(b) / REP)
         ms = st.median(ts)
         res[name] = {"bound": bound, "kernel_us": 1e3 * ms, "algorithmic_bytes": alg, "achieved": alg / ms / 1e6,
                      "frac": alg / ms / 1e6 / peak, "frac_of_8tbs_spec": alg / ms / 1e6 / 8000.0}
