@@ -291,6 +291,7 @@ def run_eval(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
+        os.environ.setdefault("TORCH_NCCL_SHOW_EAGER_INIT_P2P_SERIALIZATION_WARNING", "false")
         dist.init_process_group("nccl", device_id=torch.device(dev))
     sw = dict(EVAL_SWEEPS[args.eval_family])
     family = sw.pop("family")

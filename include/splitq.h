@@ -94,8 +94,9 @@ int splitq_importance_colmean(const float* A, int B, int H, int Sq, int Sk, cons
  *   scaling = head_dim^-0.5; causal != 0 applies the lower-triangular mask.
  *   mode: SPLITQ_FUSED_F16X3 (operands split into h0 = fp16(x), h1 = fp16(x - h0); three fp16
  *   products h0*h0 + h1*h0 + h0*h1 accumulated in fp32: ~fp32 accuracy, meets 1e-5) or
- *   SPLITQ_FUSED_F16X1 (h0*h0 only, 11-bit mantissas).  Both need |q|,|k| < 65504 (fp16 range);
- *   beyond it the scores come out NaN.
+ *   SPLITQ_FUSED_F16X1 (h0*h0 only, 11-bit mantissas).  Any finite magnitude works: a 128-row block
+ *   whose largest |x| leaves [2^-10, 2^15) is multiplied by a power of two before the fp16 conversion
+ *   and the factor is restored per tile; non-finite inputs give non-finite scores.
  *   ws: 256-byte aligned scratch of splitq_importance_fused_workspace_bytes(). */
 #define SPLITQ_FUSED_F16X3 0
 #define SPLITQ_FUSED_F16X1 1
@@ -105,6 +106,16 @@ int splitq_importance_fused(const float* Q, const long long* q_strides_host, con
                             float scaling, int causal, int mode, const float* head_w_host,
                             float* out_col, float* out_last, void* ws, size_t ws_bytes,
                             splitq_stream_t stream);
+
+/* Same call with a SECOND set of head weights over the same per-head column sums: one scoring pass
+ * yields the plain column mean / last row (head_w_host, NULL = 1/H) and the "weighted_importance" of
+ * Qwen2-0.5B/main.py:57-78 (head_w2_host -> out_col2) -- the reference's loop evaluates both methods
+ * for every window (main.py:151-178). */
+int splitq_importance_fused_dual(const float* Q, const long long* q_strides_host, const float* K,
+                                 const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
+                                 float scaling, int causal, int mode, const float* head_w_host,
+                                 float* out_col, float* out_last, const float* head_w2_host,
+                                 float* out_col2, void* ws, size_t ws_bytes, splitq_stream_t stream);
 
 /* ---- selection (K3a) -------------------------------------------------------------------
  * Replaces torch.argsort(importance)[:int(ratio*S)] (Pythia-70M/pythia_model.py:169-170,

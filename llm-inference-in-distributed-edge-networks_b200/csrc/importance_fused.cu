@@ -1095,21 +1095,24 @@ struct HeadW {
 };
 __global__ void __launch_bounds__(256)
 fused_finalize_kernel(const float* __restrict__ part_col, const float* __restrict__ part_last, size_t rows, int H, int S,
-                      HeadW hw, float* __restrict__ out_col, float* __restrict__ out_last) {
+                      HeadW hw, float* __restrict__ out_col, float* __restrict__ out_last, HeadW hw2,
+                      float* __restrict__ out_col2) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int b = blockIdx.y;
     if (j >= S) return;
-    float c = 0.f, l = 0.f;
+    float c = 0.f, l = 0.f, c2 = 0.f;
     for (int h = 0; h < H; ++h) {
         const size_t o = ((size_t)b * H + h) * S + j;
         float pc = 0.f;
 #pragma unroll
         for (int sl = 0; sl < kSlots; ++sl) pc += part_col[sl * rows + o];  // fixed order: schedule-independent
         c += hw.w[h] * pc;
+        c2 += hw2.w[h] * pc;   // a second set of head weights over the same per-head sums (weighted_importance)
         l += hw.w[h] * part_last[o];
     }
     if (out_col) out_col[(size_t)b * S + j] = c / (float)S;
     if (out_last) out_last[(size_t)b * S + j] = l;
+    if (out_col2) out_col2[(size_t)b * S + j] = c2 / (float)S;
 }
 
 // ---- last-row importance only: a single-query GEMV per head, no S x S work at all ---------------
@@ -1231,13 +1234,13 @@ extern "C" size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH,
     return ws_layout(B, H, KVH, S).total;
 }
 
-extern "C" int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
-                                       const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
-                                       float scaling, int causal, int mode, const float* head_w_host,
-                                       float* out_col, float* out_last, void* ws, size_t ws_bytes,
-                                       splitq_stream_t stream) {
-    SPLITQ_REQUIRE(Q && K && (out_col || out_last) && q_strides_host && k_strides_host, SPLITQ_ERR_ARG,
+static int fused_impl(const float* Q, const long long* q_strides_host, const float* K, const long long* k_strides_host,
+                      int B, int H, int KVH, int S, int hd, float scaling, int causal, int mode,
+                      const float* head_w_host, float* out_col, float* out_last, const float* head_w2_host,
+                      float* out_col2, void* ws, size_t ws_bytes, splitq_stream_t stream) {
+    SPLITQ_REQUIRE(Q && K && (out_col || out_last || out_col2) && q_strides_host && k_strides_host, SPLITQ_ERR_ARG,
                    "importance_fused: NULL argument");
+    SPLITQ_REQUIRE(!out_col2 || head_w2_host, SPLITQ_ERR_ARG, "importance_fused: out_col2 given without head_w2_host");
     SPLITQ_REQUIRE(B > 0 && H > 0 && KVH > 0 && S > 0 && H % KVH == 0 && H <= SPLITQ_MAX_HEADS, SPLITQ_ERR_ARG,
                    "importance_fused: bad shape B=%d H=%d KVH=%d S=%d", B, H, KVH, S);
     SPLITQ_REQUIRE(hd == kHd, SPLITQ_ERR_ARG, "importance_fused: head_dim %d unsupported (only 64); use the "
@@ -1255,7 +1258,7 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     if (int rc = check_arch()) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t* w8 = (uint8_t*)ws;
-    if (!out_col && causal) {
+    if (!out_col && !out_col2 && causal) {
         // "last_row" alone needs one query row per head: GEMV + softmax, exact fp32, no tensor cores
         HeadW hw1;
         for (int h = 0; h < H; ++h) hw1.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
@@ -1342,7 +1345,27 @@ extern "C" int splitq_importance_fused(const float* Q, const long long* q_stride
     HeadW hw;
     for (int h = 0; h < H; ++h) hw.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
     dim3 fg(cdiv(S, 256), B);
-    fused_finalize_kernel<<<fg, 256, 0, st>>>(p.part_col, p.part_last, rows, H, S, hw, out_col, out_last);
+    HeadW hw2;
+    for (int h = 0; h < H; ++h) hw2.w[h] = (out_col2 && head_w2_host) ? head_w2_host[h] : 0.f;
+    fused_finalize_kernel<<<fg, 256, 0, st>>>(p.part_col, p.part_last, rows, H, S, hw, out_col, out_last, hw2, out_col2);
     SPLITQ_LAUNCH_CHECK("fused_finalize_kernel");
     return SPLITQ_OK;
+}
+
+extern "C" int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
+                                       const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
+                                       float scaling, int causal, int mode, const float* head_w_host,
+                                       float* out_col, float* out_last, void* ws, size_t ws_bytes,
+                                       splitq_stream_t stream) {
+    return fused_impl(Q, q_strides_host, K, k_strides_host, B, H, KVH, S, hd, scaling, causal, mode, head_w_host, out_col,
+                      out_last, nullptr, nullptr, ws, ws_bytes, stream);
+}
+
+extern "C" int splitq_importance_fused_dual(const float* Q, const long long* q_strides_host, const float* K,
+                                            const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
+                                            float scaling, int causal, int mode, const float* head_w_host,
+                                            float* out_col, float* out_last, const float* head_w2_host,
+                                            float* out_col2, void* ws, size_t ws_bytes, splitq_stream_t stream) {
+    return fused_impl(Q, q_strides_host, K, k_strides_host, B, H, KVH, S, hd, scaling, causal, mode, head_w_host, out_col,
+                      out_last, head_w2_host, out_col2, ws, ws_bytes, stream);
 }

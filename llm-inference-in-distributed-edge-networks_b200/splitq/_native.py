@@ -37,6 +37,8 @@ SIGNATURES = {
     "splitq_importance_fused_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "splitq_importance_fused": (_i, [_vp, _llp, _vp, _llp, _i, _i, _i, _i, _i, C.c_float, _i, _i, _fp, _vp, _vp, _vp,
                                      _sz, _vp]),
+    "splitq_importance_fused_dual": (_i, [_vp, _llp, _vp, _llp, _i, _i, _i, _i, _i, C.c_float, _i, _i, _fp, _vp, _vp, _fp, _vp,
+                                          _vp, _sz, _vp]),
     "splitq_select_bits": (_i, [_vp, _i, _i, _i, _ip, _ip, _i, _vp, _vp, _vp]),
     "splitq_select_bits_per_window": (_i, [_vp, _i, _i, _i, _i, _ip, C.POINTER(C.c_double), _vp, _vp, _vp, _vp]),
     "splitq_payload_bytes": (_sz, [_i, _i, _ip, _ip, _i, _i]),

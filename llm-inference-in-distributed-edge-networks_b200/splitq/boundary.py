@@ -119,7 +119,8 @@ def importance_from_attention(A: torch.Tensor, head_w: Optional[Sequence[float]]
 def importance_fused(q: torch.Tensor, k: torch.Tensor, scaling: float, causal: bool = True,
                      mode: int = N.FUSED_F16X3, head_w: Optional[Sequence[float]] = None, want_col: bool = True,
                      want_last: bool = False, out_col: Optional[torch.Tensor] = None,
-                     out_last: Optional[torch.Tensor] = None, workspace: Optional[_Workspace] = None):
+                     out_last: Optional[torch.Tensor] = None, workspace: Optional[_Workspace] = None,
+                     head_w2: Optional[Sequence[float]] = None):
     """q: (B,H,S,64), k: (B,KVH,S,64) post-RoPE fp32 CUDA tensors (any batch/head/seq strides, e.g.
     HF's `.view(...).transpose(1, 2)`) -> (col (B,S) or None, last (B,S) or None) without ever
     materialising the (S,S) attention matrix."""
@@ -144,6 +145,18 @@ def importance_fused(q: torch.Tensor, k: torch.Tensor, scaling: float, causal: b
             raise N.SplitqError(f"head_w has {len(hw)} entries for {H} heads")
     qs = (C.c_longlong * 3)(q.stride(0), q.stride(1), q.stride(2))
     ks = (C.c_longlong * 3)(k.stride(0), k.stride(1), k.stride(2))
+    if head_w2 is not None:
+        # a second weighting of the same per-head sums in the same pass -> third return value (B,S)
+        hw2 = N.float_array([float(x) for x in head_w2])
+        if len(hw2) != H:
+            raise N.SplitqError(f"head_w2 has {len(hw2)} entries for {H} heads")
+        out_col2 = torch.empty(B, S, dtype=torch.float32, device=q.device)
+        with torch.cuda.device(q.device):
+            N.check(lib.splitq_importance_fused_dual(_ptr(q), qs, _ptr(k), ks, B, H, KVH, S, hd, float(scaling), int(causal),
+                                                     mode, hw, _ptr(out_col if want_col else None),
+                                                     _ptr(out_last if want_last else None), hw2, _ptr(out_col2), _ptr(ws),
+                                                     ws_bytes, _stream(q)))
+        return (out_col if want_col else None), (out_last if want_last else None), out_col2
     with torch.cuda.device(q.device):
         N.check(lib.splitq_importance_fused(_ptr(q), qs, _ptr(k), ks, B, H, KVH, S, hd, float(scaling), int(causal),
                                             mode, hw, _ptr(out_col if want_col else None),

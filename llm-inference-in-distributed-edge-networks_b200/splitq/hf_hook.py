@@ -68,16 +68,17 @@ class ImportanceCapture:
         if self.layers is not None and l not in self.layers:
             return
         q, k = query.float(), key.float()
-        col, last = boundary.importance_fused(q, k, scaling, causal=True, mode=self.mode, want_col=self.want_col,
-                                              want_last=self.want_last)
-        if col is not None:
+        # one scoring pass: the weighted column mean is a second weighting of the same per-head sums
+        hw2 = [float(x) for x in self.head_weights[l]] if self.head_weights is not None else None
+        res = boundary.importance_fused(q, k, scaling, causal=True, mode=self.mode, want_col=self.want_col or hw2 is not None,
+                                        want_last=self.want_last, head_w2=hw2)
+        col, last = res[0], res[1]
+        if col is not None and self.want_col:
             self.col[l] = col
         if last is not None:
             self.last[l] = last
-        if self.head_weights is not None:
-            w, _ = boundary.importance_fused(q, k, scaling, causal=True, mode=self.mode,
-                                             head_w=[float(x) for x in self.head_weights[l]])
-            self.weighted[l] = w
+        if hw2 is not None:
+            self.weighted[l] = res[2]
 
     def __enter__(self):
         register()
