@@ -98,6 +98,7 @@ struct SelShared {
     uint32_t tcnt[4][256];                      // top-rho: key counts per digit, per pass
     unsigned long long tmass[4][256];           // top-rho: fixed-point mass per digit, per pass
     uint32_t prefix[SPLITQ_MAX_LADDER], rem[SPLITQ_MAX_LADDER], eqcnt[SPLITQ_MAX_LADDER];
+    uint32_t cand_n[SPLITQ_MAX_LADDER], cand_fill[SPLITQ_MAX_LADDER], cand[SPLITQ_MAX_LADDER][32];
     uint32_t warp_tot[32];
     uint32_t t_prefix, t_nhi, t_done, t_keep;
     unsigned long long t_mhi;
@@ -255,6 +256,8 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
     }
     if (k_out && tid == 0) k_out[blockIdx.x] = thresh[0];
     if (tid < SPLITQ_MAX_LADDER) {
+        sh.cand_fill[tid] = 0u;
+        sh.cand_n[tid] = 0xffffffffu;
         sh.prefix[tid] = 0u;
         sh.rem[tid] = thresh[tid] > 0 ? (uint32_t)(thresh[tid] - 1) : 0u;
     }
@@ -289,9 +292,45 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
         }
         __syncthreads();
     }
-    for (int pass = 1; pass < 4; ++pass) {
+    bool finished = false;  // block-uniform: the shortcut below has already produced the pivots
+    for (int pass = 1; pass < 4 && !finished; ++pass) {
         const int shift = 24 - 8 * pass;
         const uint32_t himask = 0xffffffffu << (shift + 8);
+        if (pass == 2) {
+            // After two passes a pivot bin usually holds a handful of keys (4096 scores over 65536 bins).  If
+            // every rung's bin holds at most 32, the two remaining histogram passes are replaced by a direct
+            // ranking: the candidates of rung c are gathered into a short list and warp c ranks them with
+            // shuffles (count of smaller keys = rank, count of equal keys = what the tie rule needs).
+            bool few = true;
+            for (int c = 0; c < lad.n; ++c) few = few && sh.cand_n[c] <= 32u;
+            if (few) {
+                for (int c = 0; c < lad.n; ++c) {
+                    const uint32_t pre = sh.prefix[c];
+#pragma unroll
+                    for (int i = 0; i < ITEMS; ++i)
+                        if ((key[i] & himask) == pre) sh.cand[c][atomicAdd(&sh.cand_fill[c], 1u)] = key[i];
+                }
+                __syncthreads();
+                if (warp < lad.n) {
+                    const uint32_t n = sh.cand_n[warp], mine = lane < n ? sh.cand[warp][lane] : 0xffffffffu;
+                    uint32_t smaller = 0, equal = 0;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const uint32_t other = __shfl_sync(0xffffffffu, mine, j);
+                        if ((uint32_t)j < n) { smaller += other < mine; equal += other == mine; }
+                    }
+                    const uint32_t rem = sh.rem[warp];
+                    if (lane < n && smaller <= rem && rem < smaller + equal) {  // all lanes holding the pivot key agree
+                        sh.prefix[warp] = mine;
+                        sh.rem[warp] = rem - smaller;
+                        sh.eqcnt[warp] = equal;
+                    }
+                }
+                __syncthreads();
+                finished = true;
+                break;
+            }
+        }
         for (int c = 0; c < lad.n; ++c) {
             const uint32_t pre = sh.prefix[c];
 #pragma unroll
@@ -306,6 +345,7 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
             if (lane == 0) {
                 sh.prefix[warp] |= digit << shift;
                 sh.rem[warp] = rem;
+                if (pass == 1) sh.cand_n[warp] = sh.hist[1][warp][digit];  // keys left in the pivot bin
                 if (pass == 3) sh.eqcnt[warp] = sh.hist[3][warp][digit];  // keys equal to the pivot
             }
         }
