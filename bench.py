@@ -156,7 +156,7 @@ def side_kernel_rooflines(splitq, N, cfg, B, S, D, ladder, h, device):
     mode = cfg["scale_mode"]
     nbytes = splitq.payload_bytes(S, D, ladder, mode)
     gen = torch.Generator(device=device).manual_seed(99)
-    SETS, REP = 4, 8
+    SETS, REP = 4, 16
     hs = [h] + [torch.randn(B, S, D, device=device, generator=gen) for _ in range(SETS - 1)]
     imps = [torch.rand(B, S, device=device, generator=gen) for _ in range(SETS)]
     maps = [splitq.select_bits(imp, ladder, D) for imp in imps]

@@ -44,6 +44,9 @@ rows = [
     ("copy (hop stand-in)", lambda: splitq.transfer(payload2, payload), 2 * B * nbytes),
     ("dequant", lambda: splitq.dequant(payload, S, D, out), B * nbytes + 4 * B * S * D),
 ]
+hc = torch.randn(B, S, D, device=dev, generator=g)
+outc = torch.empty_like(hc)
+rows.append(("channel_fake_quant (channel_4)", lambda: splitq.channel_fake_quant(hc, "channel_4", out=outc), 3 * 4 * B * S * D))
 res = {}
 for name, fn, alg in rows:
     us = timed(fn)
