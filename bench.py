@@ -594,8 +594,13 @@ def main() -> None:
             l2_note = f"inputs per step ({4 * B * S * (64 * (H + KVH) + D) / 1e6:.0f} MB) exceed the 126 MB L2; no flush"
         elif fused:
             nb = (S + 127) // 128
-            tiles = B * H * nb * (nb + 1)  # causal tiles, two passes
-            tile_flops = 2.0 * 128 * 128 * 64
+            tn = N.load().splitq_importance_fused_tile_cols()    # a tile = 128 fixed rows x tn streamed rows
+            nbn = (S + tn - 1) // tn
+            # causal tiles of the two passes (the formulas of importance_fused.cu): pass 1 = query blocks x key
+            # tiles up to the block's last query, pass 2 = key blocks x query tiles from the block's first key on
+            tiles = B * H * (sum((min((b + 1) * 128, S) + tn - 1) // tn for b in range(nb)) +
+                             sum(nbn - (b * 128) // tn for b in range(nb)))
+            tile_flops = 2.0 * 128 * tn * 64
             # the kernel is timed inside a long back-to-back step loop: the sustained cuBLAS figure is its peak
             bf16_key = "bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "bf16_tflops"
             bf16 = peaks.get(bf16_key, 1590.0)
@@ -604,7 +609,7 @@ def main() -> None:
             peak_mix = bf16                                       # kind::f16 runs at the measured cuBLAS bf16 rate
             dense_equiv = 4.0 * B * H * S * S * 64
             achieved = issued / (score_ms * 1e-3) / 1e12
-            mufu_ms = tiles * 128 * 128 / (16.0 * 148 * 1.965e9) * 1e3   # 16 ex2/clk/SM at the max SM clock
+            mufu_ms = tiles * 128 * tn / (16.0 * 148 * 1.965e9) * 1e3   # 16 ex2/clk/SM at the max SM clock
             burst = peaks.get("bf16_tflops", 1590.0)
             roofline = {
                 "bound": "tensor", "kernel": "fused_importance_kernel (2 passes) + operand split + lse merge + finalize",
@@ -618,7 +623,8 @@ def main() -> None:
                 "peak_source": (f"MEASURED_PEAKS.json {bf16_key}" if peaks else "fallback 1590 (B200_PROFILING.md)") +
                                " (kind::f16 runs at the cuBLAS bf16 rate; burst figure: " +
                                f"{peaks.get('bf16_tflops', 1590.0):.0f})",
-                "flops_counted": "issued tcgen05 MMA flops: causal tiles x 2 passes x 3 fp16 products (split operands)",
+                "flops_counted": f"issued tcgen05 MMA flops: causal 128 x {tn} tiles of both passes x 3 fp16 products (split operands)",
+                "useful_128x128_tile_tflops": B * H * nb * (nb + 1) * 2.0 * 128 * 128 * 64 * (3 if x3 else 1) / (score_ms * 1e-3) / 1e12,
                 "issued_flops_per_launch": issued, "dense_equivalent_tflops": dense_equiv / (score_ms * 1e-3) / 1e12,
                 "kernel_ms": score_ms, "co_bound_mufu_frac": mufu_ms / score_ms,
                 "attention_matrix_bytes_avoided": 4 * B * H * S * S}

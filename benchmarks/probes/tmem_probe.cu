@@ -57,7 +57,7 @@ struct Out {
 };
 
 // ld_warps: 0, 4, 8 or 12 loading warps (warps 4.. of the CTA); ld_cols_per: 32 or 64 columns per wait
-// mma: 0 none, 1 TS N=128, 2 SS N=128, 3 TS N=256, 4 SS N=256
+// mma: 0 none, 1 TS N=128, 2 SS N=128, 3 TS N=256, 4 SS N=256, 5 TS N=192, 6 SS N=192, 7 TS N=64
 __global__ void __launch_bounds__(512, 1) probe(int ld_warps, int ld_per, int mma, int iters, Out* out) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[2];
@@ -83,13 +83,13 @@ __global__ void __launch_bounds__(512, 1) probe(int ld_warps, int ld_per, int mm
     long long t_ld = 0, t_mma = 0;
     if (warp == 1 && mma) {
         if (lane == 0) {
-            const int n = (mma >= 3) ? 256 : 128;
+            const int n = mma >= 7 ? 64 : (mma >= 5 ? 192 : ((mma >= 3) ? 256 : 128));
             const uint32_t idesc = (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
             const uint64_t bd = umma_desc(base), ad = umma_desc(base + 32 * 1024);
             const long long t0 = clock64();
             for (int i = 0; i < iters; ++i) {
                 const uint32_t d = tmem + (uint32_t)((i & 1) * (n == 256 ? 0 : 128));
-                if (mma == 1 || mma == 3) mma_ts(d, tmem + 384u + (uint32_t)(i & 3) * 8u, bd + (uint64_t)((i & 3) * 2), idesc);
+                if (mma == 1 || mma == 3 || mma == 5 || mma == 7) mma_ts(d, tmem + 384u + (uint32_t)(i & 3) * 8u, bd + (uint64_t)((i & 3) * 2), idesc);
                 else mma_ss(d, ad + (uint64_t)((i & 3) * 2), bd + (uint64_t)((i & 3) * 2), idesc);
             }
             tc_commit(smem_u32(&bars[0]));
@@ -135,10 +135,10 @@ int main() {
     const int smem = 64 * 1024 + 1024;
     cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const int iters = 4096;
-    const char* mma_names[] = {"none", "TS N=128", "SS N=128", "TS N=256", "SS N=256"};
-    for (int grid : {1, 148}) {
-        for (int mma = 0; mma <= 4; ++mma) {
-            for (int lw : {0, 4, 8, 12}) {
+    const char* mma_names[] = {"none", "TS N=128", "SS N=128", "TS N=256", "SS N=256", "TS N=192", "SS N=192", "TS N=64"};
+    for (int grid : {148}) {
+        for (int mma = 0; mma <= 7; ++mma) {
+            for (int lw : {0, 8}) {
                 for (int per : {32, 64}) {
                     if (lw == 0 && per == 64) continue;
                     if (lw == 0 && mma == 0) continue;
@@ -147,7 +147,7 @@ int main() {
                     cudaError_t e = cudaDeviceSynchronize();
                     if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); return 1; }
                     const double ld_clk = (double)out->ld_clk / iters, mma_clk = (double)out->mma_clk / iters;
-                    const int n = mma >= 3 ? 256 : 128;
+                    const int n = mma >= 7 ? 64 : (mma >= 5 ? 192 : (mma >= 3 ? 256 : 128));
                     printf("grid %3d mma %-9s ld warps %2d x%-2d : ", grid, mma_names[mma], lw, per);
                     if (lw) printf("%.1f clk per ld+wait per warp -> %.1f B/clk/SM  ", ld_clk, lw * per * 128.0 / ld_clk);
                     if (mma) printf("%.1f clk per MMA -> %.0f flop/clk/SM", mma_clk, 2.0 * 128 * n * 16 / mma_clk);

@@ -101,6 +101,9 @@ int splitq_importance_colmean(const float* A, int B, int H, int Sq, int Sk, cons
 #define SPLITQ_FUSED_F16X3 0
 #define SPLITQ_FUSED_F16X1 1
 size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd);
+/* columns of one tensor-core tile of the passes (128 fixed rows x this many streamed rows); lets a
+ * caller count the MMA work a call issues (bench.py's roofline) */
+int splitq_importance_fused_tile_cols(void);
 int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
                             const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
                             float scaling, int causal, int mode, const float* head_w_host,

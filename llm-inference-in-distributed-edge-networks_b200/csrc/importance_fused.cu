@@ -35,12 +35,23 @@
 namespace splitq {
 namespace k2 {
 
-constexpr int kTile = 128;
+constexpr int kTile = 128;                           // rows of the fixed operand = M of every MMA = TMEM lanes
+// Columns of one accumulator = rows of one streamed tile = N of every MMA: 128, or (build-time switch) 192 --
+// the widest that leaves room for the fixed operand in tensor memory (2 accumulators x 192 + 2 operand
+// buffers x 64 = all 512 columns).  192 is parity-green and slower at the bench shape (0.775 vs 0.725 ms on
+// one box): 6-9 % more tile area is issued around the causal diagonal and only two accumulators are in
+// flight; the MMA issue rate, which wider tiles amortise, is not what bounds the kernel.
+#ifndef SPLITQ_K2_NTILE
+#define SPLITQ_K2_NTILE 128
+#endif
+constexpr int kTileN = SPLITQ_K2_NTILE;
+static_assert(kTileN == 128 || kTileN == 192, "streamed tiles of 128 or 192 rows");
 constexpr int kHd = 64;
-constexpr uint32_t kPartBytes = 128 * 128;           // 128 rows x 64 fp16: one swizzle-128B slab (h0 or h1 part)
+constexpr uint32_t kFixPartBytes = kTile * 128;      // fixed operand in shared memory (kASmem): 128 rows x 64 fp16 per part
+constexpr uint32_t kPartBytes = kTileN * 128;        // kTileN rows x 64 fp16: one swizzle-128B slab (h0 or h1 part)
 constexpr uint32_t kOperandBytes = 2 * kPartBytes;   // h0 + h1
 #ifndef SPLITQ_K2_STAGES
-#define SPLITQ_K2_STAGES 4
+#define SPLITQ_K2_STAGES (SPLITQ_K2_NTILE == 192 ? 3 : 4)
 #endif
 constexpr int kStages = SPLITQ_K2_STAGES;            // streamed tiles in flight; one barrier pair and one TMA issue per tile
 // SPLITQ_K2_A_SMEM = 1: the fixed operand stays in shared memory (SS-mode MMA, brought in by TMA like
@@ -50,13 +61,15 @@ constexpr int kStages = SPLITQ_K2_STAGES;            // streamed tiles in flight
 #define SPLITQ_K2_A_SMEM 0
 #endif
 constexpr bool kASmem = SPLITQ_K2_A_SMEM != 0;
-constexpr int kAcc = kASmem ? 4 : 3;                 // TMEM accumulator buffers, used in rotation
+constexpr int kAcc = kTileN == 192 ? 2 : (kASmem ? 4 : 3);  // TMEM accumulator buffers, used in rotation
+static_assert(!kASmem || kTileN == 128, "the shared-memory fixed operand variant exists for 128-column tiles only");
 #ifndef SPLITQ_K2_EPI_GROUPS
 #define SPLITQ_K2_EPI_GROUPS 2
 #endif
 constexpr int kEpiGroups = SPLITQ_K2_EPI_GROUPS;      // epilogue warpgroups; tile n goes to group n % kEpiGroups
-constexpr int kChunk = kEpiGroups == 2 ? 64 : 32;     // accumulator columns per register buffer (two buffers per thread)
-constexpr int kChunks = kTile / kChunk;
+constexpr int kChunk = kEpiGroups == 2 ? (kTileN == 192 ? 48 : 64) : 32;  // accumulator columns per register buffer (two buffers per thread)
+constexpr int kChunks = kTileN / kChunk;
+static_assert(kChunks % 2 == 0 && kChunks * kChunk == kTileN, "an even number of chunks per tile keeps the two register buffers in step");
 constexpr int kEpiRegs = kEpiGroups == 2 ? 200 : 128; // setmaxnreg budgets; they add up to the launch-time pool
 constexpr int kCtlRegs = kEpiGroups == 2 ? 56 : 40;
 constexpr int kLdrRegs = 56;
@@ -70,12 +83,13 @@ static_assert(kEpiGroups == 2 || kEpiGroups == 3, "2 or 3 epilogue groups");
 static_assert(128 * (kCtlRegs + kLdrRegs + kEpiGroups * kEpiRegs) <= kThreads * (65536 / kThreads / 8 * 8),
               "setmaxnreg budgets exceed the registers the CTA is launched with");
 constexpr uint32_t kTmemCols = 512;                   // 3 accumulators (128 each) + 2 fixed-operand buffers (h0 32 + h1 32 each), or 4 accumulators
-constexpr uint32_t kTmemA = kAcc * 128;               // first column of the fixed-operand buffers
+constexpr uint32_t kTmemA = kAcc * kTileN;            // first column of the fixed-operand buffers
+static_assert(kTmemA + (kASmem ? 0 : 2 * 64) <= 512, "tensor memory overflow");
 constexpr uint32_t kTmemABuf = 64;                    // columns per fixed-operand buffer (two halfs per column)
 constexpr uint32_t kASmemOff = kStages * kOperandBytes;              // two fixed-operand buffers (kASmem only)
-constexpr uint32_t kBarOff = kASmemOff + (kASmem ? 2 * kOperandBytes : 0);
+constexpr uint32_t kBarOff = kASmemOff + (kASmem ? 2 * 2 * kFixPartBytes : 0);
 constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
-constexpr uint32_t kFlagOff = kLseOff + 4 * kEpiGroups * 2 * kTile * 4;     // lse: per epilogue warp 2 buffers x 128 floats
+constexpr uint32_t kFlagOff = kLseOff + 4 * kEpiGroups * 2 * kTileN * 4;    // per-query values: per epilogue warp 2 buffers x kTileN floats
 constexpr uint32_t kSmemBytes = kFlagOff + 256;                              // 3 floats per warp: launch-wide facts
 // (the dynamic smem base must be 1024-aligned; checked in the kernel)
 
@@ -199,10 +213,12 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
 // kind::f16 with fp16 A and B (format 0), fp32 accumulate, K-major, M = N = 128
-constexpr uint32_t kIdescF16 = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+constexpr uint32_t kIdescF16 = (1u << 4) | (((uint32_t)kTileN >> 3) << 17) | ((128u >> 4) << 24);  // M = 128, N = kTileN
 
 struct Params {
-    int B, H, KVH, S, nb;
+    int B, H, KVH, S, nb;  // nb = 128-row blocks per (b,h) = items
+    int nbn;               // streamed tiles (kTileN rows) per (b,h)
+    int per_bh;            // tiles of one (b,h) in one pass
     int causal, x3;    // x3: three products (h0*h0 + h1*h0 + h0*h1), else h0*h0 only
     int dbg;           // bit0: skip epilogue math, bit1: skip MMA issue, bit2: skip TMEM reads, bit4: loaders skip their global loads, bit5: never take the FAST epilogue
     int nq_blk, nk_blk;  // entries of bound2 / eblk that belong to Q blocks (B*H*nb) and to K blocks (B*KVH*nb)
@@ -211,7 +227,8 @@ struct Params {
     float* lse2;       // (B,H,S) log2-domain log-sum-exp (lse_combine_kernel)
     float* w2;         // (B,H,S) 2^-lse2 (FAST epilogue of pass 2)
     const float* bound2;  // per operand block: largest squared row norm (Q rows already carry scaling * log2 e)
-    const int* eblk;      // per operand block: exponent e of the power-of-two pre-scale 2^-e (0 unless |x| >= 2^15)
+    const int* ehead;     // per head (B*H query heads, then B*KVH key heads): exponent e of the power-of-two pre-scale 2^-e
+    int n_heads;          // B*H + B*KVH
     float* part_col;   // (kSlots,B,H,S) partial sum_i p[i][j] per result slot, pre-set to 0
     float* part_last;  // (B,H,S) p[S-1][j]
     const uint4 *q16, *k16;  // dense (n,S,64) fp16 h0 part; the h1 part follows at +q_part / +k_part uint4
@@ -234,21 +251,24 @@ struct Seg {
 };
 template <int PASS>
 struct SegIter {
-    int bh, blk, t, rem, nb;
+    int bh, blk, t, rem, nb, nbn, S, per_bh;
     bool causal;
-    __device__ __forceinline__ int t0(int b) const { return PASS == 1 ? 0 : (causal ? b : 0); }
-    __device__ __forceinline__ int t1(int b) const { return PASS == 1 ? (causal ? b + 1 : nb) : nb; }
+    // streamed tiles [t0, t1) of item blk.  pass 1: fixed = query block blk, streamed = key tiles up to
+    // its last query; pass 2: fixed = key block blk, streamed = query tiles from its first key on.
+    __device__ __forceinline__ int t0(int b) const { return PASS == 1 ? 0 : (causal ? (b * kTile) / kTileN : 0); }
+    __device__ __forceinline__ int t1(int b) const {
+        return PASS == 1 ? (causal ? (min((b + 1) * kTile, S) + kTileN - 1) / kTileN : nbn) : nbn;
+    }
     __device__ __forceinline__ void next_item() {
         if (++blk == nb) { blk = 0; ++bh; }
     }
     // position on the n-th tile (n >= 0) of this CTA's range
     __device__ __forceinline__ void init(const Params& p, int n) {
-        nb = p.nb;
+        nb = p.nb; nbn = p.nbn; S = p.S; per_bh = p.per_bh;
         causal = p.causal != 0;
         const long long T = p.tiles;
         const int lo = (int)(T * blockIdx.x / gridDim.x), hi = (int)(T * (blockIdx.x + 1) / gridDim.x);
         rem = hi - lo - n;
-        const int per_bh = causal ? nb * (nb + 1) / 2 : nb * nb;
         const int x = lo + n;
         bh = x / per_bh;
         int y = x - bh * per_bh;
@@ -291,6 +311,17 @@ struct SegIter {
 // NC (32 or 64) consecutive columns of this thread's TMEM lane; asynchronous until tc_ld_wait()
 template <int NC>
 __device__ __forceinline__ void tc_ld_issue(uint32_t taddr, float (&v)[NC]) {
+    static_assert(NC % 32 == 0 || NC % 32 == 16, "chunks of 32 columns plus an optional 16");
+    if (NC % 32 == 16) {
+        float* q = v + (NC / 32) * 32;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=f"(q[0]), "=f"(q[1]), "=f"(q[2]), "=f"(q[3]), "=f"(q[4]), "=f"(q[5]), "=f"(q[6]), "=f"(q[7]),
+              "=f"(q[8]), "=f"(q[9]), "=f"(q[10]), "=f"(q[11]), "=f"(q[12]), "=f"(q[13]), "=f"(q[14]), "=f"(q[15])
+            : "r"(taddr + (NC / 32) * 32)
+            : "memory");
+    }
 #pragma unroll
     for (int hlf = 0; hlf < NC / 32; ++hlf) {
         float* q = v + 32 * hlf;
@@ -563,8 +594,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const float b2 = __ldg(p.bound2 + i);
             if (i < p.nq_blk) q2 = fmaxf(q2, b2 == b2 ? b2 : INFINITY);
             else k2 = fmaxf(k2, b2 == b2 ? b2 : INFINITY);
-            emax = max(emax, __ldg(p.eblk + i));
         }
+        for (int i = threadIdx.x; i < p.n_heads; i += kThreads) emax = max(emax, abs(__ldg(p.ehead + i)));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             q2 = fmaxf(q2, __shfl_xor_sync(0xffffffffu, q2, o));
@@ -630,7 +661,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     const int fix_idx = PASS == 1 ? ia.bh : fb_ * p.KVH + fh_ / group;
                     if (elect_one()) {
                         mbar_expect_tx(bar_afull + 8 * ab, tile_tx);
-                        tma_load_4d(ring_s + kASmemOff + ab * kOperandBytes, fix_map, bar_afull + 8 * ab, 0, ia.blk * kTile,
+                        tma_load_4d(ring_s + kASmemOff + ab * (2 * kFixPartBytes), fix_map, bar_afull + 8 * ab, 0, ia.blk * kTile,
                                     fix_idx, 0);
                     }
                     __syncwarp();
@@ -648,7 +679,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                         mbar_wait_t<DBG>(bar_empty + 8 * stage, sphase ^ 1);
                         if (elect_one()) {
                             mbar_expect_tx(fb, tile_tx);
-                            tma_load_4d(dst, str_map, fb, 0, t * kTile, str_idx, 0);
+                            tma_load_4d(dst, str_map, fb, 0, t * kTileN, str_idx, 0);
                         }
                         __syncwarp();
                         if (++stage == kStages) { stage = 0; sphase ^= 1; }
@@ -670,7 +701,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 for (int k = 0; si.next(it); ++k) {
                     const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
                     const uint32_t a_h0 = tmem_base + kTmemA + ab * kTmemABuf, a_h1 = a_h0 + 32u;           // TMEM columns
-                    const uint32_t as_h0 = ring_s + kASmemOff + ab * kOperandBytes, as_h1 = as_h0 + kPartBytes;  // kASmem
+                    const uint32_t as_h0 = ring_s + kASmemOff + ab * (2 * kFixPartBytes), as_h1 = as_h0 + kFixPartBytes;  // kASmem
                     mbar_wait_t<DBG>(bar_afull + 8 * ab, abphase);
                     tc_fence_after();
                     for (int t = it.ta; t < it.tb; ++t, ++n_tile) {
@@ -692,7 +723,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                             __syncwarp();
                         }
                         tc_fence_after();
-                        const uint32_t d = tmem_base + acc * kTile;
+                        const uint32_t d = tmem_base + acc * kTileN;
                         const uint32_t st0 = ring_s + stage * kOperandBytes;
                         if (elect_one()) {
                             if (!(DBG && (p.dbg & 2))) {
@@ -777,17 +808,29 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const int grp = wg - 1;                     // this group takes tiles grp, grp + kEpiGroups, ...
         const int row = q4 * 32 + lane;
         const uint32_t tmem_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
-        const uint32_t lse_w = base + kLseOff + (uint32_t)(warp - 4) * (2u * kTile * 4u);  // two 128-float buffers per warp
+        const uint32_t lse_w = base + kLseOff + (uint32_t)(warp - 4) * (2u * kTileN * 4u);  // two kTileN-float buffers per warp
         const int S = p.S, dbg = DBG ? p.dbg : 0;
         const bool causal = p.causal != 0;
         // pass 2 stages one value per query of the tile: w = 2^-lse (FAST; 0 past S) or lse (+inf past S)
         const float* __restrict__ qval = FAST ? p.w2 : p.lse2;
         const float qfill = FAST ? 0.f : INFINITY;
         const bool lse_vec = (S & 3) == 0;
-        const int last_tile = (S - 1) / kTile, last_col = (S - 1) % kTile;
+        const int last_tile = (S - 1) / kTileN, last_col = (S - 1) % kTileN;
+        // one tile's per-query values: 32 lanes x float4 cover 128, lanes 0-15 fetch a second float4 for 192
+        struct QV { float4 a, b; };
+        auto load_qv = [&](int bh_, int t_) {
+            QV q;
+            const float* rowp = qval + (size_t)bh_ * S;
+            q.a = load_lse4(rowp, t_ * kTileN + lane * 4, S, lse_vec, qfill);
+            q.b = make_float4(qfill, qfill, qfill, qfill);
+            if (kTileN > 128 && lane < (kTileN - 128) / 4) q.b = load_lse4(rowp, t_ * kTileN + 128 + lane * 4, S, lse_vec, qfill);
+            return q;
+        };
+        auto stage_qv = [&](uint32_t buf, const QV& q) {
+            sts128(lse_w + buf * (kTileN * 4u) + 16u * lane, q.a);
+            if (kTileN > 128 && lane < (kTileN - 128) / 4) sts128(lse_w + buf * (kTileN * 4u) + 512u + 16u * lane, q.b);
+        };
         const size_t rows = (size_t)p.B * p.H * S;
-        const int nb = p.nb;
-
         SegIter<PASS> nx;                           // runs one tile ahead of the tile being processed
         nx.init(p, 0);
         const int first_bh = nx.bh, first_blk = nx.blk;
@@ -810,13 +853,12 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 if (saw_last) p.part_last[o] = lastp;
             }
         };
-        // general form only: 2^(exponents) of the two operand blocks of a tile, 1 unless a block was
-        // pre-scaled into fp16 range (eblk: Q blocks first, then K blocks)
-        auto tile_scale = [&](int bh, int blk, int t) -> float {
+        // general form only: 2^(exponents) of the query head and the key head of this item, 1 unless a head
+        // was pre-scaled into fp16 range (ehead: query heads first, then key heads)
+        auto tile_scale = [&](int bh) -> float {
             if (FAST || !scaled) return 1.0f;
             const int kv = (bh / p.H) * p.KVH + (bh % p.H) / group;
-            const int qb = PASS == 1 ? blk : t, kb = PASS == 1 ? t : blk;
-            const int e = __ldg(p.eblk + (size_t)bh * nb + qb) + __ldg(p.eblk + (size_t)p.B * p.H * nb + (size_t)kv * nb + kb);
+            const int e = __ldg(p.ehead + bh) + __ldg(p.ehead + p.B * p.H + kv);
             return __int_as_float((127 + min(max(e, -126), 127)) << 23);
         };
 
@@ -838,19 +880,19 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
 #endif
         if (have) {
             if (PASS == 2) {
-                sts128(lse_w + 16u * lane, load_lse4(qval + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec, qfill));
+                stage_qv(0u, load_qv(nx.bh, nx.t));
                 __syncwarp();
             }
             mbar_wait_t<DBG>(bar_tfull + 8 * acc_i, acc_ph);
             tc_fence_after();
-            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + acc_i * kTile, va);
+            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + acc_i * kTileN, va);
             tc_ld_wait();
         }
         while (have) {
             // ---- the tile being processed: (bh, blk, t), where nx stands before it moves on
             const int bh = nx.bh, blk = nx.blk, t = nx.t;
             const uint32_t a = acc_i;
-            const uint32_t cur_tmem = tmem_lane + a * kTile;
+            const uint32_t cur_tmem = tmem_lane + a * kTileN;
             // ---- look one tile ahead: is its accumulator ready (asked early, the answer takes ~100
             // cycles), and start fetching its per-query values
             uint32_t na = a + (uint32_t)(kEpiGroups % kAcc), nph = acc_ph;
@@ -859,8 +901,8 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             nx.advance(kEpiGroups);
             const bool has_next = nx.valid();
             bool ready = has_next && mbar_test(bar_tfull + 8 * na, nph);
-            float4 lse_nx = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (PASS == 2 && has_next) lse_nx = load_lse4(qval + (size_t)nx.bh * S, nx.t * kTile + lane * 4, S, lse_vec, qfill);
+            QV lse_nx = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+            if (PASS == 2 && has_next) lse_nx = load_qv(nx.bh, nx.t);
             // ---- entering a new item: store what the registers hold
             if (bh != st_bh || blk != st_blk) {
                 flush();
@@ -868,16 +910,21 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 st_bh = bh;
                 st_blk = blk;
             }
-            const float cs = tile_scale(bh, blk, t);
-            const bool diag = causal && t == blk;   // the causal boundary runs through this tile
+            const float cs = tile_scale(bh);
             const bool has_last = PASS == 2 && last_tile == t;
             saw_last = saw_last || has_last;
-            const uint32_t lse_t = lse_w + lb * (kTile * 4u);
-            // pass 1: largest valid tile-relative key of this row, and its range over the warp
-            const int s_hi = S - 1 - t * kTile;      // last key of the sequence, tile-relative (>= 127: no limit)
-            const int jmax = min(diag ? row : kTile - 1, s_hi);
-            const int jlo = min(diag ? q4 * 32 : kTile - 1, s_hi), jhi = min(diag ? q4 * 32 + 31 : kTile - 1, s_hi);
-            const bool edge1 = diag || s_hi < kTile - 1;
+            const uint32_t lse_t = lse_w + lb * (kTileN * 4u);
+            // Tile-relative position of the causal boundary.  The fixed block's row r (absolute index
+            // blk * 128 + r) meets the streamed tile's column c (absolute t * kTileN + c):
+            //   pass 1 (rows = queries, columns = keys): key c is valid iff c <= rel + r, and c < S - t * kTileN;
+            //   pass 2 (rows = keys, columns = queries): query c is valid iff c >= rel + r (queries past S carry
+            //   a per-query value that yields 0).
+            const int rel = causal ? blk * kTile - t * kTileN : (PASS == 1 ? kTileN : -kTile);
+            const int s_hi = S - 1 - t * kTileN;     // last key of the sequence, tile-relative
+            const int jmax = min(min(rel + row, kTileN - 1), s_hi);   // may be negative: no valid key for this row
+            const int jlo = min(min(rel + q4 * 32, kTileN - 1), s_hi), jhi = min(min(rel + q4 * 32 + 31, kTileN - 1), s_hi);
+            const bool edge1 = jlo < kTileN - 1;      // some (row, key) of this warp's part of the tile is masked
+            const bool diag = rel + q4 * 32 + 31 > 0; // pass 2: some (key, query) of this warp's part is masked
             float lastv = 0.f;
             if (has_last && !(dbg & 4)) tc_ld1_issue(cur_tmem + (uint32_t)last_col, lastv);  // lands with the next wait
 #pragma unroll
@@ -887,12 +934,12 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 if (c + 1 < kChunks) {                // next chunk of this tile in flight ...
                     if (!(dbg & 4)) tc_ld_issue<kChunk>(cur_tmem + (c + 1) * kChunk, oth);
                 } else if (has_next) {                // ... or the next tile's first chunk, if its MMAs are done
-                    if (PASS == 2) sts128(lse_w + (lb ^ 1u) * (kTile * 4u) + 16u * lane, lse_nx);
+                    if (PASS == 2) stage_qv(lb ^ 1u, lse_nx);
                     if (!ready) ready = mbar_test(bar_tfull + 8 * na, nph);
                     ready = __all_sync(0xffffffffu, ready);
                     if (ready) {
                         tc_fence_after();
-                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
+                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTileN, oth);
                     }
                 }
                 if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
@@ -906,11 +953,11 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     }
                 } else {
                     if (FAST) {
-                        if (diag) pass2_fast<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, colsum);
-                        else pass2_fast<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, colsum);
+                        if (diag) pass2_fast<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, colsum);
+                        else pass2_fast<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, colsum);
                     } else {
-                        if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
-                        else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, row, q4 * 32, cs, colsum);
+                        if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, cs, colsum);
+                        else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, cs, colsum);
                     }
                 }
                 if (c + 1 < kChunks) {
@@ -928,7 +975,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                     if (!ready) {
                         mbar_wait_t<DBG>(bar_tfull + 8 * na, nph);
                         tc_fence_after();
-                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTile, oth);
+                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTileN, oth);
                     }
                     tc_ld_wait();                     // next tile's first chunk landed
                     __syncwarp();                     // the per-query values staged by the other lanes are visible
@@ -974,9 +1021,22 @@ struct SplitArgs {
     float2* ml;               // result slots preset by the Q blocks: (kSlots, rows) (max, sum) = (-inf, 0)
     float* part_col;          // (kSlots, rows) = 0
     size_t rows;
-    float* bound2;            // (BH + BKV) * nb
-    int* eblk;                // (BH + BKV) * nb
+    float* bound2;            // (BH + BKV) * nb: largest squared row norm per block
+    int* eblk;                // (BH + BKV) * nb: exponent each block would like for itself
+    int* ehead;               // (BH + BKV): exponent every block of the head ends up with
 };
+// exponent all blocks of one head share: a tile of the passes spans more than one 128-row block of the
+// streamed operand, so the power of two must be uniform along a head.  If any block is beyond the fp16
+// range, the largest request wins; if EVERY block is far below it, the least negative one; otherwise 0.
+__device__ __forceinline__ int head_exponent(const int* __restrict__ e, int nb) {
+    int emax = -1000;
+    for (int i = 0; i < nb; ++i) emax = max(emax, __ldg(e + i));
+    return emax;  // > 0: some block is too large; < 0: every block is tiny; 0 otherwise
+}
+// FIXUP = false: convert every block with the exponent it asks for itself and record the request.
+// FIXUP = true (second launch, a few microseconds when nothing is to do): blocks whose own exponent
+// differs from the head's are converted again with the head's; records ehead.
+template <bool FIXUP>
 __global__ void __launch_bounds__(256)
 split_f16_kernel(const SplitArgs a) {
     __shared__ float s_red[2][8];
@@ -984,6 +1044,12 @@ split_f16_kernel(const SplitArgs a) {
     const bool isq = y < a.BH;
     const int bh = isq ? y : y - a.BH;
     const int heads = isq ? a.H : a.KVH;
+    int e_forced = 0;
+    if (FIXUP) {
+        e_forced = head_exponent(a.eblk + (size_t)y * a.nb, a.nb);
+        if (blockIdx.x == 0 && threadIdx.x == 0) a.ehead[y] = e_forced;
+        if (e_forced == __ldg(a.eblk + (size_t)y * a.nb + blockIdx.x)) return;  // block-uniform
+    }
     const int b = bh / heads, h = bh - b * heads;
     const long long* st = isq ? a.qs : a.ks;
     const float* src0 = (isq ? a.q : a.k) + b * st[0] + h * st[1];
@@ -992,8 +1058,6 @@ split_f16_kernel(const SplitArgs a) {
     const int row0 = blockIdx.x * kTile;
     constexpr int UN = kTile * (kHd / 4) / 256;  // 8 float4 per thread; 16 consecutive threads share a row
     float4 v[UN];
-    uint32_t amax = 0u;
-    float rmax = 0.f;
 #pragma unroll
     for (int u = 0; u < UN; ++u) {
         const int i = threadIdx.x + 256 * u;
@@ -1006,41 +1070,46 @@ split_f16_kernel(const SplitArgs a) {
         }
         v[u].x *= pre; v[u].y *= pre; v[u].z *= pre; v[u].w *= pre;
     }
+    int e = e_forced;
+    if (!FIXUP) {
+        uint32_t amax = 0u;
+        float rmax = 0.f;
 #pragma unroll
-    for (int u = 0; u < UN; ++u) {
-        amax = max(amax, __float_as_uint(v[u].x) & 0x7fffffffu);
-        amax = max(amax, __float_as_uint(v[u].y) & 0x7fffffffu);
-        amax = max(amax, __float_as_uint(v[u].z) & 0x7fffffffu);
-        amax = max(amax, __float_as_uint(v[u].w) & 0x7fffffffu);
-        float ss = fmaf(v[u].x, v[u].x, fmaf(v[u].y, v[u].y, fmaf(v[u].z, v[u].z, v[u].w * v[u].w)));
+        for (int u = 0; u < UN; ++u) {
+            amax = max(amax, __float_as_uint(v[u].x) & 0x7fffffffu);
+            amax = max(amax, __float_as_uint(v[u].y) & 0x7fffffffu);
+            amax = max(amax, __float_as_uint(v[u].z) & 0x7fffffffu);
+            amax = max(amax, __float_as_uint(v[u].w) & 0x7fffffffu);
+            float ss = fmaf(v[u].x, v[u].x, fmaf(v[u].y, v[u].y, fmaf(v[u].z, v[u].z, v[u].w * v[u].w)));
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);  // the 16 lanes of one row
-        rmax = fmaxf(rmax, ss == ss ? ss : INFINITY);
-    }
-    amax = __reduce_max_sync(0xffffffffu, amax);
+            for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);  // the 16 lanes of one row
+            rmax = fmaxf(rmax, ss == ss ? ss : INFINITY);
+        }
+        amax = __reduce_max_sync(0xffffffffu, amax);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) rmax = fmaxf(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) {
-        s_red[0][warp] = __uint_as_float(amax);
-        s_red[1][warp] = rmax;
-    }
-    __syncthreads();
+        for (int o = 16; o > 0; o >>= 1) rmax = fmaxf(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        if (lane == 0) {
+            s_red[0][warp] = __uint_as_float(amax);
+            s_red[1][warp] = rmax;
+        }
+        __syncthreads();
 #pragma unroll
-    for (int w = 0; w < 8; ++w) {
-        amax = max(amax, __float_as_uint(s_red[0][w]));
-        rmax = fmaxf(rmax, s_red[1][w]);
+        for (int w = 0; w < 8; ++w) {
+            amax = max(amax, __float_as_uint(s_red[0][w]));
+            rmax = fmaxf(rmax, s_red[1][w]);
+        }
+        // a block whose maximum lies in [2^-10, 2^15) asks for nothing (every ordinary activation); otherwise
+        // 2^-e brings the block maximum into [2^14, 2^15): down from beyond the fp16 range, or up from so far
+        // below it that the fp16 parts would be subnormal (e < 0)
+        const int ex = (int)(amax >> 23) - 127;
+        e = (ex >= 15 || (ex < -10 && amax != 0u)) ? ex - 14 : 0;
+        if (threadIdx.x == 0) {
+            a.bound2[(size_t)y * a.nb + blockIdx.x] = rmax;
+            a.eblk[(size_t)y * a.nb + blockIdx.x] = e;
+        }
     }
-    // a block whose maximum lies in [2^-10, 2^15) stays as it is (every ordinary activation); otherwise
-    // 2^-e brings the block maximum into [2^14, 2^15): down from beyond the fp16 range, or up from so far
-    // below it that the fp16 parts would be subnormal (e < 0)
-    const int ex = (int)(amax >> 23) - 127;
-    const int e = (ex >= 15 || (ex < -10 && amax != 0u)) ? ex - 14 : 0;
-    const float sc = __int_as_float((127 - e) << 23);
-    if (threadIdx.x == 0) {
-        a.bound2[(size_t)y * a.nb + blockIdx.x] = rmax;
-        a.eblk[(size_t)y * a.nb + blockIdx.x] = e;
-    }
+    const float sc = __int_as_float((127 - min(max(e, -126), 126)) << 23);
     const size_t n4 = (size_t)a.S * (kHd / 4);
     uint2* o0 = (isq ? a.q0 : a.k0) + (size_t)bh * n4 + (size_t)row0 * (kHd / 4);
     uint2* o1 = (isq ? a.q1 : a.k1) + (size_t)bh * n4 + (size_t)row0 * (kHd / 4);
@@ -1056,7 +1125,7 @@ split_f16_kernel(const SplitArgs a) {
             const __half2 l23 = __floats2half2_rn(x2 - f23.x, x3 - f23.y);
             o0[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a01), *reinterpret_cast<const uint32_t*>(&a23));
             o1[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
-            if (isq && (i & 15) == 0) {  // the Q blocks also preset the result slots of their (b,h,s) rows
+            if (!FIXUP && isq && (i & 15) == 0) {  // the Q blocks also preset the result slots of their (b,h,s) rows
                 const size_t rr = (size_t)bh * a.S + r;
 #pragma unroll
                 for (int sl = 0; sl < kSlots; ++sl) {
@@ -1197,7 +1266,7 @@ static int make_map(CUtensorMap* map, void* base, int S, long long n, size_t par
     SPLITQ_REQUIRE(enc != nullptr, SPLITQ_ERR_CUDA, "importance_fused: cuTensorMapEncodeTiled is unavailable");
     cuuint64_t dims[4] = {(cuuint64_t)kHd, (cuuint64_t)S, (cuuint64_t)n, 2};
     cuuint64_t strides[3] = {(cuuint64_t)kHd * 2, (cuuint64_t)S * kHd * 2, (cuuint64_t)part_stride_bytes};
-    cuuint32_t box[4] = {(cuuint32_t)kHd, (cuuint32_t)kTile, 1, (cuuint32_t)parts};
+    cuuint32_t box[4] = {(cuuint32_t)kHd, (cuuint32_t)kTileN, 1, (cuuint32_t)parts};  // one streamed tile
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, base, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1209,7 +1278,7 @@ static int make_map(CUtensorMap* map, void* base, int S, long long n, size_t par
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
 
 struct WsLayout {
-    size_t q0, q1, k0, k1, lse, pcol, plast, ml, w2, bound2, eblk, total;  // fp16 h0 / h1 parts of Q and K, per-(b,h,s) floats, per-block facts
+    size_t q0, q1, k0, k1, lse, pcol, plast, ml, w2, bound2, eblk, ehead, total;  // fp16 h0 / h1 parts of Q and K, per-(b,h,s) floats, per-block / per-head facts
 };
 static WsLayout ws_layout(int B, int H, int KVH, int S) {
     WsLayout w;
@@ -1219,7 +1288,8 @@ static WsLayout ws_layout(int B, int H, int KVH, int S) {
     w.q0 = 0; w.q1 = q; w.k0 = 2 * q; w.k1 = 2 * q + k;
     w.lse = 2 * q + 2 * k; w.pcol = w.lse + v; w.plast = w.pcol + kSlots * v; w.ml = w.plast + v;
     w.w2 = w.ml + 2 * kSlots * v; w.bound2 = w.w2 + v; w.eblk = w.bound2 + blk;
-    w.total = w.eblk + blk;
+    w.ehead = w.eblk + blk;
+    w.total = w.ehead + align256((size_t)B * (H + KVH) * 4);
     return w;
 }
 
@@ -1228,6 +1298,8 @@ static WsLayout ws_layout(int B, int H, int KVH, int S) {
 
 using namespace splitq;
 using namespace splitq::k2;
+
+extern "C" int splitq_importance_fused_tile_cols(void) { return kTileN; }
 
 extern "C" size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd) {
     if (B <= 0 || H <= 0 || KVH <= 0 || S <= 0 || hd != kHd) return 0;
@@ -1287,8 +1359,9 @@ static int fused_impl(const float* Q, const long long* q_strides_host, const flo
         a.cs = scaling * 1.4426950408889634f;
         a.q0 = (uint2*)(w8 + wl.q0); a.q1 = (uint2*)(w8 + wl.q1); a.k0 = (uint2*)(w8 + wl.k0); a.k1 = (uint2*)(w8 + wl.k1);
         a.ml = (float2*)(w8 + wl.ml); a.part_col = (float*)(w8 + wl.pcol); a.rows = (size_t)B * H * S;
-        a.bound2 = (float*)(w8 + wl.bound2); a.eblk = (int*)(w8 + wl.eblk);
-        split_f16_kernel<<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
+        a.bound2 = (float*)(w8 + wl.bound2); a.eblk = (int*)(w8 + wl.eblk); a.ehead = (int*)(w8 + wl.ehead);
+        split_f16_kernel<false><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
+        split_f16_kernel<true><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);  // head-uniform exponents; exits at once normally
         SPLITQ_LAUNCH_CHECK("split_f16_kernel");
     }
 
@@ -1300,7 +1373,9 @@ static int fused_impl(const float* Q, const long long* q_strides_host, const flo
     Params p;
     p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = nb;
     p.nq_blk = B * H * nb; p.nk_blk = B * KVH * nb;
-    p.w2 = (float*)(w8 + wl.w2); p.bound2 = (const float*)(w8 + wl.bound2); p.eblk = (const int*)(w8 + wl.eblk);
+    p.w2 = (float*)(w8 + wl.w2); p.bound2 = (const float*)(w8 + wl.bound2); p.ehead = (const int*)(w8 + wl.ehead);
+    p.n_heads = B * (H + KVH);
+    p.nbn = cdiv(S, kTileN);
     p.causal = causal ? 1 : 0;
     p.x3 = mode == SPLITQ_FUSED_F16X3;
     p.dbg = dbg;
@@ -1328,20 +1403,34 @@ static int fused_impl(const float* Q, const long long* q_strides_host, const flo
         if (dev < 64) attr_set[dev] = true;
     }
     }
-    const long long per_bh = p.causal ? (long long)p.nb * (p.nb + 1) / 2 : (long long)p.nb * p.nb;
-    const long long tiles = (long long)B * H * per_bh;
-    SPLITQ_REQUIRE(tiles < (1ll << 31), SPLITQ_ERR_ARG, "importance_fused: %lld tiles per pass do not fit 31 bits", tiles);
-    p.tiles = (int)tiles;
-    // every CTA's range is at least as long as the longest item (nb tiles), so an item is cut at most once
-    const int grid = (int)std::max<long long>(1, std::min<long long>(sms, tiles / p.nb));
+    // Tiles of one (b,h): item blk (a 128-row block of the fixed operand) meets the streamed kTileN-row tiles
+    // [0, ceil(min((blk+1)*128, S) / kTileN)) in pass 1 (keys up to its last query) and
+    // [floor(blk*128 / kTileN), nbn) in pass 2 (queries from its first key on); the two counts differ
+    // unless the tile is 128 wide.  SegIter<PASS>::t0/t1 are the device-side twins of these formulas.
+    long long per_bh[2] = {0, 0};
+    for (int blk = 0; blk < p.nb; ++blk) {
+        per_bh[0] += p.causal ? cdiv(std::min((blk + 1) * kTile, S), kTileN) : p.nbn;
+        per_bh[1] += p.causal ? p.nbn - (blk * kTile) / kTileN : p.nbn;
+    }
     const size_t rows = (size_t)B * H * S;
-    if (dbg) fused_importance_kernel<1, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
-    else fused_importance_kernel<1, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
-    SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 1)");
-    lse_combine_kernel<<<(unsigned)cdiv((long long)rows, 256), 256, 0, st>>>(p.ml, rows, p.lse2, p.w2);
-    if (dbg) fused_importance_kernel<2, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
-    else fused_importance_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
-    SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 2)");
+    for (int pass = 0; pass < 2; ++pass) {
+        const long long tiles = (long long)B * H * per_bh[pass];
+        SPLITQ_REQUIRE(tiles < (1ll << 31), SPLITQ_ERR_ARG, "importance_fused: %lld tiles per pass do not fit 31 bits", tiles);
+        p.per_bh = (int)per_bh[pass];
+        p.tiles = (int)tiles;
+        // every CTA's range is at least as long as the longest item (nbn tiles), so an item is cut at most once
+        const int grid = (int)std::max<long long>(1, std::min<long long>(sms, tiles / p.nbn));
+        if (pass == 0) {
+            if (dbg) fused_importance_kernel<1, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+            else fused_importance_kernel<1, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+            SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 1)");
+            lse_combine_kernel<<<(unsigned)cdiv((long long)rows, 256), 256, 0, st>>>(p.ml, rows, p.lse2, p.w2);
+        } else {
+            if (dbg) fused_importance_kernel<2, true><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+            else fused_importance_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(mq, mk, p);
+            SPLITQ_LAUNCH_CHECK("fused_importance_kernel (pass 2)");
+        }
+    }
     HeadW hw;
     for (int h = 0; h < H; ++h) hw.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
     dim3 fg(cdiv(S, 256), B);

@@ -35,6 +35,7 @@ SIGNATURES = {
     "splitq_importance_colmean_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "splitq_importance_colmean": (_i, [_vp, _i, _i, _i, _i, _fp, _vp, _vp, _vp, _sz, _u, _vp]),
     "splitq_importance_fused_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "splitq_importance_fused_tile_cols": (_i, []),
     "splitq_importance_fused": (_i, [_vp, _llp, _vp, _llp, _i, _i, _i, _i, _i, C.c_float, _i, _i, _fp, _vp, _vp, _vp,
                                      _sz, _vp]),
     "splitq_importance_fused_dual": (_i, [_vp, _llp, _vp, _llp, _i, _i, _i, _i, _i, C.c_float, _i, _i, _fp, _vp, _vp, _fp, _vp,
