@@ -667,7 +667,7 @@ def main() -> None:
                             "value": tokens_per_step / (max(r["step_ms"]["median"] for r in per_rank_all) * 1e-3),
                             "note": "tokens/s at the slowest rank's MEDIAN step-completion interval; `value` above "
                                     "stays total tokens / total time"},
-            "gpu_launches": (plan.launches_per_run(fused) - (4 if fused and cfg["method"] == "last_row" else 0)) * args.steps,
+            "gpu_launches": (plan.launches_per_run(fused) - (3 if fused and cfg["method"] == "last_row" else 0)) * args.steps,
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -227,7 +227,11 @@ struct Params {
     float* lse2;       // (B,H,S) log2-domain log-sum-exp (lse_combine_kernel)
     float* w2;         // (B,H,S) 2^-lse2 (FAST epilogue of pass 2)
     const float* bound2;  // per operand block: largest squared row norm (Q rows already carry scaling * log2 e)
-    const int* ehead;     // per head (B*H query heads, then B*KVH key heads): exponent e of the power-of-two pre-scale 2^-e
+    // exponent e of the power-of-two pre-scale 2^-e: with 128-column tiles every streamed tile is one block of
+    // the split, so each block keeps its own exponent (eblk, per block); wider tiles straddle blocks and need one
+    // exponent per head (ehead: B*H query heads, then B*KVH key heads; written by the fix-up launch)
+    const int* eblk;
+    const int* ehead;
     int n_heads;          // B*H + B*KVH
     float* part_col;   // (kSlots,B,H,S) partial sum_i p[i][j] per result slot, pre-set to 0
     float* part_last;  // (B,H,S) p[S-1][j]
@@ -595,7 +599,11 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             if (i < p.nq_blk) q2 = fmaxf(q2, b2 == b2 ? b2 : INFINITY);
             else k2 = fmaxf(k2, b2 == b2 ? b2 : INFINITY);
         }
-        for (int i = threadIdx.x; i < p.n_heads; i += kThreads) emax = max(emax, abs(__ldg(p.ehead + i)));
+        if (kTileN == kTile) {
+            for (int i = threadIdx.x; i < p.nq_blk + p.nk_blk; i += kThreads) emax = max(emax, abs(__ldg(p.eblk + i)));
+        } else {
+            for (int i = threadIdx.x; i < p.n_heads; i += kThreads) emax = max(emax, abs(__ldg(p.ehead + i)));
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             q2 = fmaxf(q2, __shfl_xor_sync(0xffffffffu, q2, o));
@@ -855,10 +863,16 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         };
         // general form only: 2^(exponents) of the query head and the key head of this item, 1 unless a head
         // was pre-scaled into fp16 range (ehead: query heads first, then key heads)
-        auto tile_scale = [&](int bh) -> float {
+        auto tile_scale = [&](int bh, int blk, int t) -> float {
             if (FAST || !scaled) return 1.0f;
             const int kv = (bh / p.H) * p.KVH + (bh % p.H) / group;
-            const int e = __ldg(p.ehead + bh) + __ldg(p.ehead + p.B * p.H + kv);
+            int e;
+            if (kTileN == kTile) {  // the streamed tile t is block t of the split
+                const int qb = PASS == 1 ? blk : t, kb = PASS == 1 ? t : blk;
+                e = __ldg(p.eblk + (size_t)bh * p.nb + qb) + __ldg(p.eblk + (size_t)p.B * p.H * p.nb + (size_t)kv * p.nb + kb);
+            } else {
+                e = __ldg(p.ehead + bh) + __ldg(p.ehead + p.B * p.H + kv);
+            }
             return __int_as_float((127 + min(max(e, -126), 127)) << 23);
         };
 
@@ -910,7 +924,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 st_bh = bh;
                 st_blk = blk;
             }
-            const float cs = tile_scale(bh);
+            const float cs = tile_scale(bh, blk, t);
             const bool has_last = PASS == 2 && last_tile == t;
             saw_last = saw_last || has_last;
             const uint32_t lse_t = lse_w + lb * (kTileN * 4u);
@@ -1361,7 +1375,8 @@ static int fused_impl(const float* Q, const long long* q_strides_host, const flo
         a.ml = (float2*)(w8 + wl.ml); a.part_col = (float*)(w8 + wl.pcol); a.rows = (size_t)B * H * S;
         a.bound2 = (float*)(w8 + wl.bound2); a.eblk = (int*)(w8 + wl.eblk); a.ehead = (int*)(w8 + wl.ehead);
         split_f16_kernel<false><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
-        split_f16_kernel<true><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);  // head-uniform exponents; exits at once normally
+        if (kTileN != kTile)  // tiles that straddle blocks need head-uniform exponents; exits at once normally
+            split_f16_kernel<true><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
         SPLITQ_LAUNCH_CHECK("split_f16_kernel");
     }
 
@@ -1373,7 +1388,8 @@ static int fused_impl(const float* Q, const long long* q_strides_host, const flo
     Params p;
     p.B = B; p.H = H; p.KVH = KVH; p.S = S; p.nb = nb;
     p.nq_blk = B * H * nb; p.nk_blk = B * KVH * nb;
-    p.w2 = (float*)(w8 + wl.w2); p.bound2 = (const float*)(w8 + wl.bound2); p.ehead = (const int*)(w8 + wl.ehead);
+    p.w2 = (float*)(w8 + wl.w2); p.bound2 = (const float*)(w8 + wl.bound2);
+    p.eblk = (const int*)(w8 + wl.eblk); p.ehead = (const int*)(w8 + wl.ehead);
     p.n_heads = B * (H + KVH);
     p.nbn = cdiv(S, kTileN);
     p.causal = causal ? 1 : 0;

@@ -471,7 +471,7 @@ class BoundaryPlan:
 
     #: kernels launched by one run(): colsum partial + finalize, select, [memset+class absmax,] pack, dequant
     def launches_per_run(self, fused: bool = False) -> int:
-        n = 6 if fused else (2 if self.method != "last_row" else 1)  # fused: split, exponent fix-up, pass 1, lse merge, pass 2, finalize
+        n = 5 if fused else (2 if self.method != "last_row" else 1)  # fused: split, pass 1, lse merge, pass 2, finalize
         n += 1
         n += 2 if self.scale_mode == N.SCALE_GROUP else 1
         n += 1
