@@ -296,3 +296,41 @@ def test_gpu_pair_eval_equals_single_gpu_eval(tmp_path, batch_combos):
     assert got["n"] == single.n_tokens and got["w"] == single.windows
     assert torch.equal(torch.tensor(got["total"]), torch.tensor(single.total_nll))
     assert os.path.exists(out + "avg_ppl_results_pythia_70m.pkl")
+
+
+@pytest.mark.gpu
+def test_main_run_reads_optional_params_keys(tmp_path):
+    """splitq.main.run with the optional params.json keys of SURVEY section 5: `bits` / `ladder` /
+    `scale_mode` reach the wrapper, `head_weights_file` feeds weighted_importance like the reference's
+    ../../attention_head_weights.pkl, channel methods route to the channel-wise driver, and the output
+    files carry the family's reference names."""
+    from splitq import compat
+    from splitq.main import run
+    L, H = compat.QWEN2_TINY["num_hidden_layers"], compat.QWEN2_TINY["num_attention_heads"]
+    base = {"ratios": [0, 0.5], "layers_of_interest": [1], "methods": ["regular_importance"], "max_length": 128, "stride": 32}
+    n = 128 + 2 * 32
+    # head_dim of the tiny configs is 16: the fused kernel needs 64, so score from materialised attention
+    mat = dict(base, importance_impl="materialised")
+    a = run("qwen", mat, n, "cuda:0", tiny=True)
+    b = run("qwen", dict(mat, bits=8), n, "cuda:0", tiny=True)
+    c = run("qwen", dict(mat, scale_mode="token", ladder=[[0.5, 2], [0.5, 8]]), n, "cuda:0", tiny=True)
+    assert a.total_nll[0][0][0] == b.total_nll[0][0][0] == c.total_nll[0][0][0]          # ratio 0: no quantiser
+    assert len({a.total_nll[0][0][1], b.total_nll[0][0][1], c.total_nll[0][0][1]}) == 3   # ratio 0.5: three quantisers
+    hw = (torch.randn(L, H, generator=torch.Generator().manual_seed(1)) * 0.3 + 0.1).tolist()
+    path = tmp_path / "attention_head_weights.pkl"
+    pickle.dump(hw, open(path, "wb"))
+    w1 = run("qwen", dict(mat, methods=["weighted_importance"], head_weights_file=str(path)), n, "cuda:0", tiny=True)
+    w2 = run("qwen", dict(mat, methods=["weighted_importance"], head_weights=hw), n, "cuda:0", tiny=True)
+    assert w1.total_nll == w2.total_nll
+    with pytest.raises(FileNotFoundError):
+        run("qwen", dict(mat, methods=["weighted_importance"]), n, "cuda:0", tiny=True)
+    out = str(tmp_path) + "/"
+    ch = run("qwen", {"layers_of_interest": [1], "methods": ["channel_8", "channel_1_max"], "max_length": 512,
+                      "stride": 32, "ratios": [0]}, 512 + 32, "cuda:0", tiny=True, out_prefix=out)
+    assert len(ch.total_nll) == 1 and len(ch.total_nll[0]) == 2 and os.path.exists(out + "ppl_channel.pkl")
+    run("pythia", dict(mat, experiment="last_row"), n, "cuda:0", tiny=True, out_prefix=out)
+    assert os.path.exists(out + "avg_ppl_results_pythia_70m.pkl") and os.path.exists(out + "total_nll_pythia_70m.pkl")
+    with pytest.raises(ValueError):
+        run("pythia", dict(mat, experiment="initial"), n, "cuda:0", tiny=True)
+    with pytest.raises(ValueError):
+        run("qwen", dict(mat, pairs=True, split_devices=["cuda:0", "cuda:0"]), n, "cuda:0", tiny=True)
