@@ -22,7 +22,8 @@
  *            u32 payload_bytes, u32 flags (bit 0 = SPLITQ_HDR_DEQUANT_RECIP, else 0)
  *   bits     u8[S]   per-token width: 2, 4, 8 or 32 (= raw fp32 row)
  *   row_off  u32[S]  row start, in 16-byte units from codes_offset
- *   scales   f32[n_scales]  group mode: 4 slots (8-bit, 4-bit, 2-bit, unused); token mode: S
+ *   scales   f32[n_scales]  group mode: 4 slots (8-bit, 4-bit, 2-bit, unused); token mode: S;
+ *            channel modes (scale_mode = SPLITQ_SCALE_CHANNEL_BASE + method): D, one per channel
  *   codes    rows in ascending token order; a b-bit row holds D two's-complement fields,
  *            element e at bit e*b (LSB first), padded to 16 bytes; a raw row is D floats.
  */
@@ -47,6 +48,7 @@ extern "C" {
 #define SPLITQ_HEADER_BYTES 32
 #define SPLITQ_SCALE_GROUP 0 /* one absmax per width class (reference: one per selected set) */
 #define SPLITQ_SCALE_TOKEN 1 /* one absmax per token (extension) */
+#define SPLITQ_SCALE_CHANNEL_BASE 2 /* + SPLITQ_CHANNEL_* : one scale per channel (splitq_channel_quant_pack) */
 /* OR into splitq_quant_pack's scale_mode: the receiver dequantises as (q * fl(1/L)) * m instead of
  * (q / L) * m.  The reference writes `quantized_values / 7 * max_val` (pythia_model.py:186); CPU
  * ATen divides (the default here, bit-identical), CUDA ATen -- the device every reference entry
@@ -222,6 +224,19 @@ int splitq_channel_fake_quant(const float* h, int B, int S, int D, int method, f
  * js_out (L,L,N) fp64, entry [i][j][n] = JS(dist[i][n], dist[j][n]) for i < j (other entries are
  * left untouched).  fp64 arithmetic, fixed reduction order. */
 int splitq_layer_js(const float* dist, int L, int N, int S, double* js_out, splitq_stream_t stream);
+
+/* The same quantisers emitting a payload instead of fake-quantised floats ("shares the
+ * pack format, per-channel scales"): per window, the per-channel statistic (over that window's S rows;
+ * the reference always has one window) goes into the scales section, every token row is packed at 8
+ * (channel_8), 4 (channel_4) or 2 bits (the two ternary methods), header scale_mode =
+ * SPLITQ_SCALE_CHANNEL_BASE + method.  splitq_dequant / splitq_dequant_norm read it back with the
+ * reference's operation order (q * m / L for the absmax widths, q * u for the ternary ones), so
+ * pack -> dequantise equals splitq_channel_fake_quant on one window bit for bit (a channel whose
+ * statistic is 0 dequantises to NaN, as the reference's 0/0 does).  D % 4 == 0.
+ *   ws: scratch of splitq_channel_workspace_bytes(B, S, D). */
+size_t splitq_channel_payload_bytes(int S, int D, int method);
+int splitq_channel_quant_pack(const float* h, int B, int S, int D, int method, uint8_t* payload,
+                              size_t payload_stride, void* ws, size_t ws_bytes, splitq_stream_t stream);
 
 /* ---- transfer --------------------------------------------------------------------------
  * The device hop the reference only simulates (in-place quant->dequant,

@@ -20,6 +20,9 @@ template <bool MEAN>
 __global__ void __launch_bounds__(kCWarps * 32)
 channel_partial_kernel(const float* __restrict__ h, long long R, int D, int rows_per_chunk,
                        float* __restrict__ partial) {
+    // blockIdx.z = window when the statistic is taken per window (R = rows of one window)
+    h += (size_t)blockIdx.z * R * D;
+    partial += (size_t)blockIdx.z * gridDim.y * D;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c0 = blockIdx.x * 128 + lane * 4;
     const long long r0 = (long long)blockIdx.y * rows_per_chunk;
@@ -62,9 +65,11 @@ channel_partial_kernel(const float* __restrict__ h, long long R, int D, int rows
 
 template <bool MEAN>
 __global__ void channel_finalize_kernel(const float* __restrict__ partial, int nparts, int D, long long R,
-                                        float* __restrict__ stats) {
+                                        float* __restrict__ stats, size_t stats_stride_bytes) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= D) return;
+    partial += (size_t)blockIdx.y * nparts * D;                                   // blockIdx.y = window
+    stats = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(stats) + (size_t)blockIdx.y * stats_stride_bytes);
     if (MEAN) {
         double s = 0.0;
         for (int p = 0; p < nparts; ++p) s += (double)partial[(size_t)p * D + c];
@@ -127,6 +132,55 @@ channel_quant_vec_kernel(const float* __restrict__ h, long long R, int D, int me
     }
 }
 
+// ---- payload form: one warp per token packs the channel codes (statistics already in the payload) ----
+__global__ void __launch_bounds__(128)
+channel_pack_kernel(const float* __restrict__ h, int S, int D, int method, uint8_t* __restrict__ payload, size_t stride) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * 4 + warp, b = blockIdx.y;
+    if (t >= S) return;
+    const int mode = SPLITQ_SCALE_CHANNEL_BASE + method, nb = channel_bits(method);
+    const PayloadLayout lay = payload_layout((uint32_t)S, mode, (uint32_t)D);
+    uint8_t* P = payload + (size_t)b * stride;
+    const uint32_t rb = row_bytes((uint32_t)D, (uint32_t)nb);
+    const uint32_t off16 = (uint32_t)t * (rb / 16u);
+    if (t == 0) {
+        if (lane < 8) {
+            const uint32_t w[8] = {SPLITQ_MAGIC, (uint32_t)mode, (uint32_t)S, (uint32_t)D, lay.n_scales, lay.codes_off,
+                                   lay.codes_off + (uint32_t)S * rb, 0u};
+            reinterpret_cast<uint32_t*>(P)[lane] = w[lane];
+        }
+        for (uint32_t i = (uint32_t)S + lane; i < pad16((uint32_t)S); i += 32) P[lay.bits_off + i] = 0;
+        for (uint32_t i = 4u * S + lane; i < pad16(4u * S); i += 32) P[lay.rowoff_off + i] = 0;
+        for (uint32_t i = 4u * D + lane; i < pad16(4u * D); i += 32) P[lay.scales_off + i] = 0;
+    }
+    if (lane == 0) {
+        P[lay.bits_off + t] = (uint8_t)nb;
+        reinterpret_cast<uint32_t*>(P + lay.rowoff_off)[t] = off16;
+    }
+    const float4* src = reinterpret_cast<const float4*>(h + ((size_t)b * S + t) * D);
+    const float4* sc = reinterpret_cast<const float4*>(P + lay.scales_off);
+    uint8_t* dst = P + lay.codes_off + (size_t)off16 * 16u;
+    const uint32_t mask = (1u << nb) - 1u;
+    const int nch = D >> 2;
+    for (int c = lane; (uint32_t)c * (uint32_t)nb / 2u < rb; c += 32) {  // chunks past D pad the row with zeros
+        uint32_t w = 0u;
+        if (c < nch) {
+            const float4 x = ld_stream_f4(src + c);
+            const float4 m = sc[c];  // written by the statistics kernel of this call: a plain load
+            int8_t q0, q1, q2, q3;
+            channel_fake(x.x, m.x, method, &q0);
+            channel_fake(x.y, m.y, method, &q1);
+            channel_fake(x.z, m.z, method, &q2);
+            channel_fake(x.w, m.w, method, &q3);
+            w = ((uint32_t)q0 & mask) | (((uint32_t)q1 & mask) << nb) | (((uint32_t)q2 & mask) << (2 * nb)) |
+                (((uint32_t)q3 & mask) << (3 * nb));
+        }
+        if (nb == 8) reinterpret_cast<uint32_t*>(dst)[c] = w;
+        else if (nb == 4) reinterpret_cast<uint16_t*>(dst)[c] = (uint16_t)w;
+        else dst[c] = (uint8_t)w;
+    }
+}
+
 static int pick_rows(long long R, int D) {
     const long long tiles = cdiv(D, 128);
     int rows = 512;
@@ -141,7 +195,9 @@ using namespace splitq;
 extern "C" size_t splitq_channel_workspace_bytes(int B, int S, int D) {
     if (B <= 0 || S <= 0 || D <= 0) return 0;
     const long long R = (long long)B * S;
-    return (size_t)cdiv(R, pick_rows(R, D)) * D * sizeof(float);
+    const size_t whole = (size_t)cdiv(R, pick_rows(R, D)) * D * sizeof(float);            // statistic over all B*S rows
+    const size_t per_window = (size_t)B * cdiv(S, pick_rows(S, D)) * D * sizeof(float);   // splitq_channel_quant_pack
+    return std::max(whole, per_window);
 }
 
 extern "C" int splitq_channel_fake_quant(const float* h, int B, int S, int D, int method, float* stats_out,
@@ -163,10 +219,10 @@ extern "C" int splitq_channel_fake_quant(const float* h, int B, int S, int D, in
     const bool mean = method == SPLITQ_CHANNEL_1_MEAN;
     if (mean) {
         channel_partial_kernel<true><<<grid, kCWarps * 32, 0, st>>>(h, R, D, rows, (float*)ws);
-        channel_finalize_kernel<true><<<cdiv(D, 256), 256, 0, st>>>((const float*)ws, nparts, D, R, stats_out);
+        channel_finalize_kernel<true><<<cdiv(D, 256), 256, 0, st>>>((const float*)ws, nparts, D, R, stats_out, 0);
     } else {
         channel_partial_kernel<false><<<grid, kCWarps * 32, 0, st>>>(h, R, D, rows, (float*)ws);
-        channel_finalize_kernel<false><<<cdiv(D, 256), 256, 0, st>>>((const float*)ws, nparts, D, R, stats_out);
+        channel_finalize_kernel<false><<<cdiv(D, 256), 256, 0, st>>>((const float*)ws, nparts, D, R, stats_out, 0);
     }
     SPLITQ_LAUNCH_CHECK("channel stats kernels");
     const long long n = R * D;
@@ -182,5 +238,45 @@ extern "C" int splitq_channel_fake_quant(const float* h, int B, int S, int D, in
     const int blocks = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
     channel_quant_kernel<<<blocks, 256, 0, st>>>(h, n, D, method, stats_out, h_out, codes_out);
     SPLITQ_LAUNCH_CHECK("channel_quant_kernel");
+    return SPLITQ_OK;
+}
+
+extern "C" size_t splitq_channel_payload_bytes(int S, int D, int method) {
+    if (S <= 0 || D <= 0 || method < SPLITQ_CHANNEL_8 || method > SPLITQ_CHANNEL_1_MAX) return 0;
+    const PayloadLayout lay = payload_layout((uint32_t)S, SPLITQ_SCALE_CHANNEL_BASE + method, (uint32_t)D);
+    return (size_t)lay.codes_off + (size_t)S * row_bytes((uint32_t)D, (uint32_t)channel_bits(method));
+}
+
+extern "C" int splitq_channel_quant_pack(const float* h, int B, int S, int D, int method, uint8_t* payload,
+                                         size_t payload_stride, void* ws, size_t ws_bytes, splitq_stream_t stream) {
+    SPLITQ_REQUIRE(h && payload, SPLITQ_ERR_ARG, "channel_quant_pack: NULL buffer");
+    SPLITQ_REQUIRE(B > 0 && S > 0 && D > 0 && B <= 65535, SPLITQ_ERR_ARG, "channel_quant_pack: bad shape B=%d S=%d D=%d", B, S, D);
+    SPLITQ_REQUIRE(method >= SPLITQ_CHANNEL_8 && method <= SPLITQ_CHANNEL_1_MAX, SPLITQ_ERR_ARG,
+                   "channel_quant_pack: unknown method %d", method);
+    SPLITQ_REQUIRE(D % 4 == 0 && aligned16(h), SPLITQ_ERR_ALIGN, "channel_quant_pack: D must be a multiple of 4 and h 16-byte aligned");
+    SPLITQ_REQUIRE(aligned16(payload) && payload_stride % 16 == 0, SPLITQ_ERR_ALIGN,
+                   "channel_quant_pack: payload and payload_stride must be 16-byte aligned");
+    const size_t nbytes = splitq_channel_payload_bytes(S, D, method);
+    SPLITQ_REQUIRE(B == 1 || payload_stride >= nbytes, SPLITQ_ERR_WORKSPACE, "channel_quant_pack: payload_stride %zu < %zu",
+                   payload_stride, nbytes);
+    const int rows = pick_rows(S, D), nparts = cdiv(S, rows);
+    const size_t need = (size_t)B * nparts * D * sizeof(float);
+    SPLITQ_REQUIRE(ws && ws_bytes >= need, SPLITQ_ERR_WORKSPACE, "channel_quant_pack: workspace %zu < %zu bytes", ws_bytes, need);
+    SPLITQ_REQUIRE(nparts <= 65535, SPLITQ_ERR_ARG, "channel_quant_pack: too many rows");
+    if (int rc = check_arch()) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const PayloadLayout lay = payload_layout((uint32_t)S, SPLITQ_SCALE_CHANNEL_BASE + method, (uint32_t)D);
+    float* scales0 = reinterpret_cast<float*>(payload + lay.scales_off);  // window 0; the others payload_stride apart
+    dim3 grid(cdiv(D, 128), nparts, B);
+    if (method == SPLITQ_CHANNEL_1_MEAN) {
+        channel_partial_kernel<true><<<grid, kCWarps * 32, 0, st>>>(h, S, D, rows, (float*)ws);
+        channel_finalize_kernel<true><<<dim3(cdiv(D, 256), B), 256, 0, st>>>((const float*)ws, nparts, D, S, scales0, payload_stride);
+    } else {
+        channel_partial_kernel<false><<<grid, kCWarps * 32, 0, st>>>(h, S, D, rows, (float*)ws);
+        channel_finalize_kernel<false><<<dim3(cdiv(D, 256), B), 256, 0, st>>>((const float*)ws, nparts, D, S, scales0, payload_stride);
+    }
+    SPLITQ_LAUNCH_CHECK("channel stats kernels");
+    channel_pack_kernel<<<dim3(cdiv(S, 4), B), 128, 0, st>>>(h, S, D, method, payload, payload_stride);
+    SPLITQ_LAUNCH_CHECK("channel_pack_kernel");
     return SPLITQ_OK;
 }

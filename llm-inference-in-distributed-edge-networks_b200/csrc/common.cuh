@@ -52,15 +52,21 @@ __host__ __device__ inline int slot_of_bits(int bits) { return bits == 8 ? 0 : (
 struct PayloadLayout {
     uint32_t bits_off, rowoff_off, scales_off, codes_off, n_scales;
 };
-__host__ __device__ inline PayloadLayout payload_layout(uint32_t S, int scale_mode) {
+// scale_mode SPLITQ_SCALE_GROUP / _TOKEN, or SPLITQ_SCALE_CHANNEL_BASE + channel method (one scale per
+// channel: D entries; every token has the same width)
+__host__ __device__ inline PayloadLayout payload_layout(uint32_t S, int scale_mode, uint32_t D = 0) {
     PayloadLayout l;
     l.bits_off = SPLITQ_HEADER_BYTES;
     l.rowoff_off = l.bits_off + pad16(S);
     l.scales_off = l.rowoff_off + pad16(4u * S);
-    l.n_scales = scale_mode == SPLITQ_SCALE_GROUP ? 4u : S;
+    l.n_scales = scale_mode == SPLITQ_SCALE_GROUP ? 4u : (scale_mode == SPLITQ_SCALE_TOKEN ? S : D);
     l.codes_off = l.scales_off + pad16(4u * l.n_scales);
     return l;
 }
+__host__ __device__ inline bool is_channel_mode(int scale_mode) {
+    return scale_mode >= SPLITQ_SCALE_CHANNEL_BASE && scale_mode <= SPLITQ_SCALE_CHANNEL_BASE + 3;
+}
+__host__ __device__ inline int channel_bits(int method) { return method == 0 ? 8 : (method == 1 ? 4 : 2); }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }

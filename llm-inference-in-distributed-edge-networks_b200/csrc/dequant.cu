@@ -52,8 +52,20 @@ struct RowInfo {
     int nb;
     float m, L, rL;
     bool nan_row, bad, recip;
+    int channel;              // -1, or the channel method of a per-channel payload (scales: one per channel)
+    const float* ch_scales;
     const uint8_t* src;
 };
+// per-channel payloads (qwen_layer_wise.py:132-134,139-150): q * m / L for the absmax widths (multiply first,
+// then divide -- not the token path's q / L * m), q * u for the ternary methods; a zero statistic is the
+// reference's 0/0
+__device__ __forceinline__ float channel_decode(uint32_t w, int i, int nb, float st, int method) {
+    const int q = (int)(w << (32 - nb * (i + 1))) >> (32 - nb);
+    if (st == 0.f) return __uint_as_float(0x7fc00000u);
+    if (method == SPLITQ_CHANNEL_8) return __fdiv_rn(__fmul_rn((float)q, st), 127.f);
+    if (method == SPLITQ_CHANNEL_4) return __fdiv_rn(__fmul_rn((float)q, st), 7.f);
+    return __fmul_rn((float)q, st);
+}
 
 // `limit` = bytes the caller says one window's payload may span (payload_stride; 0 = unknown).  The
 // payload crosses process and device boundaries, so nothing read from it is trusted: a header that
@@ -71,12 +83,15 @@ __device__ __forceinline__ RowInfo row_info(const uint8_t* P, int S, int D, int 
     const float4 gs = __ldg(reinterpret_cast<const float4*>(P + lt.scales_off));  // group slots (or tokens 0..3)
     const float ts = __ldg(reinterpret_cast<const float*>(P + lt.scales_off) + t);  // token slot (inside the payload in either mode)
     const int mode = (int)h0.y;
+    r.channel = is_channel_mode(mode) ? mode - SPLITQ_SCALE_CHANNEL_BASE : -1;
+    r.ch_scales = reinterpret_cast<const float*>(P + lt.scales_off);
     r.bad = h0.x != SPLITQ_MAGIC || h0.z != (uint32_t)S || h0.w != (uint32_t)D ||
-            (mode != SPLITQ_SCALE_GROUP && mode != SPLITQ_SCALE_TOKEN);
+            (mode != SPLITQ_SCALE_GROUP && mode != SPLITQ_SCALE_TOKEN && r.channel < 0);
     if (!r.bad) {
         const uint32_t nbw = (nb == 2 || nb == 4 || nb == 8 || nb == SPLITQ_BITS_RAW) ? (uint32_t)nb : 8u;
         const unsigned long long end = (unsigned long long)h1.y + 16ull * off16 + row_bytes((uint32_t)D, nbw);
-        r.bad = h1.y != payload_layout((uint32_t)S, mode).codes_off || end > h1.z || (limit != 0 && h1.z > limit);
+        r.bad = h1.y != payload_layout((uint32_t)S, mode, (uint32_t)D).codes_off || end > h1.z || (limit != 0 && h1.z > limit) ||
+                (r.channel >= 0 && nb != channel_bits(r.channel));
     }
     r.nb = nb;
     r.recip = (h1.w & SPLITQ_HDR_DEQUANT_RECIP) != 0u;
@@ -137,13 +152,29 @@ dequant_kernel(const uint8_t* __restrict__ payload, size_t stride, int S, int D,
                 else w[u] = __ldg(r.src + c);
             }
         }
+        if (r.channel >= 0) {
 #pragma unroll
-        for (int u = 0; u < MAXCH; ++u) {
-            v[u].x = decode_field(w[u], 0, r.nb, r.L, r.rL, r.m, r.recip);
-            v[u].y = decode_field(w[u], 1, r.nb, r.L, r.rL, r.m, r.recip);
-            v[u].z = decode_field(w[u], 2, r.nb, r.L, r.rL, r.m, r.recip);
-            v[u].w = decode_field(w[u], 3, r.nb, r.L, r.rL, r.m, r.recip);
-            if (r.nan_row) v[u] = make_float4(qnan, qnan, qnan, qnan);
+            for (int u = 0; u < MAXCH; ++u) {
+                const int c = lane + 32 * u;
+                if (c < nch) {
+                    const float4 st = __ldg(reinterpret_cast<const float4*>(r.ch_scales) + c);
+                    v[u].x = channel_decode(w[u], 0, r.nb, st.x, r.channel);
+                    v[u].y = channel_decode(w[u], 1, r.nb, st.y, r.channel);
+                    v[u].z = channel_decode(w[u], 2, r.nb, st.z, r.channel);
+                    v[u].w = channel_decode(w[u], 3, r.nb, st.w, r.channel);
+                } else {
+                    v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < MAXCH; ++u) {
+                v[u].x = decode_field(w[u], 0, r.nb, r.L, r.rL, r.m, r.recip);
+                v[u].y = decode_field(w[u], 1, r.nb, r.L, r.rL, r.m, r.recip);
+                v[u].z = decode_field(w[u], 2, r.nb, r.L, r.rL, r.m, r.recip);
+                v[u].w = decode_field(w[u], 3, r.nb, r.L, r.rL, r.m, r.recip);
+                if (r.nan_row) v[u] = make_float4(qnan, qnan, qnan, qnan);
+            }
         }
     }
 
@@ -227,6 +258,7 @@ dequant_generic_kernel(const uint8_t* __restrict__ payload, size_t stride, int S
         if (r.nb == SPLITQ_BITS_RAW) return reinterpret_cast<const float*>(r.src)[d];
         const int per = 8 / r.nb;
         const uint32_t byte = r.src[d / per];
+        if (r.channel >= 0) return channel_decode(byte, d % per, r.nb, r.ch_scales[d], r.channel);
         return decode_field(byte, d % per, r.nb, r.L, r.rL, r.m, r.recip);
     };
     if (h_out)

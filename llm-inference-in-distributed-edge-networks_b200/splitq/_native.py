@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("SPLITQ_LIB") or os.path.join(os.path.dirname(_HERE), 
 
 OK = 0
 SCALE_GROUP, SCALE_TOKEN = 0, 1
+SCALE_CHANNEL_BASE = 2  # + CHANNEL_METHODS[name]: per-channel payloads
 BITS_RAW = 32
 NORM_LAYERNORM, NORM_RMSNORM = 0, 1
 FLAG_CAUSAL_HINT = 1
@@ -51,6 +52,8 @@ SIGNATURES = {
     "splitq_channel_workspace_bytes": (_sz, [_i, _i, _i]),
     "splitq_channel_fake_quant": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "splitq_layer_js": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "splitq_channel_payload_bytes": (_sz, [_i, _i, _i]),
+    "splitq_channel_quant_pack": (_i, [_vp, _i, _i, _i, _i, _vp, _sz, _vp, _sz, _vp]),
     "splitq_transfer_peer": (_i, [_vp, _i, _vp, _i, _sz, _vp]),
     "splitq_ipc_export": (_i, [_vp, _vp, C.POINTER(C.c_size_t)]),
     "splitq_ipc_open": (_i, [_vp, _sz, C.POINTER(C.c_void_p)]),

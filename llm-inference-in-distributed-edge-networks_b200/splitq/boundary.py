@@ -317,6 +317,40 @@ def channel_fake_quant(h: torch.Tensor, method: str, out: Optional[torch.Tensor]
     return out, stats, codes
 
 
+def channel_payload_bytes(S: int, D: int, method: str) -> int:
+    if method not in N.CHANNEL_METHODS:
+        raise ValueError(f"Unknown method: {method}")
+    return N.load().splitq_channel_payload_bytes(S, D, N.CHANNEL_METHODS[method])
+
+
+def channel_quant_pack(h: torch.Tensor, method: str, payload: Optional[torch.Tensor] = None,
+                       workspace: Optional[_Workspace] = None) -> torch.Tensor:
+    """The channel-wise quantisers as a real payload (SPQ1, scale mode SCALE_CHANNEL_BASE + method): per
+    window the per-channel statistic and the 8 / 4 / 2-bit codes of every row.  `dequant` / `dequant_norm`
+    read it back; for one window pack -> dequant equals channel_fake_quant bit for bit."""
+    if method not in N.CHANNEL_METHODS:
+        raise ValueError(f"Unknown method: {method}")
+    h = _need_cuda_f32(h, "hidden_states")
+    if h.dim() == 2:
+        h = h.unsqueeze(0)
+    B, S, D = h.shape
+    nbytes = channel_payload_bytes(S, D, method)
+    if nbytes == 0:
+        raise N.SplitqError(f"channel_quant_pack: unsupported shape {tuple(h.shape)}")
+    if payload is None:
+        payload = torch.empty(B, nbytes, dtype=torch.uint8, device=h.device)
+    if not (payload.device == h.device and payload.dtype == torch.uint8 and payload.shape[0] == B
+            and payload.shape[1] >= nbytes and payload.stride(1) == 1 and payload.stride(0) % 16 == 0):
+        raise N.SplitqError(f"channel_quant_pack: payload must be a ({B}, >= {nbytes}) uint8 tensor on {h.device}")
+    lib = N.load()
+    ws_bytes = lib.splitq_channel_workspace_bytes(B, S, D)
+    ws = (workspace or _WS).get(h.device, "channel", ws_bytes)
+    with torch.cuda.device(h.device):
+        N.check(lib.splitq_channel_quant_pack(_ptr(h), B, S, D, N.CHANNEL_METHODS[method], _ptr(payload), payload.stride(0),
+                                              _ptr(ws), ws_bytes, _stream(h)))
+    return payload
+
+
 def transfer(dst: torch.Tensor, src: torch.Tensor, nbytes: Optional[int] = None) -> torch.Tensor:
     """Payload hop between the halves' devices (cudaMemcpyPeerAsync; same device = D2D copy).
     Enqueued on the current stream of the SOURCE device."""

@@ -304,6 +304,69 @@ def row_codes(h_row: torch.Tensor, m: float, bits: int, scale_mode: int) -> np.n
     return q.to(torch.int8).numpy()
 
 
+SCALE_CHANNEL_BASE = 2  # header scale_mode of a per-channel payload = SCALE_CHANNEL_BASE + index in CHANNEL_METHODS
+CHANNEL_METHODS = ("channel_8", "channel_4", "channel_1_mean", "channel_1_max")
+CHANNEL_BITS = {"channel_8": 8, "channel_4": 4, "channel_1_mean": 2, "channel_1_max": 2}
+
+
+def channel_codes_reference(h: torch.Tensor, method: str):
+    """(per-channel statistic (D,), integer codes (S,D) as fp32) of ONE window (S,D): the first halves of the
+    formulas of qwen_layer_wise.py:132,139-141,147-148 (channel_fake_quant_reference is codes -> floats)."""
+    if method in ("channel_8", "channel_4"):
+        L = 127 if method == "channel_8" else 7
+        m = h.abs().amax(dim=0)
+        return m, torch.round(h / m * L)
+    if method == "channel_1_max":
+        m = h.abs().amax(dim=0)
+        return m, torch.clamp(torch.round(h / m), -1, 1)
+    if method == "channel_1_mean":
+        u = torch.stack([torch.mean(h[:, c]) + 1e-8 for c in range(h.shape[1])])
+        return u, torch.clamp(torch.round(h / u), -1, 1)
+    raise ValueError(f"Unknown method: {method}")
+
+
+def pack_payload_channel(h: torch.Tensor, method: str) -> np.ndarray:
+    """One window (S,D) -> per-channel payload: same sections as pack_payload, scales = D statistics, every
+    row at CHANNEL_BITS[method] bits, rows back to back."""
+    S, D = h.shape
+    mode = SCALE_CHANNEL_BASE + CHANNEL_METHODS.index(method)
+    b = CHANNEL_BITS[method]
+    bits_off = HEADER_BYTES
+    rowoff_off = bits_off + pad16(S)
+    scales_off = rowoff_off + pad16(4 * S)
+    codes_off = scales_off + pad16(4 * D)
+    rb = row_bytes(D, b)
+    total = codes_off + S * rb
+    buf = np.zeros(total, dtype=np.uint8)
+    buf[:HEADER_BYTES] = np.frombuffer(struct.pack("<8I", MAGIC, mode, S, D, D, codes_off, total, 0), dtype=np.uint8)
+    buf[bits_off:bits_off + S] = b
+    buf[rowoff_off:rowoff_off + 4 * S] = (np.arange(S, dtype=np.uint32) * (rb // 16)).view(np.uint8)
+    stat, q = channel_codes_reference(h, method)
+    buf[scales_off:scales_off + 4 * D] = stat.numpy().astype(np.float32).view(np.uint8)
+    codes = torch.nan_to_num(q, nan=0.0).to(torch.int8).numpy()
+    for t in range(S):
+        packed = _pack_row(codes[t], b)
+        buf[codes_off + t * rb:codes_off + t * rb + packed.size] = packed
+    return buf
+
+
+def unpack_payload_channel(buf: np.ndarray) -> torch.Tensor:
+    """Dequantise a per-channel payload with the reference's operation order: q * m / L (absmax widths),
+    q * u (ternary); a zero statistic gives NaN like the reference's division by it."""
+    magic, mode, S, D, n_scales, codes_off, total, _ = struct.unpack("<8I", buf[:HEADER_BYTES].tobytes())
+    assert magic == MAGIC and total == buf.size and n_scales == D
+    method = CHANNEL_METHODS[mode - SCALE_CHANNEL_BASE]
+    b = CHANNEL_BITS[method]
+    scales_off = HEADER_BYTES + pad16(S) + pad16(4 * S)
+    stat = torch.from_numpy(buf[scales_off:scales_off + 4 * D].view(np.float32).copy())
+    rb = row_bytes(D, b)
+    q = torch.stack([torch.from_numpy(_unpack_row(buf[codes_off + t * rb:codes_off + t * rb + (D * b + 7) // 8], b, D)
+                                      .astype(np.float32)) for t in range(S)])
+    out = q * stat / (127.0 if method == "channel_8" else 7.0) if method in ("channel_8", "channel_4") else q * stat
+    out[:, stat == 0] = float("nan")
+    return out
+
+
 HDR_DEQUANT_RECIP = 1  # header word 7, bit 0: the receiver dequantises with q * fl(1/L) (CUDA ATen flavour)
 
 

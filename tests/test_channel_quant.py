@@ -103,3 +103,57 @@ def test_wrapper_channel_wise_matches_reference_nll(gold, name, cfg):
         got = w.channel_wise(ids, ids.clone(), book[name]["layer"], method).item()
         assert abs(got - want) / abs(want) <= 1e-3, (method, got, want)
         assert abs(np.expm1(got - want)) <= 1e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("method", ["channel_8", "channel_4", "channel_1_mean", "channel_1_max"])
+def test_channel_payload_pack_and_dequant(method, golden_dir):
+    """The channel quantisers as an SPQ1 payload (per-channel scales section): bytes equal the oracle's
+    packing of the reference formulas, and dequantising the payload equals the fake-quantised floats of
+    splitq_channel_fake_quant (hence the reference fixtures) bit for bit, window by window."""
+    import numpy as np
+    import splitq_oracle as O
+    gen = torch.Generator().manual_seed(7)
+    B, S, D = 3, 130, 96
+    h = torch.randn(B, S, D, generator=gen) * 3
+    h[:, :, 5] *= 40
+    if method != "channel_1_mean":
+        h[1, :, 9] = 0.0     # a dead channel in one window: statistic 0 -> NaN, as the reference's 0/0
+    payload = splitq.channel_quant_pack(h.cuda(), method)
+    assert payload.shape == (B, splitq.channel_payload_bytes(S, D, method))
+    out = splitq.dequant(payload, S, D).cpu()
+    for b in range(B):
+        want_bytes = O.pack_payload_channel(h[b], method)
+        got = payload[b].cpu().numpy()
+        if method == "channel_1_mean":   # the statistic is a mean: GPU and CPU summation orders differ in the last bits
+            so = 32 + O.pad16(S) + O.pad16(4 * S)
+            stat_g = got[so:so + 4 * D].view(np.float32)
+            stat_w = want_bytes[so:so + 4 * D].view(np.float32)
+            assert np.allclose(stat_g, stat_w, rtol=1e-4, atol=1e-6)
+        else:
+            assert np.array_equal(got, want_bytes), (method, b)
+            want = O.unpack_payload_channel(want_bytes)
+            assert np.array_equal(out[b].numpy().view(np.uint32)[~np.isnan(want.numpy())],
+                                  want.numpy().view(np.uint32)[~np.isnan(want.numpy())])
+            assert np.array_equal(np.isnan(out[b].numpy()), np.isnan(want.numpy()))
+        fq, _, _ = splitq.channel_fake_quant(h[b:b + 1].cuda(), method)
+        a, c = out[b].numpy(), fq[0].cpu().numpy()
+        finite = ~np.isnan(c)
+        assert np.array_equal(np.isnan(a), np.isnan(c))
+        nz = finite & (c != 0)   # an integer code has no -0
+        assert np.array_equal(a.view(np.uint32)[nz], c.view(np.uint32)[nz]) and np.array_equal(a[finite], c[finite])
+    # a reference fixture through the payload: qwen_tiny hidden states before / after the reference's own loop
+    g = np.load(os.path.join(golden_dir, "channel_quant.npz"))
+    key = f"qwen_tiny|{method}"
+    pre, post = torch.from_numpy(g[key + "|pre"]), g[key + "|post"]
+    got = splitq.dequant(splitq.channel_quant_pack(pre.cuda().unsqueeze(0), method), pre.shape[0], pre.shape[1])[0].cpu().numpy()
+    if method == "channel_1_mean":  # the scale is a mean (summation order): values agree to its rounding, a few codes may flip
+        assert np.mean(~np.isclose(got, post, rtol=1e-4, atol=1e-9)) < 0.02
+    else:
+        assert np.array_equal(got, post)
+    # fused with the downstream norm, like the token payloads
+    gamma = torch.rand(D).cuda()
+    _, normed, _ = splitq.dequant_norm(payload, S, D, splitq.NORM_RMSNORM, gamma, None, 1e-6, want_resid=True)
+    ok = ~torch.isnan(out).any(dim=2)
+    want_n = O.rms_norm(out[ok], gamma.cpu(), 1e-6)
+    assert torch.allclose(normed.cpu()[ok], want_n, rtol=1e-5, atol=1e-6)

@@ -117,3 +117,16 @@ def test_window_schedule_matches_loop():
     assert sched[-1][1] == 1000
     assert sum(t for _, _, t in sched) == 1000
     assert O.window_schedule(100, 256, 32) == [(0, 100, 100)]
+
+
+@pytest.mark.parametrize("method", ["channel_8", "channel_4", "channel_1_mean", "channel_1_max"])
+def test_channel_payload_roundtrip_equals_reference_channel_wise(method, golden_dir):
+    """Oracle only: packing the channel codes into the payload format and dequantising them reproduces
+    what the reference's channel_wise loop left in the hidden states (captured from its own run)."""
+    g = np.load(os.path.join(golden_dir, "channel_quant.npz"))
+    pre, post = torch.from_numpy(g[f"qwen_tiny|{method}|pre"]), g[f"qwen_tiny|{method}|post"]
+    buf = O.pack_payload_channel(pre, method)
+    assert buf.size == 32 + O.pad16(pre.shape[0]) + O.pad16(4 * pre.shape[0]) + O.pad16(4 * pre.shape[1]) + \
+        pre.shape[0] * O.row_bytes(pre.shape[1], O.CHANNEL_BITS[method])
+    got = O.unpack_payload_channel(buf).numpy()
+    assert np.array_equal(got, post)
