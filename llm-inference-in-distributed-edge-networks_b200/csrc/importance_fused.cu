@@ -32,8 +32,17 @@
 
 #include "common.cuh"
 
+// This file is compiled once per epilogue layout (SPLITQ_K2_EPI_GROUPS = 2 and 3, see the Makefile): each
+// build lives in its own namespace and importance_fused_api.cu picks one per call by the problem's shape.
+#ifndef SPLITQ_K2_EPI_GROUPS
+#define SPLITQ_K2_EPI_GROUPS 2
+#endif
+#define SPLITQ_K2_CAT_(a, b) a##b
+#define SPLITQ_K2_CAT(a, b) SPLITQ_K2_CAT_(a, b)
+#define SPLITQ_K2_NS SPLITQ_K2_CAT(k2_g, SPLITQ_K2_EPI_GROUPS)
+
 namespace splitq {
-namespace k2 {
+namespace SPLITQ_K2_NS {
 
 constexpr int kTile = 128;                           // rows of the fixed operand = M of every MMA = TMEM lanes
 // Columns of one accumulator = rows of one streamed tile = N of every MMA: 128, or (build-time switch) 192 --
@@ -63,9 +72,6 @@ constexpr int kStages = SPLITQ_K2_STAGES;            // streamed tiles in flight
 constexpr bool kASmem = SPLITQ_K2_A_SMEM != 0;
 constexpr int kAcc = kTileN == 192 ? 2 : (kASmem ? 4 : 3);  // TMEM accumulator buffers, used in rotation
 static_assert(!kASmem || kTileN == 128, "the shared-memory fixed operand variant exists for 128-column tiles only");
-#ifndef SPLITQ_K2_EPI_GROUPS
-#define SPLITQ_K2_EPI_GROUPS 2
-#endif
 constexpr int kEpiGroups = SPLITQ_K2_EPI_GROUPS;      // epilogue warpgroups; tile n goes to group n % kEpiGroups
 constexpr int kChunk = kEpiGroups == 2 ? (kTileN == 192 ? 48 : 64) : 32;  // accumulator columns per register buffer (two buffers per thread)
 constexpr int kChunks = kTileN / kChunk;
@@ -1307,20 +1313,15 @@ static WsLayout ws_layout(int B, int H, int KVH, int S) {
     return w;
 }
 
-}  // namespace k2
-}  // namespace splitq
+// ---- this build's entry points (C++ linkage; the exported C symbols are in importance_fused_api.cu) ----
+int tile_cols() { return kTileN; }
 
-using namespace splitq;
-using namespace splitq::k2;
-
-extern "C" int splitq_importance_fused_tile_cols(void) { return kTileN; }
-
-extern "C" size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd) {
+size_t workspace_bytes(int B, int H, int KVH, int S, int hd) {
     if (B <= 0 || H <= 0 || KVH <= 0 || S <= 0 || hd != kHd) return 0;
     return ws_layout(B, H, KVH, S).total;
 }
 
-static int fused_impl(const float* Q, const long long* q_strides_host, const float* K, const long long* k_strides_host,
+int fused_impl(const float* Q, const long long* q_strides_host, const float* K, const long long* k_strides_host,
                       int B, int H, int KVH, int S, int hd, float scaling, int causal, int mode,
                       const float* head_w_host, float* out_col, float* out_last, const float* head_w2_host,
                       float* out_col2, void* ws, size_t ws_bytes, splitq_stream_t stream) {
@@ -1457,20 +1458,5 @@ static int fused_impl(const float* Q, const long long* q_strides_host, const flo
     return SPLITQ_OK;
 }
 
-extern "C" int splitq_importance_fused(const float* Q, const long long* q_strides_host, const float* K,
-                                       const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
-                                       float scaling, int causal, int mode, const float* head_w_host,
-                                       float* out_col, float* out_last, void* ws, size_t ws_bytes,
-                                       splitq_stream_t stream) {
-    return fused_impl(Q, q_strides_host, K, k_strides_host, B, H, KVH, S, hd, scaling, causal, mode, head_w_host, out_col,
-                      out_last, nullptr, nullptr, ws, ws_bytes, stream);
-}
-
-extern "C" int splitq_importance_fused_dual(const float* Q, const long long* q_strides_host, const float* K,
-                                            const long long* k_strides_host, int B, int H, int KVH, int S, int hd,
-                                            float scaling, int causal, int mode, const float* head_w_host,
-                                            float* out_col, float* out_last, const float* head_w2_host,
-                                            float* out_col2, void* ws, size_t ws_bytes, splitq_stream_t stream) {
-    return fused_impl(Q, q_strides_host, K, k_strides_host, B, H, KVH, S, hd, scaling, causal, mode, head_w_host, out_col,
-                      out_last, head_w2_host, out_col2, ws, ws_bytes, stream);
-}
+}  // namespace SPLITQ_K2_NS
+}  // namespace splitq

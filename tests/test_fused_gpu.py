@@ -11,6 +11,17 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
+@pytest.fixture(autouse=True, params=["by shape", "2", "3"], ids=lambda v: f"k2-groups={v}")
+def k2_build(request, monkeypatch):
+    """The library holds two builds of K2 (two / three epilogue warpgroups, csrc/importance_fused_api.cu) and
+    picks one per call by shape; every case of this module also runs pinned to each of them."""
+    if request.param == "by shape":
+        monkeypatch.delenv("SPLITQ_K2_GROUPS", raising=False)
+    else:
+        monkeypatch.setenv("SPLITQ_K2_GROUPS", request.param)
+    return request.param
+
+
 def make_qk(gen, B, H, KVH, S, sigma, hf_layout=False):
     hd = 64
     if hf_layout:  # (B,S,H,hd) storage viewed as (B,H,S,hd), like q_proj(...).view(...).transpose(1, 2)
@@ -254,3 +265,27 @@ def test_fused_bench_shape_against_fp64():
     want_col, want_last = fp64_scores(q, k)
     assert max_rel(col, want_col.float()) <= 1e-5
     assert max_rel(last, want_last.float()) <= 1e-5
+
+
+def test_the_two_builds_agree_to_rounding_and_share_one_workspace_size(monkeypatch):
+    """Same inputs through both builds: different partial-sum orders (2 x groups slots), so equal to fp32
+    rounding, not bitwise; the workspace query covers whichever build a call is handed to."""
+    q, k = make_qk(torch.Generator().manual_seed(21), 2, 4, 2, 1000, 1.0)
+    got = {}
+    for g in ("2", "3"):
+        monkeypatch.setenv("SPLITQ_K2_GROUPS", g)
+        got[g] = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_last=True)
+    assert max_rel(got["2"][0], got["3"][0]) < 2e-6 and max_rel(got["2"][1], got["3"][1]) < 2e-6
+    lib = N.load()
+    need = lib.splitq_importance_fused_workspace_bytes(2, 4, 2, 1000, 64)
+    ws = torch.empty(need, dtype=torch.uint8, device=DEV)
+    col = torch.empty(2, 1000, device=DEV)
+    qd, kd = q.to(DEV), k.to(DEV)
+    import ctypes
+    for g in ("2", "3"):
+        monkeypatch.setenv("SPLITQ_K2_GROUPS", g)
+        qs = (ctypes.c_longlong * 3)(*qd.stride()[:3]); ks = (ctypes.c_longlong * 3)(*kd.stride()[:3])
+        N.check(lib.splitq_importance_fused(qd.data_ptr(), qs, kd.data_ptr(), ks, 2, 4, 2, 1000, 64, 0.125, 1,
+                                            N.FUSED_F16X3, None, col.data_ptr(), None, ws.data_ptr(), need,
+                                            torch.cuda.current_stream().cuda_stream))
+        assert max_rel(col, got[g][0]) == 0.0
