@@ -5,6 +5,6 @@ B, H, KVH, S = 8, 14, 2, 4096
 mode = int(sys.argv[1]) if len(sys.argv) > 1 else 0
 g = torch.Generator(device="cuda").manual_seed(0)
 q = torch.randn(B, H, S, 64, device="cuda", generator=g); k = torch.randn(B, KVH, S, 64, device="cuda", generator=g)
-for _ in range(3):
+for _ in range(int(os.environ.get("K2_ONE_REPS", "3"))):
     splitq.importance_fused(q, k, 0.125, mode=mode)
 torch.cuda.synchronize()

@@ -58,7 +58,7 @@ struct Out {
 
 // ld_warps: 0, 4, 8 or 12 loading warps (warps 4.. of the CTA); ld_cols_per: 32 or 64 columns per wait
 // mma: 0 none, 1 TS N=128, 2 SS N=128, 3 TS N=256, 4 SS N=256, 5 TS N=192, 6 SS N=192, 7 TS N=64
-__global__ void __launch_bounds__(512, 1) probe(int ld_warps, int ld_per, int mma, int iters, Out* out) {
+__global__ void __launch_bounds__(512, 1) probe(int ld_warps, int ld_per, int mma, int iters, int chains, Out* out) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bars[2];
     __shared__ uint32_t tmem_slot;
@@ -86,9 +86,14 @@ __global__ void __launch_bounds__(512, 1) probe(int ld_warps, int ld_per, int mm
             const int n = mma >= 7 ? 64 : (mma >= 5 ? 192 : ((mma >= 3) ? 256 : 128));
             const uint32_t idesc = (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
             const uint64_t bd = umma_desc(base), ad = umma_desc(base + 32 * 1024);
+            uint32_t acc_off = 0;
             const long long t0 = clock64();
             for (int i = 0; i < iters; ++i) {
-                const uint32_t d = tmem + (uint32_t)((i & 1) * (n == 256 ? 0 : 128));
+                // `chains` accumulators in rotation: consecutive MMAs on one accumulator depend on each other
+                // (kept to an add and a select: a runtime modulo here made the issuing thread the limit, 157 clk
+                // per MMA whatever N)
+                const uint32_t d = tmem + acc_off;
+                acc_off = (acc_off + (uint32_t)n >= (uint32_t)(chains * n)) ? 0u : acc_off + (uint32_t)n;
                 if (mma == 1 || mma == 3 || mma == 5 || mma == 7) mma_ts(d, tmem + 384u + (uint32_t)(i & 3) * 8u, bd + (uint64_t)((i & 3) * 2), idesc);
                 else mma_ss(d, ad + (uint64_t)((i & 3) * 2), bd + (uint64_t)((i & 3) * 2), idesc);
             }
@@ -140,18 +145,24 @@ int main() {
         for (int mma = 0; mma <= 7; ++mma) {
             for (int lw : {0, 8}) {
                 for (int per : {32, 64}) {
+                  for (int chains : {1, 2, 3}) {
                     if (lw == 0 && per == 64) continue;
                     if (lw == 0 && mma == 0) continue;
+                    if (mma == 0 && chains > 1) continue;
+                    if (lw != 0 && chains != 2) continue;
+                    const int nn = mma >= 7 ? 64 : (mma >= 5 ? 192 : (mma >= 3 ? 256 : 128));
+                    if (chains * nn > 384) continue;   // accumulators below the A operand's columns
                     *out = Out{0, 0, 0.f};
-                    probe<<<grid, 512, smem>>>(lw, per, mma, iters, out);
+                    probe<<<grid, 512, smem>>>(lw, per, mma, iters, chains, out);
                     cudaError_t e = cudaDeviceSynchronize();
                     if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); return 1; }
                     const double ld_clk = (double)out->ld_clk / iters, mma_clk = (double)out->mma_clk / iters;
                     const int n = mma >= 7 ? 64 : (mma >= 5 ? 192 : (mma >= 3 ? 256 : 128));
-                    printf("grid %3d mma %-9s ld warps %2d x%-2d : ", grid, mma_names[mma], lw, per);
+                    printf("grid %3d mma %-9s chains %d ld warps %2d x%-2d : ", grid, mma_names[mma], chains, lw, per);
                     if (lw) printf("%.1f clk per ld+wait per warp -> %.1f B/clk/SM  ", ld_clk, lw * per * 128.0 / ld_clk);
                     if (mma) printf("%.1f clk per MMA -> %.0f flop/clk/SM", mma_clk, 2.0 * 128 * n * 16 / mma_clk);
                     printf("\n");
+                  }
                 }
             }
         }
