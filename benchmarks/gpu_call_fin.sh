@@ -1,4 +1,5 @@
 mkdir -p gpurun_out
+timeout 1200 python -m pytest tests/test_fused_gpu.py tests/test_hf_hook_gpu.py -q -x -m gpu 2>&1 | tail -2
 for n in old new old new; do
   if [ $n = new ]; then unset SPLITQ_LIB; else export SPLITQ_LIB=$PWD/llm-inference-in-distributed-edge-networks_b200/lib/variants/libsplitq_old.so; fi
   K2_ONE_REPS=8 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/fin_launches_$n.csv python benchmarks/k2_one.py > /dev/null 2>&1

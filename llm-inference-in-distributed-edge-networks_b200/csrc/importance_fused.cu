@@ -1182,23 +1182,36 @@ lse_combine_kernel(const float2* __restrict__ ml, size_t n, float* __restrict__ 
 struct HeadW {
     float w[SPLITQ_MAX_HEADS];
 };
+// 32 columns per CTA, one warp per head chain: warp g sums the heads h = g, g + 8, ... of its 32 columns (the loop
+// over heads is pure load latency -- 2 x groups + 1 loads per head and column -- so eight short chains instead of
+// one long one: 14.9 -> 8.1 us under ncu, with four chains as with eight), then the partial sums meet in shared
+// memory in fixed order
 __global__ void __launch_bounds__(256)
 fused_finalize_kernel(const float* __restrict__ part_col, const float* __restrict__ part_last, size_t rows, int H, int S,
                       HeadW hw, float* __restrict__ out_col, float* __restrict__ out_last, HeadW hw2,
                       float* __restrict__ out_col2) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ float red[3][8][32];
+    const int jj = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + jj;
     const int b = blockIdx.y;
-    if (j >= S) return;
     float c = 0.f, l = 0.f, c2 = 0.f;
-    for (int h = 0; h < H; ++h) {
-        const size_t o = ((size_t)b * H + h) * S + j;
-        float pc = 0.f;
+    if (j < S) {
+        for (int h = g; h < H; h += 8) {
+            const size_t o = ((size_t)b * H + h) * S + j;
+            float pc = 0.f;
 #pragma unroll
-        for (int sl = 0; sl < kSlots; ++sl) pc += part_col[sl * rows + o];  // fixed order: schedule-independent
-        c += hw.w[h] * pc;
-        c2 += hw2.w[h] * pc;   // a second set of head weights over the same per-head sums (weighted_importance)
-        l += hw.w[h] * part_last[o];
+            for (int sl = 0; sl < kSlots; ++sl) pc += part_col[sl * rows + o];  // fixed order: schedule-independent
+            c += hw.w[h] * pc;
+            c2 += hw2.w[h] * pc;   // a second set of head weights over the same per-head sums (weighted_importance)
+            l += hw.w[h] * part_last[o];
+        }
     }
+    red[0][g][jj] = c; red[1][g][jj] = l; red[2][g][jj] = c2;
+    __syncthreads();
+    if (g != 0 || j >= S) return;
+    c = l = c2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { c += red[0][k][jj]; l += red[1][k][jj]; c2 += red[2][k][jj]; }
     if (out_col) out_col[(size_t)b * S + j] = c / (float)S;
     if (out_last) out_last[(size_t)b * S + j] = l;
     if (out_col2) out_col2[(size_t)b * S + j] = c2 / (float)S;
@@ -1450,7 +1463,7 @@ int fused_impl(const float* Q, const long long* q_strides_host, const float* K, 
     }
     HeadW hw;
     for (int h = 0; h < H; ++h) hw.w[h] = head_w_host ? head_w_host[h] : 1.0f / (float)H;
-    dim3 fg(cdiv(S, 256), B);
+    dim3 fg(cdiv(S, 32), B);
     HeadW hw2;
     for (int h = 0; h < H; ++h) hw2.w[h] = (out_col2 && head_w2_host) ? head_w2_host[h] : 0.f;
     fused_finalize_kernel<<<fg, 256, 0, st>>>(p.part_col, p.part_last, rows, H, S, hw, out_col, out_last, hw2, out_col2);
