@@ -16,12 +16,13 @@
 // h0*h0 + h1*h0 + h0*h1 in fp32 -- three kind::f16 products, K = 16 per instruction.  The error is
 // that of the classic 3xTF32 scheme (same mantissa widths; the dropped h1*h1 term is ~2^-22) at 3/4
 // of the tensor time of one tf32 product plus two fp16 corrections, and with half the operand bytes.
-// Valid for |x| < 65504; beyond that fp16 overflows and the scores come out NaN (loudly wrong).
-// SPLITQ_FUSED_F16X1 keeps only h0*h0.  Four warpgroups per CTA: control (warp 0 = TMA producer of
-// the streamed operand, warps 1 and 2 = MMA issuers of alternate tiles), two epilogue groups
-// (alternate tiles, three TMEM accumulators in rotation), and loaders that put the fixed operand
-// of the next work item into tensor memory, so the MMA reads A from TMEM and only B from shared
-// memory.
+// Blocks whose values leave the fp16 range are multiplied by a power of two first (see the operand
+// preparation below).  SPLITQ_FUSED_F16X1 keeps only h0*h0.  Warpgroups per CTA: control (warp 0 = TMA
+// producer of the streamed operand, warps 1 and 2 = MMA issuers of alternate tiles), two or three
+// epilogue groups (alternate tiles, three TMEM accumulators in rotation), and loaders that put the
+// fixed operand of the next work item into tensor memory, so the MMA reads A from TMEM and only B
+// from shared memory.  K is split by a small kernel before pass 1; Q is split by pass 1's own loaders
+// on its way into tensor memory (kFuseQ), which also write the parts out for pass 2 to stream.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <math.h>
@@ -76,9 +77,18 @@ constexpr int kEpiGroups = SPLITQ_K2_EPI_GROUPS;      // epilogue warpgroups; ti
 constexpr int kChunk = kEpiGroups == 2 ? (kTileN == 192 ? 48 : 64) : 32;  // accumulator columns per register buffer (two buffers per thread)
 constexpr int kChunks = kTileN / kChunk;
 static_assert(kChunks % 2 == 0 && kChunks * kChunk == kTileN, "an even number of chunks per tile keeps the two register buffers in step");
+// SPLITQ_K2_FUSE_QSPLIT = 1 (default): pass 1's loader warps read the fp32 queries themselves -- fold the softmax
+// scale, split into fp16 h0 + h1, put the block into tensor memory AND write the parts out for pass 2 to stream
+// -- so the operand-split launch before pass 1 only converts K (an eighth of the bytes at Qwen's 14:2 heads).
+// The per-block facts the split used to provide for the whole launch (norm bound, pre-scale exponent) then
+// exist per item only, and pass 1 picks the bounded-logit (FAST) or the general epilogue body item by item.
+#ifndef SPLITQ_K2_FUSE_QSPLIT
+#define SPLITQ_K2_FUSE_QSPLIT 1
+#endif
+constexpr bool kFuseQ = SPLITQ_K2_FUSE_QSPLIT != 0 && kTileN == kTile && !kASmem;
 constexpr int kEpiRegs = kEpiGroups == 2 ? 200 : 128; // setmaxnreg budgets; they add up to the launch-time pool
-constexpr int kCtlRegs = kEpiGroups == 2 ? 56 : 40;
-constexpr int kLdrRegs = 56;
+constexpr int kCtlRegs = 40;
+constexpr int kLdrRegs = kEpiGroups == 2 ? 72 : 56;
 #ifndef SPLITQ_K2_MMA_WARPS
 #define SPLITQ_K2_MMA_WARPS 2
 #endif
@@ -96,7 +106,11 @@ constexpr uint32_t kASmemOff = kStages * kOperandBytes;              // two fixe
 constexpr uint32_t kBarOff = kASmemOff + (kASmem ? 2 * 2 * kFixPartBytes : 0);
 constexpr uint32_t kLseOff = kBarOff + 512;            // 18 mbarriers + TMEM base slot
 constexpr uint32_t kFlagOff = kLseOff + 4 * kEpiGroups * 2 * kTileN * 4;    // per-query values: per epilogue warp 2 buffers x kTileN floats
-constexpr uint32_t kSmemBytes = kFlagOff + 256;                              // 3 floats per warp: launch-wide facts
+constexpr uint32_t kFactOff = kFlagOff + 256;                                // 3 floats per warp: launch-wide facts
+// kFuseQ: per-item facts from the loaders -- a ring of 8 (largest squared row norm, exponent) pairs for the
+// epilogue, and behind it two sets of 4 per-loader-warp partials (largest row norm, largest |x| bits)
+constexpr int kFactRing = 8;
+constexpr uint32_t kSmemBytes = kFactOff + 8 * kFactRing + 2 * 4 * 8;
 // (the dynamic smem base must be 1024-aligned; checked in the kernel)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -179,6 +193,28 @@ __device__ __forceinline__ void tc_st32(uint32_t taddr, const uint4 (&q)[8]) {
           "r"(q[6].x), "r"(q[6].y), "r"(q[6].z), "r"(q[6].w), "r"(q[7].x), "r"(q[7].y), "r"(q[7].z), "r"(q[7].w)
         : "memory");
 }
+// 256-bit global accesses (sm_100): a lane moves one whole 32-byte sector, so the loaders' row-per-thread
+// pattern does not depend on the L1 to put two 16-byte pieces of a sector together
+__device__ __forceinline__ void ldg256(const float* p, float4& a, float4& b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void stg256(uint4* p, const uint4& a, const uint4& b) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w),
+                 "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+                 : "memory");
+}
+// 16 consecutive columns of this thread's TMEM lane <- registers
+__device__ __forceinline__ void tc_st16(uint32_t taddr, const uint4 (&q)[4]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+        ::"r"(taddr),
+          "r"(q[0].x), "r"(q[0].y), "r"(q[0].z), "r"(q[0].w), "r"(q[1].x), "r"(q[1].y), "r"(q[1].z), "r"(q[1].w),
+          "r"(q[2].x), "r"(q[2].y), "r"(q[2].z), "r"(q[2].w), "r"(q[3].x), "r"(q[3].y), "r"(q[3].z), "r"(q[3].w)
+        : "memory");
+}
 // one lane of a converged warp; the surrounding code stays warp-uniform so that descriptors and
 // addresses live in uniform registers (a divergent `if (lane == 0)` costs ~6 R2UR moves per MMA)
 __device__ __forceinline__ bool elect_one() {
@@ -243,6 +279,15 @@ struct Params {
     float* part_last;  // (B,H,S) p[S-1][j]
     const uint4 *q16, *k16;  // dense (n,S,64) fp16 h0 part; the h1 part follows at +q_part / +k_part uint4
     size_t q_part, k_part;
+    // kFuseQ, pass 1: the fp32 queries as the caller holds them (element strides of batch, head, row; head_dim
+    // contiguous), scaling * log2(e), and writable views of what the loaders produce for pass 2
+    const float* qsrc;
+    long long qs0, qs1, qs2;
+    int qvec;             // rows may be read as float4 (1) or as 32-byte pieces (2)
+    float cs;
+    uint4* q16_w;
+    float* bound2_w;
+    int* eblk_w;
 };
 
 // ---- schedule, shared by all warp roles --------------------------------------------------------
@@ -262,6 +307,7 @@ struct Seg {
 template <int PASS>
 struct SegIter {
     int bh, blk, t, rem, nb, nbn, S, per_bh;
+    int item;   // items entered so far on this CTA's range (0 for the first): index of the loaders' per-item facts
     bool causal;
     // streamed tiles [t0, t1) of item blk.  pass 1: fixed = query block blk, streamed = key tiles up to
     // its last query; pass 2: fixed = key block blk, streamed = query tiles from its first key on.
@@ -270,12 +316,14 @@ struct SegIter {
         return PASS == 1 ? (causal ? (min((b + 1) * kTile, S) + kTileN - 1) / kTileN : nbn) : nbn;
     }
     __device__ __forceinline__ void next_item() {
+        ++item;
         if (++blk == nb) { blk = 0; ++bh; }
     }
     // position on the n-th tile (n >= 0) of this CTA's range
     __device__ __forceinline__ void init(const Params& p, int n) {
         nb = p.nb; nbn = p.nbn; S = p.S; per_bh = p.per_bh;
         causal = p.causal != 0;
+        item = 0;   // counted from the range's first item: callers that need it start with n = 0
         const long long T = p.tiles;
         const int lo = (int)(T * blockIdx.x / gridDim.x), hi = (int)(T * (blockIdx.x + 1) / gridDim.x);
         rem = hi - lo - n;
@@ -597,16 +645,20 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     // launch-wide facts from the operand split (every CTA reduces the small per-block arrays itself):
     // the largest squared row norms of Q' = Q * scaling * log2(e) and of K bound every logit of the
     // launch by Cauchy-Schwarz; any non-zero block exponent means some block was pre-scaled
+    // (kFuseQ, pass 1: the Q blocks' facts do not exist yet -- the loaders produce them item by item -- so only
+    // the K blocks are reduced here)
+    constexpr bool kItemFacts = kFuseQ && PASS == 1;
     {
         float q2 = 0.f, k2 = 0.f;
         int emax = 0;
-        for (int i = threadIdx.x; i < p.nq_blk + p.nk_blk; i += kThreads) {
+        const int i0 = kItemFacts ? p.nq_blk : 0;
+        for (int i = i0 + threadIdx.x; i < p.nq_blk + p.nk_blk; i += kThreads) {
             const float b2 = __ldg(p.bound2 + i);
             if (i < p.nq_blk) q2 = fmaxf(q2, b2 == b2 ? b2 : INFINITY);
             else k2 = fmaxf(k2, b2 == b2 ? b2 : INFINITY);
         }
         if (kTileN == kTile) {
-            for (int i = threadIdx.x; i < p.nq_blk + p.nk_blk; i += kThreads) emax = max(emax, abs(__ldg(p.eblk + i)));
+            for (int i = i0 + threadIdx.x; i < p.nq_blk + p.nk_blk; i += kThreads) emax = max(emax, abs(__ldg(p.eblk + i)));
         } else {
             for (int i = threadIdx.x; i < p.n_heads; i += kThreads) emax = max(emax, abs(__ldg(p.ehead + i)));
         }
@@ -626,6 +678,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     bool fast, scaled;
+    float k2_all;   // largest squared key row norm of the launch
     {
         float q2 = 0.f, k2 = 0.f;
         int emax = 0;
@@ -637,6 +690,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         // the norm caps keep the absolute fp16 floor of one operand (2^-25 per element) times the other
         // operand's norm far below the 1e-6 a logit may be off by
         fast = !scaled && q2 < 16384.f && k2 < 16384.f && q2 * k2 < kFastBound * kFastBound && !(DBG && (p.dbg & 32));
+        k2_all = k2;
     }
 
     const CUtensorMap* str_map = PASS == 1 ? &mapK : &mapQ;  // streamed operand, h0 and h1 parts in dim 3
@@ -782,7 +836,124 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         SegIter<PASS> si;
         si.init(p, 0);
         Seg it;
-        for (int k = 0; !kASmem && si.next(it); ++k) {   // kASmem: the producer's TMA does this job
+        if (kItemFacts) {
+            // pass 1 with the fused operand split: this thread's row comes in as fp32, half a row (32 floats) at
+            // a time; scaled, split into h0 = fp16(x), h1 = fp16(x - h0) exactly as split_f16_kernel does, stored
+            // to tensor memory (16 columns per half row and part) and written out for pass 2's TMA.  The block's
+            // largest squared row norm and largest |x| meet across the four warps in shared memory; a block
+            // whose values leave the fp16 range (exponent e != 0, rare) is converted a second time with 2^-e.
+            float2* ring = reinterpret_cast<float2*>(gen + kFactOff);
+            float2* part = ring + kFactRing;
+            float4 v[8];
+            for (int k = 0; si.next(it); ++k) {
+                const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
+                const int g = it.blk * kTile + row;
+                const bool live = g < p.S && !(DBG && (p.dbg & 16));
+                const float* src = p.qsrc + (it.bh / p.H) * p.qs0 + (it.bh % p.H) * p.qs1 + (long long)(live ? g : 0) * p.qs2;
+                uint4* dst = p.q16_w + ((size_t)it.bh * p.S + (live ? g : 0)) * (kHd * 2 / 16);
+                const uint32_t a0 = tmem_base + kTmemA + ab * kTmemABuf + lane_addr;
+                auto load_half = [&](int half) {
+                    if (live && p.qvec == 2) {
+#pragma unroll
+                        for (int i = 0; i < 8; i += 2) ldg256(src + half * 32 + i * 4, v[i], v[i + 1]);
+                        return;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float* s4 = src + half * 32 + i * 4;
+                        if (!live) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        else if (p.qvec) v[i] = __ldg(reinterpret_cast<const float4*>(s4));
+                        else v[i] = make_float4(__ldg(s4), __ldg(s4 + 1), __ldg(s4 + 2), __ldg(s4 + 3));
+                    }
+                };
+                float ss = 0.f;
+                uint32_t amax = 0u;
+                auto convert_half = [&](int half, float sc, bool stats) {
+                    uint4 h0[4], h1[4];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float4 x = v[i];
+                        x.x *= p.cs; x.y *= p.cs; x.z *= p.cs; x.w *= p.cs;
+                        if (stats) {
+                            amax = max(amax, __float_as_uint(x.x) & 0x7fffffffu);
+                            amax = max(amax, __float_as_uint(x.y) & 0x7fffffffu);
+                            amax = max(amax, __float_as_uint(x.z) & 0x7fffffffu);
+                            amax = max(amax, __float_as_uint(x.w) & 0x7fffffffu);
+                            ss += fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, x.w * x.w)));
+                        }
+                        const float x0 = x.x * sc, x1 = x.y * sc, x2 = x.z * sc, x3 = x.w * sc;
+                        const __half2 a01 = __floats2half2_rn(x0, x1), a23 = __floats2half2_rn(x2, x3);
+                        const float2 f01 = __half22float2(a01), f23 = __half22float2(a23);
+                        const __half2 l01 = __floats2half2_rn(x0 - f01.x, x1 - f01.y);
+                        const __half2 l23 = __floats2half2_rn(x2 - f23.x, x3 - f23.y);
+                        const uint32_t a01u = *reinterpret_cast<const uint32_t*>(&a01), a23u = *reinterpret_cast<const uint32_t*>(&a23);
+                        const uint32_t l01u = *reinterpret_cast<const uint32_t*>(&l01), l23u = *reinterpret_cast<const uint32_t*>(&l23);
+                        if (i & 1) { h0[i >> 1].z = a01u; h0[i >> 1].w = a23u; h1[i >> 1].z = l01u; h1[i >> 1].w = l23u; }
+                        else { h0[i >> 1].x = a01u; h0[i >> 1].y = a23u; h1[i >> 1].x = l01u; h1[i >> 1].y = l23u; }
+                    }
+                    tc_st16(a0 + 16u * half, h0);
+                    if (p.x3) tc_st16(a0 + 32u + 16u * half, h1);
+                    if (live) {
+#pragma unroll
+                        for (int i = 0; i < 4; i += 2) {
+                            stg256(dst + 4 * half + i, h0[i], h0[i + 1]);
+                            if (p.x3) stg256(dst + p.q_part + 4 * half + i, h1[i], h1[i + 1]);
+                        }
+                    }
+                };
+                load_half(0);                                   // on its way before the buffer is free
+                {   // the next item's row: into the L2 now, so that both of its half-row loads are short ones
+                    SegIter<PASS> peek = si;
+                    Seg nxt;
+                    if (peek.next(nxt)) {
+                        const int gn = nxt.blk * kTile + row;
+                        if (gn < p.S && !(DBG && (p.dbg & 16))) {
+                            const float* pn = p.qsrc + (nxt.bh / p.H) * p.qs0 + (nxt.bh % p.H) * p.qs1 + (long long)gn * p.qs2;
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(pn));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(pn + 32));
+                        }
+                    }
+                }
+                mbar_wait_t<false>(bar_aempty + 8 * ab, abphase ^ 1);
+                tc_fence_after();
+                convert_half(0, 1.0f, true);
+                load_half(1);
+                convert_half(1, 1.0f, true);
+                // block facts: four warp partials, combined by every thread after a 128-thread barrier
+                float rmax = ss == ss ? ss : INFINITY;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) rmax = fmaxf(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+                amax = __reduce_max_sync(0xffffffffu, amax);
+                float2* mine = part + 4 * ab;
+                if (lane == 0) mine[q4] = make_float2(rmax, __uint_as_float(amax));
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const float2 f = mine[w];
+                    rmax = fmaxf(rmax, f.x);
+                    amax = max(amax, __float_as_uint(f.y));
+                }
+                const int ex = (int)(amax >> 23) - 127;
+                const int e = (ex >= 15 || (ex < -10 && amax != 0u)) ? ex - 14 : 0;
+                if (e != 0) {
+                    const float sc = __int_as_float((127 - min(max(e, -126), 126)) << 23);
+                    load_half(0);
+                    convert_half(0, sc, false);
+                    load_half(1);
+                    convert_half(1, sc, false);
+                }
+                if (q4 == 0 && lane == 0) {
+                    ring[k & (kFactRing - 1)] = make_float2(rmax, __int_as_float(e));
+                    p.bound2_w[(size_t)it.bh * p.nb + it.blk] = rmax;   // pass 2 reduces these over the launch
+                    p.eblk_w[(size_t)it.bh * p.nb + it.blk] = e;
+                }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_afull + 8 * ab);
+            }
+        }
+        for (int k = 0; !kItemFacts && !kASmem && si.next(it); ++k) {   // kASmem: the producer's TMA does this job
             const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
             const int b = it.bh / p.H, h = it.bh % p.H;
             const int fix_idx = PASS == 1 ? it.bh : b * p.KVH + h / group;
@@ -816,8 +987,13 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         // of them for itself) are on their way from L2.  When the sequence moves to another item the
         // per-row partial results are stored to this (piece, group) slot.  The loop exists twice:
         // FAST (bounded logits, see pass1_fast) and the general form; the choice is launch-wide.
-        auto epilogue = [&](auto fast_tag) {
-        constexpr bool FAST = decltype(fast_tag)::value;
+        // (kFuseQ, pass 1: a third form, MODE 2, takes the choice item by item from the loaders' facts.)
+        auto epilogue = [&](auto mode_tag) {
+        constexpr int MODE = decltype(mode_tag)::value;   // 0 general, 1 FAST, 2 per item (pass 1 only)
+        constexpr bool FAST = MODE == 1;                  // launch-wide FAST: all of pass 2's uses
+        bool item_fast = false;                           // MODE 2: the current item's choice ...
+        int item_e = 0;                                   // ... and its query block's exponent
+        auto fast_now = [&]() { return MODE == 2 ? item_fast : FAST; };
         const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
         const int grp = wg - 1;                     // this group takes tiles grp, grp + kEpiGroups, ...
         const int row = q4 * 32 + lane;
@@ -851,7 +1027,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const int first_part = nx.t != nx.t0(nx.blk);  // the range starts inside an item
         nx.advance(grp);
         int st_bh = -1, st_blk = 0;                 // item whose partial results are in registers
-        float m = FAST ? 0.f : -INFINITY, l = 0.f;  // pass 1
+        float m = FAST ? 0.f : -INFINITY, l = 0.f;  // pass 1 (MODE 2: set when the first item is entered)
         float colsum = 0.f, lastp = 0.f;            // pass 2
         bool saw_last = false;
 
@@ -870,10 +1046,12 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         // general form only: 2^(exponents) of the query head and the key head of this item, 1 unless a head
         // was pre-scaled into fp16 range (ehead: query heads first, then key heads)
         auto tile_scale = [&](int bh, int blk, int t) -> float {
-            if (FAST || !scaled) return 1.0f;
+            if (fast_now() || !(scaled || (MODE == 2 && item_e != 0))) return 1.0f;
             const int kv = (bh / p.H) * p.KVH + (bh % p.H) / group;
             int e;
-            if (kTileN == kTile) {  // the streamed tile t is block t of the split
+            if (MODE == 2) {        // the query block's exponent came with the item, the key blocks' are final
+                e = item_e + (scaled ? __ldg(p.eblk + (size_t)p.B * p.H * p.nb + (size_t)kv * p.nb + t) : 0);
+            } else if (kTileN == kTile) {  // the streamed tile t is block t of the split
                 const int qb = PASS == 1 ? blk : t, kb = PASS == 1 ? t : blk;
                 e = __ldg(p.eblk + (size_t)bh * p.nb + qb) + __ldg(p.eblk + (size_t)p.B * p.H * p.nb + (size_t)kv * p.nb + kb);
             } else {
@@ -910,7 +1088,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
         while (have) {
             // ---- the tile being processed: (bh, blk, t), where nx stands before it moves on
-            const int bh = nx.bh, blk = nx.blk, t = nx.t;
+            const int bh = nx.bh, blk = nx.blk, t = nx.t, item = nx.item;
             const uint32_t a = acc_i;
             const uint32_t cur_tmem = tmem_lane + a * kTileN;
             // ---- look one tile ahead: is its accumulator ready (asked early, the answer takes ~100
@@ -926,7 +1104,16 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             // ---- entering a new item: store what the registers hold
             if (bh != st_bh || blk != st_blk) {
                 flush();
-                m = FAST ? 0.f : -INFINITY; l = 0.f; colsum = 0.f; lastp = 0.f; saw_last = false;
+                if (MODE == 2) {
+                    // the loaders' facts of this item (written before the block went to the MMAs whose result
+                    // this warp has just waited for): FAST iff nothing was pre-scaled and Cauchy-Schwarz bounds
+                    // every logit of the item, with the same norm caps as the launch-wide test
+                    const float2 f = reinterpret_cast<const float2*>(gen + kFactOff)[item & (kFactRing - 1)];
+                    item_e = __float_as_int(f.y);
+                    item_fast = !scaled && item_e == 0 && f.x < 16384.f && k2_all < 16384.f &&
+                                f.x * k2_all < kFastBound * kFastBound && !(DBG && (p.dbg & 32));
+                }
+                m = fast_now() ? 0.f : -INFINITY; l = 0.f; colsum = 0.f; lastp = 0.f; saw_last = false;
                 st_bh = bh;
                 st_blk = blk;
             }
@@ -947,69 +1134,88 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             const bool diag = rel + q4 * 32 + 31 > 0; // pass 2: some (key, query) of this warp's part is masked
             float lastv = 0.f;
             if (has_last && !(dbg & 4)) tc_ld1_issue(cur_tmem + (uint32_t)last_col, lastv);  // lands with the next wait
-#pragma unroll
-            for (int c = 0; c < kChunks; ++c) {
-                float (&cur)[kChunk] = (c & 1) ? vb : va;
-                float (&oth)[kChunk] = (c & 1) ? va : vb;
-                if (c + 1 < kChunks) {                // next chunk of this tile in flight ...
-                    if (!(dbg & 4)) tc_ld_issue<kChunk>(cur_tmem + (c + 1) * kChunk, oth);
-                } else if (has_next) {                // ... or the next tile's first chunk, if its MMAs are done
-                    if (PASS == 2) stage_qv(lb ^ 1u, lse_nx);
-                    if (!ready) ready = mbar_test(bar_tfull + 8 * na, nph);
-                    ready = __all_sync(0xffffffffu, ready);
-                    if (ready) {
-                        tc_fence_after();
-                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTileN, oth);
+            // one tile's chunks, once per epilogue body: the choice between the FAST and the general body is made
+            // here, outside the chunk loop, so that each copy is as tight as a loop that only knows one of them
+            auto run_tile = [&](auto fast_c) {
+                constexpr bool FASTC = decltype(fast_c)::value;
+    #pragma unroll
+                for (int c = 0; c < kChunks; ++c) {
+                    float (&cur)[kChunk] = (c & 1) ? vb : va;
+                    float (&oth)[kChunk] = (c & 1) ? va : vb;
+                    if (c + 1 < kChunks) {                // next chunk of this tile in flight ...
+                        if (!(dbg & 4)) tc_ld_issue<kChunk>(cur_tmem + (c + 1) * kChunk, oth);
+                    } else if (has_next) {                // ... or the next tile's first chunk, if its MMAs are done
+                        if (PASS == 2) stage_qv(lb ^ 1u, lse_nx);
+                        if (!ready) ready = mbar_test(bar_tfull + 8 * na, nph);
+                        ready = __all_sync(0xffffffffu, ready);
+                        if (ready) {
+                            tc_fence_after();
+                            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTileN, oth);
+                        }
                     }
-                }
-                if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
-                else if (PASS == 1) {
-                    if (FAST) {
-                        if (edge1) pass1_fast<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, l);
-                        else pass1_fast<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, l);
+                    if (dbg & 1) { colsum += cur[0] + cur[kChunk - 1]; l += cur[1]; }
+                    else if (PASS == 1) {
+                        if (FASTC) {
+                            if (edge1) pass1_fast<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, l);
+                            else pass1_fast<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, l);
+                        } else {
+                            if (edge1) pass1_body<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                            else pass1_body<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                        }
                     } else {
-                        if (edge1) pass1_body<kChunk, true>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
-                        else pass1_body<kChunk, false>(cur, c * kChunk, jmax, jlo, jhi, cs, m, l);
+                        if (FASTC) {
+                            if (diag) pass2_fast<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, colsum);
+                            else pass2_fast<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, colsum);
+                        } else {
+                            if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, cs, colsum);
+                            else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, cs, colsum);
+                        }
                     }
-                } else {
-                    if (FAST) {
-                        if (diag) pass2_fast<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, colsum);
-                        else pass2_fast<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, colsum);
-                    } else {
-                        if (diag) pass2_body<kChunk, true>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, cs, colsum);
-                        else pass2_body<kChunk, false>(cur, lse_t + c * (kChunk * 4u), c * kChunk, rel + row, rel + q4 * 32, cs, colsum);
+                    if (c + 1 < kChunks) {
+                        tc_ld_wait();
+                        if (c == 0 && has_last) {         // p[S-1][key]: the last query is never masked
+                            const float qv = lds32(lse_t + 4u * (uint32_t)last_col);
+                            lastp = FASTC ? ex2(lastv) * qv : ex2(fmaf(lastv, cs, -qv));
+                        }
+                        if (c + 2 == kChunks) {           // the last chunk is in registers: accumulator drained
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
+                        }
+                    } else if (has_next) {
+                        if (!ready) {
+                            mbar_wait_t<DBG>(bar_tfull + 8 * na, nph);
+                            tc_fence_after();
+                            if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTileN, oth);
+                        }
+                        tc_ld_wait();                     // next tile's first chunk landed
+                        __syncwarp();                     // the per-query values staged by the other lanes are visible
+                        lb ^= 1u;
+                        acc_i = na;
+                        acc_ph = nph;
                     }
                 }
-                if (c + 1 < kChunks) {
-                    tc_ld_wait();
-                    if (c == 0 && has_last) {         // p[S-1][key]: the last query is never masked
-                        const float qv = lds32(lse_t + 4u * (uint32_t)last_col);
-                        lastp = FAST ? ex2(lastv) * qv : ex2(fmaf(lastv, cs, -qv));
-                    }
-                    if (c + 2 == kChunks) {           // the last chunk is in registers: accumulator drained
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(bar_tempty + 8 * a);
-                    }
-                } else if (has_next) {
-                    if (!ready) {
-                        mbar_wait_t<DBG>(bar_tfull + 8 * na, nph);
-                        tc_fence_after();
-                        if (!(dbg & 4)) tc_ld_issue<kChunk>(tmem_lane + na * kTileN, oth);
-                    }
-                    tc_ld_wait();                     // next tile's first chunk landed
-                    __syncwarp();                     // the per-query values staged by the other lanes are visible
-                    lb ^= 1u;
-                    acc_i = na;
-                    acc_ph = nph;
-                }
+            };
+            if (MODE == 2) {
+                if (item_fast) run_tile(std::true_type{});
+                else run_tile(std::false_type{});
+            } else {
+                run_tile(std::integral_constant<bool, FAST>{});
             }
             have = has_next;
         }
         flush();
         };
-        if (fast) epilogue(std::true_type{});
-        else epilogue(std::false_type{});
+        if constexpr (kItemFacts) {
+#ifdef SPLITQ_K2_FORCE_FAST1   // timing experiment: the launch-wide FAST loop on top of the fused split (valid for tame inputs only)
+            epilogue(std::integral_constant<int, 1>{});
+#else
+            epilogue(std::integral_constant<int, 2>{});
+#endif
+        } else {
+            if (fast) epilogue(std::integral_constant<int, 1>{});
+            else epilogue(std::integral_constant<int, 0>{});
+        }
     }
 
     tc_fence_before();
@@ -1023,7 +1229,10 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
 // ---- operand preparation: fp32 -> fp16 h0 = fp16(x) and h1 = fp16(x - h0), gathered from arbitrary
 // (b,h,s) strides into dense (n, S, 64) fp16 arrays (one 128-byte row per token).  One CTA = one
 // 128-row block of one head of Q (blockIdx.y < BH) or of K.  Q is multiplied by scaling * log2(e)
-// first, so the tensor-core products are log2-domain logits.  Per block the kernel also records
+// first, so the tensor-core products are log2-domain logits.  With kFuseQ (the default) the Q blocks are
+// converted by pass 1's loader warps instead -- same arithmetic, same facts, written to the same arrays --
+// and their CTAs here only preset the result slots: this launch then moves 67 MB instead of 300 MB at the
+// bench shape (52 -> 12 us).  Per block the kernel (or the loader) also records
 //   bound2: the largest squared row norm (of the values as they enter the products' true magnitude),
 //           from which the passes bound every logit of the launch (FAST epilogue), and
 //   eblk:   e such that the block was multiplied by 2^-e before the fp16 conversion: operands beyond
@@ -1044,6 +1253,7 @@ struct SplitArgs {
     float* bound2;            // (BH + BKV) * nb: largest squared row norm per block
     int* eblk;                // (BH + BKV) * nb: exponent each block would like for itself
     int* ehead;               // (BH + BKV): exponent every block of the head ends up with
+    int fuse_q;               // kFuseQ: pass 1 converts the Q blocks itself; their CTAs here only preset the result slots
 };
 // exponent all blocks of one head share: a tile of the passes spans more than one 128-row block of the
 // streamed operand, so the power of two must be uniform along a head.  If any block is beyond the fp16
@@ -1069,6 +1279,18 @@ split_f16_kernel(const SplitArgs a) {
         e_forced = head_exponent(a.eblk + (size_t)y * a.nb, a.nb);
         if (blockIdx.x == 0 && threadIdx.x == 0) a.ehead[y] = e_forced;
         if (e_forced == __ldg(a.eblk + (size_t)y * a.nb + blockIdx.x)) return;  // block-uniform
+    }
+    if (!FIXUP && isq && a.fuse_q) {   // one thread per row and array: (max, sum) slots, column-sum slots
+        const int r = blockIdx.x * kTile + (threadIdx.x & (kTile - 1));
+        if (r < a.S) {
+            const size_t rr = (size_t)bh * a.S + r;
+#pragma unroll
+            for (int sl = 0; sl < kSlots; ++sl) {
+                if (threadIdx.x < kTile) a.ml[sl * a.rows + rr] = make_float2(-INFINITY, 0.f);
+                else a.part_col[sl * a.rows + rr] = 0.f;
+            }
+        }
+        return;
     }
     const int b = bh / heads, h = bh - b * heads;
     const long long* st = isq ? a.qs : a.ks;
@@ -1388,6 +1610,7 @@ int fused_impl(const float* Q, const long long* q_strides_host, const float* K, 
         a.q0 = (uint2*)(w8 + wl.q0); a.q1 = (uint2*)(w8 + wl.q1); a.k0 = (uint2*)(w8 + wl.k0); a.k1 = (uint2*)(w8 + wl.k1);
         a.ml = (float2*)(w8 + wl.ml); a.part_col = (float*)(w8 + wl.pcol); a.rows = (size_t)B * H * S;
         a.bound2 = (float*)(w8 + wl.bound2); a.eblk = (int*)(w8 + wl.eblk); a.ehead = (int*)(w8 + wl.ehead);
+        a.fuse_q = kFuseQ ? 1 : 0;
         split_f16_kernel<false><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
         if (kTileN != kTile)  // tiles that straddle blocks need head-uniform exponents; exits at once normally
             split_f16_kernel<true><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
@@ -1415,6 +1638,11 @@ int fused_impl(const float* Q, const long long* q_strides_host, const float* K, 
     p.part_last = (float*)(w8 + wl.plast);
     p.q16 = (const uint4*)(w8 + wl.q0); p.k16 = (const uint4*)(w8 + wl.k0);
     p.q_part = (wl.q1 - wl.q0) / 16; p.k_part = (wl.k1 - wl.k0) / 16;
+    p.qsrc = Q; p.qs0 = q_strides_host[0]; p.qs1 = q_strides_host[1]; p.qs2 = q_strides_host[2];
+    p.qvec = aligned16(Q) && p.qs0 % 4 == 0 && p.qs1 % 4 == 0 && p.qs2 % 4 == 0;
+    if (p.qvec && (reinterpret_cast<uintptr_t>(Q) & 31u) == 0 && p.qs0 % 8 == 0 && p.qs1 % 8 == 0 && p.qs2 % 8 == 0) p.qvec = 2;
+    p.cs = scaling * 1.4426950408889634f;
+    p.q16_w = (uint4*)(w8 + wl.q0); p.bound2_w = (float*)(w8 + wl.bound2); p.eblk_w = (int*)(w8 + wl.eblk);
 
     // one-time per-device set-up; the entry point is re-entrant (any thread, any stream), so the
     // bookkeeping is under a lock -- the attribute calls themselves are idempotent

@@ -289,3 +289,41 @@ def test_the_two_builds_agree_to_rounding_and_share_one_workspace_size(monkeypat
                                             N.FUSED_F16X3, None, col.data_ptr(), None, ws.data_ptr(), need,
                                             torch.cuda.current_stream().cuda_stream))
         assert max_rel(col, got[g][0]) == 0.0
+
+
+@pytest.mark.parametrize("causal", [True, False])
+def test_fused_mixed_items_some_bounded_some_not(causal):
+    """Pass 1 converts the queries itself and picks its epilogue body per 128-row query block from that
+    block's own norm and exponent: one launch here holds ordinary blocks (bounded-logit body), a block
+    with rows of large norm (general body, online maximum), a block beyond the fp16 range (pre-scaled and
+    converted a second time) and a block of tiny values (scaled up), next to each other and in one head."""
+    B, H, KVH, S = 2, 4, 2, 1024
+    gen = torch.Generator(device=DEV).manual_seed(77)
+    q = torch.randn(B, H, S, 64, device=DEV, generator=gen)
+    k = torch.randn(B, KVH, S, 64, device=DEV, generator=gen)
+    q[0, 0, 3 * 128:4 * 128] *= 12.0          # |q'| ~ 17 x 8: beyond the product cap with |k| ~ 8
+    q[0, 1, 5 * 128 + 7, 11] = 9.0e4          # beyond fp16 once scaled: this block gets an exponent
+    q[1, 2, 2 * 128:3 * 128] *= 1.0e-6        # far below the fp16 normal range: scaled up
+    q[1, 3, 6 * 128:7 * 128] *= 12.0
+    want_col, want_last = fp64_scores(q, k, causal=causal)
+    col, last = splitq.importance_fused(q, k, 0.125, causal=causal, want_last=True)
+    assert torch.isfinite(col).all()
+    assert max_rel(col, want_col.float()) <= 2e-5
+    assert max_rel(last, want_last.float()) <= 2e-5
+
+
+@pytest.mark.parametrize("offset", [0, 4, 1])
+def test_fused_query_alignments(offset):
+    """The loaders read the caller's fp32 queries in 32-byte pieces, as float4 or scalar by scalar,
+    whichever the base pointer and the strides allow; same values, same result bits."""
+    B, H, KVH, S = 1, 4, 2, 640
+    gen = torch.Generator(device=DEV).manual_seed(5)
+    q = torch.randn(B, H, S, 64, device=DEV, generator=gen)
+    k = torch.randn(B, KVH, S, 64, device=DEV, generator=gen)
+    ref_col, ref_last = splitq.importance_fused(q, k, 0.125, want_last=True)
+    store = torch.empty(q.numel() + 8, device=DEV)
+    q_off = store[offset:offset + q.numel()].view_as(q)
+    q_off.copy_(q)
+    assert q_off.data_ptr() % 32 == (offset * 4) % 32
+    col, last = splitq.importance_fused(q_off, k, 0.125, want_last=True)
+    assert torch.equal(col, ref_col) and torch.equal(last, ref_last)
