@@ -86,6 +86,11 @@ static_assert(kChunks % 2 == 0 && kChunks * kChunk == kTileN, "an even number of
 #define SPLITQ_K2_FUSE_QSPLIT 1
 #endif
 constexpr bool kFuseQ = SPLITQ_K2_FUSE_QSPLIT != 0 && kTileN == kTile && !kASmem;
+// Result slots nobody fills (a group without a tile in a short run, the second piece of an item that is not cut)
+// must still hold the neutral element when the merge kernels read all of them.  The loader warps see every run
+// of their CTA and know which slots the epilogue will write, so they store the neutral element into the others;
+// only the build whose loaders idle (kASmem) leaves that to the split kernel.
+constexpr bool kLoaderPresets = !kASmem;
 constexpr int kEpiRegs = kEpiGroups == 2 ? 200 : 128; // setmaxnreg budgets; they add up to the launch-time pool
 constexpr int kCtlRegs = 40;
 constexpr int kLdrRegs = kEpiGroups == 2 ? 72 : 56;
@@ -836,6 +841,34 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         SegIter<PASS> si;
         si.init(p, 0);
         Seg it;
+        // neutral elements for the slots of this run's rows that no epilogue group will write (kLoaderPresets):
+        // the epilogue fills (piece, g) for every group g that owns a tile of the run -- tile n of the CTA's
+        // range belongs to group n % groups -- and, if the run is not a whole item, the CTA holding the other
+        // piece looks after that piece's slots
+        int n_before = 0;   // tiles of this CTA's range before the current run
+        auto preset_unwritten = [&](const Seg& r) {
+            const int len = r.tb - r.ta;
+            const int piece = r.ta != si.t0(r.blk) ? 1 : 0;
+            const bool whole = piece == 0 && r.tb == si.t1(r.blk);
+            const int g0 = n_before % kEpiGroups;
+            n_before += len;
+            const int gr = r.blk * kTile + row;
+            if (!kLoaderPresets || gr >= p.S) return;
+            const size_t rows = (size_t)p.B * p.H * p.S, o = (size_t)r.bh * p.S + gr;
+#pragma unroll
+            for (int pc = 0; pc < 2; ++pc) {
+#pragma unroll
+                for (int gq = 0; gq < kEpiGroups; ++gq) {
+                    const int rel_g = gq - g0 + (gq < g0 ? kEpiGroups : 0);   // position of group gq in this run's rotation
+                    const bool filled = pc == piece && rel_g < len;
+                    const bool ours = pc == piece || whole;
+                    if (ours && !filled) {
+                        if (PASS == 1) p.ml[(pc * kEpiGroups + gq) * rows + o] = make_float2(-INFINITY, 0.f);
+                        else p.part_col[(pc * kEpiGroups + gq) * rows + o] = 0.f;
+                    }
+                }
+            }
+        };
         if (kItemFacts) {
             // pass 1 with the fused operand split: this thread's row comes in as fp32, half a row (32 floats) at
             // a time; scaled, split into h0 = fp16(x), h1 = fp16(x - h0) exactly as split_f16_kernel does, stored
@@ -849,6 +882,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
                 const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
                 const int g = it.blk * kTile + row;
                 const bool live = g < p.S && !(DBG && (p.dbg & 16));
+                preset_unwritten(it);
                 const float* src = p.qsrc + (it.bh / p.H) * p.qs0 + (it.bh % p.H) * p.qs1 + (long long)(live ? g : 0) * p.qs2;
                 uint4* dst = p.q16_w + ((size_t)it.bh * p.S + (live ? g : 0)) * (kHd * 2 / 16);
                 const uint32_t a0 = tmem_base + kTmemA + ab * kTmemABuf + lane_addr;
@@ -955,6 +989,7 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         }
         for (int k = 0; !kItemFacts && !kASmem && si.next(it); ++k) {   // kASmem: the producer's TMA does this job
             const uint32_t ab = k & 1, abphase = (k >> 1) & 1;
+            preset_unwritten(it);
             const int b = it.bh / p.H, h = it.bh % p.H;
             const int fix_idx = PASS == 1 ? it.bh : b * p.KVH + h / group;
             const int g = it.blk * kTile + row;
@@ -1253,7 +1288,8 @@ struct SplitArgs {
     float* bound2;            // (BH + BKV) * nb: largest squared row norm per block
     int* eblk;                // (BH + BKV) * nb: exponent each block would like for itself
     int* ehead;               // (BH + BKV): exponent every block of the head ends up with
-    int fuse_q;               // kFuseQ: pass 1 converts the Q blocks itself; their CTAs here only preset the result slots
+    int fuse_q;               // kFuseQ: pass 1 converts the Q blocks itself
+    int y0;                   // first (b,head) row of the launch: B*H when only the K blocks are launched
 };
 // exponent all blocks of one head share: a tile of the passes spans more than one 128-row block of the
 // streamed operand, so the power of two must be uniform along a head.  If any block is beyond the fp16
@@ -1270,7 +1306,7 @@ template <bool FIXUP>
 __global__ void __launch_bounds__(256)
 split_f16_kernel(const SplitArgs a) {
     __shared__ float s_red[2][8];
-    const int y = blockIdx.y;
+    const int y = blockIdx.y + a.y0;
     const bool isq = y < a.BH;
     const int bh = isq ? y : y - a.BH;
     const int heads = isq ? a.H : a.KVH;
@@ -1280,18 +1316,7 @@ split_f16_kernel(const SplitArgs a) {
         if (blockIdx.x == 0 && threadIdx.x == 0) a.ehead[y] = e_forced;
         if (e_forced == __ldg(a.eblk + (size_t)y * a.nb + blockIdx.x)) return;  // block-uniform
     }
-    if (!FIXUP && isq && a.fuse_q) {   // one thread per row and array: (max, sum) slots, column-sum slots
-        const int r = blockIdx.x * kTile + (threadIdx.x & (kTile - 1));
-        if (r < a.S) {
-            const size_t rr = (size_t)bh * a.S + r;
-#pragma unroll
-            for (int sl = 0; sl < kSlots; ++sl) {
-                if (threadIdx.x < kTile) a.ml[sl * a.rows + rr] = make_float2(-INFINITY, 0.f);
-                else a.part_col[sl * a.rows + rr] = 0.f;
-            }
-        }
-        return;
-    }
+    if (!FIXUP && isq && a.fuse_q) return;   // (not launched at all in the default build, see y0)
     const int b = bh / heads, h = bh - b * heads;
     const long long* st = isq ? a.qs : a.ks;
     const float* src0 = (isq ? a.q : a.k) + b * st[0] + h * st[1];
@@ -1367,7 +1392,7 @@ split_f16_kernel(const SplitArgs a) {
             const __half2 l23 = __floats2half2_rn(x2 - f23.x, x3 - f23.y);
             o0[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a01), *reinterpret_cast<const uint32_t*>(&a23));
             o1[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&l01), *reinterpret_cast<const uint32_t*>(&l23));
-            if (!FIXUP && isq && (i & 15) == 0) {  // the Q blocks also preset the result slots of their (b,h,s) rows
+            if (!kLoaderPresets && !FIXUP && isq && (i & 15) == 0) {  // the Q blocks also preset the result slots of their (b,h,s) rows
                 const size_t rr = (size_t)bh * a.S + r;
 #pragma unroll
                 for (int sl = 0; sl < kSlots; ++sl) {
@@ -1611,7 +1636,9 @@ int fused_impl(const float* Q, const long long* q_strides_host, const float* K, 
         a.ml = (float2*)(w8 + wl.ml); a.part_col = (float*)(w8 + wl.pcol); a.rows = (size_t)B * H * S;
         a.bound2 = (float*)(w8 + wl.bound2); a.eblk = (int*)(w8 + wl.eblk); a.ehead = (int*)(w8 + wl.ehead);
         a.fuse_q = kFuseQ ? 1 : 0;
-        split_f16_kernel<false><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
+        a.y0 = (kFuseQ && kLoaderPresets) ? B * H : 0;   // nothing left to do for the Q blocks' CTAs
+        split_f16_kernel<false><<<dim3(nb, B * (H + KVH) - a.y0), 256, 0, st>>>(a);
+        a.y0 = 0;
         if (kTileN != kTile)  // tiles that straddle blocks need head-uniform exponents; exits at once normally
             split_f16_kernel<true><<<dim3(nb, B * (H + KVH)), 256, 0, st>>>(a);
         SPLITQ_LAUNCH_CHECK("split_f16_kernel");

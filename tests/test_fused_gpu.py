@@ -327,3 +327,27 @@ def test_fused_query_alignments(offset):
     assert q_off.data_ptr() % 32 == (offset * 4) % 32
     col, last = splitq.importance_fused(q_off, k, 0.125, want_last=True)
     assert torch.equal(col, ref_col) and torch.equal(last, ref_last)
+
+
+@pytest.mark.parametrize("B,H,KVH,S,causal", [(1, 2, 1, 1, True), (3, 2, 2, 100, True), (2, 4, 2, 300, False),
+                                              (1, 6, 3, 1100, True), (5, 6, 2, 1536, True), (40, 4, 4, 130, True)])
+def test_fused_fills_every_result_slot_it_reads(B, H, KVH, S, causal):
+    """The merge kernels read 2 x groups partial-result slots per row; slots that no epilogue group
+    fills (short runs, items that are not cut) get their neutral element from the loader warps of the
+    CTA that owns the run.  A workspace full of NaN bit patterns must therefore give the same bits as
+    a workspace that was used before."""
+    import ctypes
+    gen = torch.Generator(device=DEV).manual_seed(B * 1000 + S)
+    q = torch.randn(B, H, S, 64, device=DEV, generator=gen)
+    k = torch.randn(B, KVH, S, 64, device=DEV, generator=gen)
+    ref_col, ref_last = splitq.importance_fused(q, k, 0.125, causal=causal, want_last=True)
+    lib = N.load()
+    need = lib.splitq_importance_fused_workspace_bytes(B, H, KVH, S, 64)
+    qs = (ctypes.c_longlong * 3)(*q.stride()[:3]); ks = (ctypes.c_longlong * 3)(*k.stride()[:3])
+    for fill in (0xFF, 0x7F):
+        ws = torch.full((need,), fill, dtype=torch.uint8, device=DEV)
+        col = torch.empty(B, S, device=DEV); last = torch.empty(B, S, device=DEV)
+        N.check(lib.splitq_importance_fused(q.data_ptr(), qs, k.data_ptr(), ks, B, H, KVH, S, 64, 0.125, int(causal),
+                                            N.FUSED_F16X3, None, col.data_ptr(), last.data_ptr(), ws.data_ptr(), need,
+                                            torch.cuda.current_stream().cuda_stream))
+        assert torch.equal(col, ref_col) and torch.equal(last, ref_last)
