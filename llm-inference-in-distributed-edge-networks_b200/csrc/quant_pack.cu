@@ -18,7 +18,8 @@ namespace splitq {
 
 // 4 warps per CTA and (for rows of up to 1024 floats) a register cap that lets 10 CTAs share an SM: 40
 // independent row-warps per SM instead of 32 was worth 15 % at the bench shape (37.2 -> 31.5 us; 8 warps x
-// 5 CTAs 32.2, 16 x 2 33.3), the kernel lives on bytes in flight and has no barrier to amortise.
+// 5 CTAs 32.2, 16 x 2 33.3), the kernel lives on bytes in flight and has no barrier to amortise.  What it
+// lived on even more was its instruction footprint: see pack4_exact (31.5 -> 23.1 us).
 constexpr int kQWarps = 4;
 constexpr int qp_min_blocks(int maxch) { return maxch <= 8 ? 10 : (maxch == 16 ? 5 : 2); }
 
@@ -31,26 +32,48 @@ __device__ __forceinline__ int code_of(float x, float m, float L, float lo) {
     return (int)rintf(s);  // round half to even, like torch.round
 }
 
-// Same result as code_of() for every input, at a fraction of the instruction count: the IEEE
-// division is replaced by a multiplication with rcp = 1/m, which can differ from the exact
-// sequence by at most ~3e-7 * |s| <= 4e-5 in s; whenever s is farther than 2^-13 from a rounding
-// boundary (k + 1/2) that cannot change the rounded code, otherwise (about 1 element in 4000, and
-// always for NaN/Inf) the exact sequence decides.  Codes therefore stay bit-identical to ATen.
-__device__ __forceinline__ int code_fast(float x, float m, float rcp, float L, float lo) {
-    const float s = __fmul_rn(__fmul_rn(x, rcp), L);
-    const float r = rintf(s);
-    if (fabsf(fabsf(s - r) - 0.5f) > 1.220703125e-4f)  // false for NaN
-        return (int)fminf(fmaxf(r, lo), L);
-    return code_of(x, m, L, lo);
+// Four codes of one float4, packed, for a width known at compile time.  Same result as code_of() for every
+// input at a fraction of the instruction count (with one code at a time through rintf / F2I the kernel was
+// issue-bound: 64 % of the issue slots, 37 % of the conversion pipe, 48 % of DRAM).  The IEEE division is
+// replaced by a multiplication with rcp = 1/m, which can differ from the exact sequence by at most
+// ~3e-7 * |s| <= 4e-5 in s.  Rounding is the 1.5 * 2^23 trick:
+// t = s + 12582912 rounds s to the nearest integer, ties to even, like rintf, and leaves the two's-complement
+// code in t's low mantissa bits -- no FRND, no F2I, no clamp (|x| <= m bounds |s| by L, so the approximate s
+// cannot round past L either).  The four distances d = s - round(s) decide together whether the reciprocal
+// could have changed a rounding (some |d| within 2e-4 of 1/2, or NaN anywhere): then, about once in 600
+// chunks, all four codes come from the exact sequence.
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
 }
-
-__device__ __forceinline__ uint32_t pack4(float4 v, float m, float rcp, float L, float lo, int nb) {
+__device__ __forceinline__ uint32_t bfi(uint32_t field, uint32_t into, int pos, int len) {
+    uint32_t r;
+    asm("bfi.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(field), "r"(into), "r"(pos), "r"(len));
+    return r;
+}
+// the exact sequence for one chunk, out of line: it runs about once in 600 chunks, and inlined into every chunk of
+// every width it made the row loop ~80 KB of code -- the warps of an SM, each in another width's copy, then stalled
+// on instruction fetch more than on anything else (ncu: "no instructions" the top stall reason)
+__device__ __noinline__ uint32_t pack4_exact(float4 v, float m, float L, float lo, int nb) {
     const uint32_t mask = (1u << nb) - 1u;
-    const uint32_t q0 = (uint32_t)code_fast(v.x, m, rcp, L, lo) & mask;
-    const uint32_t q1 = (uint32_t)code_fast(v.y, m, rcp, L, lo) & mask;
-    const uint32_t q2 = (uint32_t)code_fast(v.z, m, rcp, L, lo) & mask;
-    const uint32_t q3 = (uint32_t)code_fast(v.w, m, rcp, L, lo) & mask;
-    return q0 | (q1 << nb) | (q2 << (2 * nb)) | (q3 << (3 * nb));
+    return ((uint32_t)code_of(v.x, m, L, lo) & mask) | (((uint32_t)code_of(v.y, m, L, lo) & mask) << nb) |
+           (((uint32_t)code_of(v.z, m, L, lo) & mask) << (2 * nb)) | (((uint32_t)code_of(v.w, m, L, lo) & mask) << (3 * nb));
+}
+template <int NB>
+__device__ __forceinline__ uint32_t pack4_w(float4 v, float m, float rcp, float L, float lo) {
+    constexpr float kMagic = 12582912.f;
+    const float s0 = __fmul_rn(__fmul_rn(v.x, rcp), L), s1 = __fmul_rn(__fmul_rn(v.y, rcp), L);
+    const float s2 = __fmul_rn(__fmul_rn(v.z, rcp), L), s3 = __fmul_rn(__fmul_rn(v.w, rcp), L);
+    const float t0 = __fadd_rn(s0, kMagic), t1 = __fadd_rn(s1, kMagic), t2 = __fadd_rn(s2, kMagic), t3 = __fadd_rn(s3, kMagic);
+    const float d0 = __fsub_rn(s0, __fsub_rn(t0, kMagic)), d1 = __fsub_rn(s1, __fsub_rn(t1, kMagic));
+    const float d2 = __fsub_rn(s2, __fsub_rn(t2, kMagic)), d3 = __fsub_rn(s3, __fsub_rn(t3, kMagic));
+    const float worst = max_nan(max_nan(__fmul_rn(d0, d0), __fmul_rn(d1, d1)), max_nan(__fmul_rn(d2, d2), __fmul_rn(d3, d3)));
+    // |d| > 0.4998 somewhere (the bound that matters is 0.5 - 1.2e-4), or NaN / Inf
+    if (!(worst <= 0.2498f)) return pack4_exact(v, m, L, lo, NB);
+    const uint32_t q0 = __float_as_uint(t0), q1 = __float_as_uint(t1), q2 = __float_as_uint(t2), q3 = __float_as_uint(t3);
+    if (NB == 8) return __byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+    return bfi(q3, bfi(q2, bfi(q1, q0 & ((1u << NB) - 1u), NB, NB), 2 * NB, NB), 3 * NB, NB);
 }
 
 // Window index written by the warp that owns token 0: header words (all but the total size, which
@@ -117,33 +140,14 @@ class_absmax_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __
     if (threadIdx.x < 3 && smax[threadIdx.x] != 0u) atomicMax(&class_max[b * 4 + threadIdx.x], smax[threadIdx.x]);
 }
 
-// ---- main kernel: one warp per token, row resident in registers -------------------------------
+// ---- one token row, resident in registers as MAXCH float4 per lane (chunk c = lane + 32 u) -> payload ----
 template <int MAXCH, bool GROUP>
-__global__ void __launch_bounds__(kQWarps * 32, qp_min_blocks(MAXCH))
-quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
-                  const uint32_t* __restrict__ row_off, uint8_t* __restrict__ payload, size_t stride,
-                  const uint32_t* __restrict__ class_max, uint32_t hdr_flags) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t = blockIdx.x * kQWarps + warp;
-    const int b = blockIdx.y;
-    if (t >= S) return;
-    const size_t tok = (size_t)b * S + t;
-    const PayloadLayout lay = payload_layout((uint32_t)S, GROUP ? SPLITQ_SCALE_GROUP : SPLITQ_SCALE_TOKEN);
-    uint8_t* P = payload + (size_t)b * stride;
-    const int nb = bits[tok];
-    const uint32_t off16 = row_off[tok];
+__device__ __forceinline__ void emit_row(const float4 (&v)[MAXCH], uint8_t* __restrict__ P, const PayloadLayout& lay, int t,
+                                         int S, int D, int nb, uint32_t off16, int lane,
+                                         const uint32_t* __restrict__ class_max_w, uint32_t hdr_flags) {
     const int nch = D >> 2;
-
-    const float4* src = reinterpret_cast<const float4*>(h + tok * D);
-    float4 v[MAXCH];
-#pragma unroll
-    for (int u = 0; u < MAXCH; ++u) {
-        const int c = lane + 32 * u;
-        v[u] = c < nch ? ld_stream_f4(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-
     float* scales = reinterpret_cast<float*>(P + lay.scales_off);
-    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max + b * 4, lane, hdr_flags);
+    if (t == 0) write_window_index<GROUP>(P, S, D, lay, class_max_w, lane, hdr_flags);
     if (lane == 0) {
         P[lay.bits_off + t] = (uint8_t)nb;
         reinterpret_cast<uint32_t*>(P + lay.rowoff_off)[t] = off16;
@@ -164,7 +168,7 @@ quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __re
 
     float m;
     if (GROUP) {
-        m = __uint_as_float(class_max[b * 4 + slot_of_bits(nb)]);
+        m = __uint_as_float(class_max_w[slot_of_bits(nb)]);
     } else {
         uint32_t mx = 0u;
 #pragma unroll
@@ -182,19 +186,50 @@ quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __re
     const float rcp = __fdiv_rn(1.0f, m);
     const uint32_t rb = row_bytes((uint32_t)D, (uint32_t)nb);
     // chunk c (4 elements) occupies nb/2 bytes at byte c*nb/2; chunks past D pad the row with zeros
+    if (nb == 8) {           // one copy of the loop per width: shifts, masks and the store width are constants
 #pragma unroll
-    for (int u = 0; u < MAXCH; ++u) {
-        const int c = lane + 32 * u;
-        const uint32_t byte = (uint32_t)c * (uint32_t)nb >> 1;
-        if (byte < rb) {
-            const uint32_t w = pack4(v[u], m, rcp, L, lo, nb);
-            if (nb == 8) reinterpret_cast<uint32_t*>(dst)[c] = w;
-            else if (nb == 4) reinterpret_cast<uint16_t*>(dst)[c] = (uint16_t)w;
-            else dst[c] = (uint8_t)w;
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            if ((uint32_t)c * 4u < rb) reinterpret_cast<uint32_t*>(dst)[c] = pack4_w<8>(v[u], m, rcp, L, lo);
+        }
+    } else if (nb == 4) {
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            if ((uint32_t)c * 2u < rb) reinterpret_cast<uint16_t*>(dst)[c] = (uint16_t)pack4_w<4>(v[u], m, rcp, L, lo);
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < MAXCH; ++u) {
+            const int c = lane + 32 * u;
+            if ((uint32_t)c < rb) dst[c] = (uint8_t)pack4_w<2>(v[u], m, rcp, L, lo);
         }
     }
     // rows wider than the register tile never reach here (dispatch guarantees nch <= 32*MAXCH);
     // padding beyond 32*MAXCH chunks cannot exist because rb <= pad16(nch*nb/2) < (nch+32)*nb/2
+}
+
+// ---- main kernel: one warp per token, row resident in registers -------------------------------
+template <int MAXCH, bool GROUP>
+__global__ void __launch_bounds__(kQWarps * 32, qp_min_blocks(MAXCH))
+quant_pack_kernel(const float* __restrict__ h, int S, int D, const uint8_t* __restrict__ bits,
+                  const uint32_t* __restrict__ row_off, uint8_t* __restrict__ payload, size_t stride,
+                  const uint32_t* __restrict__ class_max, uint32_t hdr_flags) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * kQWarps + warp;
+    const int b = blockIdx.y;
+    if (t >= S) return;
+    const size_t tok = (size_t)b * S + t;
+    const PayloadLayout lay = payload_layout((uint32_t)S, GROUP ? SPLITQ_SCALE_GROUP : SPLITQ_SCALE_TOKEN);
+    const int nch = D >> 2;
+    const float4* src = reinterpret_cast<const float4*>(h + tok * D);
+    float4 v[MAXCH];
+#pragma unroll
+    for (int u = 0; u < MAXCH; ++u) {
+        const int c = lane + 32 * u;
+        v[u] = c < nch ? ld_stream_f4(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    emit_row<MAXCH, GROUP>(v, payload + (size_t)b * stride, lay, t, S, D, bits[tok], row_off[tok], lane, class_max + b * 4, hdr_flags);
 }
 
 // ---- generic path: any D / unaligned rows; one warp per token, scalar accesses ----------------
