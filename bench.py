@@ -617,7 +617,7 @@ def main() -> None:
                 "frac_of_sustained_peak": achieved / peak_mix, "frac_of_burst_peak": achieved / burst,
                 "which_peak_applies": "sustained: the kernel runs back to back inside the step loop and the SM clock sits "
                                       "near 1.65 GHz under sw_power_cap while it does (ncu: cycles / duration)",
-                "traffic": (captured_traffic("r2_h_ncu_full_k2_summary.csv", "fused_importance_kernel")
+                "traffic": (captured_traffic("r2_i_ncu_full_k2_summary.csv", "fused_importance_kernel")
                             if args.workload == DEFAULT_WORKLOAD and B == cfg["B_fused"] and x3 else None),
                 "traffic_note": "DRAM bytes of the two tensor-core passes (ncu); operands are re-read from L2, not HBM",
                 "peak_source": (f"MEASURED_PEAKS.json {bf16_key}" if peaks else "fallback 1590 (B200_PROFILING.md)") +
