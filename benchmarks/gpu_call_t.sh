@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout 1800 python -m pytest tests -x -q -m gpu > gpurun_out/full_tests.log 2>&1; tail -60 gpurun_out/full_tests.log
+timeout 600 python benchmarks/k2_margin.py 2>&1 | tail -8
+timeout 600 python -m pytest tests/test_fused_gpu.py -q -x -m gpu -k general_epilogue_forced 2>&1 | tail -3

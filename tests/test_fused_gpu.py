@@ -144,12 +144,14 @@ def test_fused_general_epilogue_forced(B, H, KVH, S, sigma):
     the oracle and, to rounding, with the bounded path."""
     gen = torch.Generator().manual_seed(S + H)
     q, k = make_qk(gen, B, H, KVH, S, sigma)
-    want_col, want_last = oracle_scores(q, k, True)
+    # against fp64 attention: at sigma = 2 the fp32 CPU oracle is itself 2-4e-6 away from it, by an amount that
+    # depends on the host's BLAS threading, which made a 1e-5 bar against that oracle pass on some boxes only
+    want_col, want_last = fp64_scores(q.to(DEV), k.to(DEV))
     col_g, last_g = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_last=True, mode=N.FUSED_F16X3 | GENERAL_PATH)
     col_f, last_f = splitq.importance_fused(q.to(DEV), k.to(DEV), 0.125, want_last=True)
     for got_c, got_l in ((col_g, last_g), (col_f, last_f)):
-        assert max_rel(got_c.cpu(), want_col) <= 1e-5
-        assert max_rel(got_l.cpu(), want_last) <= 1e-5
+        assert max_rel(got_c, want_col.float()) <= 1e-5
+        assert max_rel(got_l, want_last.float()) <= 1e-5
     assert max_rel(col_g, col_f) <= 2e-6
 
 
