@@ -99,7 +99,10 @@ int splitq_importance_colmean(const float* A, int B, int H, int Sq, int Sk, cons
  *   SPLITQ_FUSED_F16X1 (h0*h0 only, 11-bit mantissas).  Any finite magnitude works: a 128-row block
  *   whose largest |x| leaves [2^-10, 2^15) is multiplied by a power of two before the fp16 conversion
  *   and the factor is restored per tile; non-finite inputs give non-finite scores.
- *   ws: 256-byte aligned scratch of splitq_importance_fused_workspace_bytes(). */
+ *   Q must stay unchanged until the call's kernels retire: the first pass reads it in place.
+ *   Two builds of the kernels exist (two / three epilogue warpgroups); each call picks one by shape.
+ *   Scores are bit-reproducible for a given build; SPLITQ_K2_GROUPS=2|3 in the environment pins one.
+ *   ws: 256-byte aligned scratch of splitq_importance_fused_workspace_bytes() (covers both builds). */
 #define SPLITQ_FUSED_F16X3 0
 #define SPLITQ_FUSED_F16X1 1
 size_t splitq_importance_fused_workspace_bytes(int B, int H, int KVH, int S, int hd);
