@@ -40,12 +40,18 @@ __device__ __forceinline__ float div_levels(float q, float L, float rL) {
     const float e = __fmaf_rn(-L, y, q);
     return __fmaf_rn(e, rL, y);
 }
+// exact int -> float for |q| < 2^22 on the integer and FMA pipes (I2F runs on the quarter-rate conversion pipe,
+// one per element here): 1.5 * 2^23 + q is representable, and subtracting the constant leaves q
+__device__ __forceinline__ float small_int_to_float(int q) {
+    return __fsub_rn(__int_as_float(0x4B400000 + q), 12582912.f);
+}
 // recip: the flavour CUDA ATen computes for `q / 7 * m` -- a tensor divided by a Python scalar is
 // multiplied by fl(1/7) there (BinaryDivTrueKernel.cu), which differs from the IEEE quotient by up
 // to one ulp for some codes; the default is the correctly rounded quotient (CPU ATen).
 __device__ __forceinline__ float decode_field(uint32_t w, int i, int nb, float L, float rL, float m, bool recip) {
     const int q = (int)(w << (32 - nb * (i + 1))) >> (32 - nb);  // sign-extend field i
-    return __fmul_rn(recip ? __fmul_rn((float)q, rL) : div_levels((float)q, L, rL), m);
+    const float qf = small_int_to_float(q);
+    return __fmul_rn(recip ? __fmul_rn(qf, rL) : div_levels(qf, L, rL), m);
 }
 
 struct RowInfo {
