@@ -32,6 +32,7 @@ int pinned_groups() {
 }
 
 bool three_groups(int B, int H, int S, int causal) {
+    if (k2_g3::tile_cols() != 128) return false;   // the wide-tile build switch exists for two groups only
     const int pin = pinned_groups();
     if (pin == 2 || pin == 3) return pin == 3;
     const long long nb = cdiv(S, 128);
