@@ -30,7 +30,14 @@
 
 namespace splitq {
 
-constexpr int kSelThreads = 1024;
+#ifndef SPLITQ_SEL_THREADS
+#define SPLITQ_SEL_THREADS 1024
+#endif
+// 1024 threads per window: with 512 / 256 the kernel takes 13.8 / 15.0 us instead of 10.4 at S = 4096 (ncu) -- the
+// per-key work dominates the per-thread overhead, so more threads per window win as long as they fit one CTA
+constexpr int kSelThreads = SPLITQ_SEL_THREADS;
+constexpr int kSelWarps = kSelThreads / 32;
+static_assert(32 * kSelThreads >= SPLITQ_MAX_SELECT_S, "32 keys per thread must cover the longest window");
 constexpr int kSelMaxWindows = 32;  // windows per launch of the per-window modes (kernel-parameter space)
 
 struct Ladder {
@@ -72,7 +79,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* w
     }
     if (lane == 31) warp_tot[warp] = inc;
     __syncthreads();
-    uint32_t w = warp_tot[lane];  // every warp scans the 32 warp totals itself: no second barrier
+    uint32_t w = lane < kSelWarps ? warp_tot[lane] : 0u;  // every warp scans the warp totals itself: no second barrier
     uint32_t wi = w;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -80,7 +87,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* w
         if (lane >= o) wi += t;
     }
     const uint32_t base = __shfl_sync(0xffffffffu, wi - w, warp);
-    if (total) *total = __shfl_sync(0xffffffffu, wi, 31);
+    if (total) *total = __shfl_sync(0xffffffffu, wi, 31);  // lanes past the last warp carry the running total
     __syncthreads();  // warp_tot may be reused by the caller
     return base + inc - x;
 }
@@ -281,7 +288,7 @@ select_bits_kernel(const float* __restrict__ imp, int S, Ladder lad, const PerWi
         if (tid < 256) {
             uint32_t sum = 0;
 #pragma unroll 8
-            for (int w = 0; w < 32; ++w) sum += sh.whist[w][tid];
+            for (int w = 0; w < kSelWarps; ++w) sum += sh.whist[w][tid];
             sh.hist[0][0][tid] = sum;
         }
         __syncthreads();
