@@ -1266,8 +1266,9 @@ fused_importance_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
 // 128-row block of one head of Q (blockIdx.y < BH) or of K.  Q is multiplied by scaling * log2(e)
 // first, so the tensor-core products are log2-domain logits.  With kFuseQ (the default) the Q blocks are
 // converted by pass 1's loader warps instead -- same arithmetic, same facts, written to the same arrays --
-// and their CTAs here only preset the result slots: this launch then moves 67 MB instead of 300 MB at the
-// bench shape (52 -> 12 us).  Per block the kernel (or the loader) also records
+// and this launch covers the K blocks only: 34 MB instead of 300 MB at the bench shape (52 -> 9 us; the
+// result slots are looked after by the passes' loader warps, see kLoaderPresets).  Per block the kernel (or
+// the loader) also records
 //   bound2: the largest squared row norm (of the values as they enter the products' true magnitude),
 //           from which the passes bound every logit of the launch (FAST epilogue), and
 //   eblk:   e such that the block was multiplied by 2^-e before the fp16 conversion: operands beyond
@@ -1282,7 +1283,7 @@ struct SplitArgs {
     int vecq, veck;
     float cs;                 // scaling * log2(e), folded into Q
     uint2 *q0, *q1, *k0, *k1; // h0 / h1 parts
-    float2* ml;               // result slots preset by the Q blocks: (kSlots, rows) (max, sum) = (-inf, 0)
+    float2* ml;               // result slots, preset here only if the loaders do not (kLoaderPresets): (kSlots, rows) (max, sum) = (-inf, 0)
     float* part_col;          // (kSlots, rows) = 0
     size_t rows;
     float* bound2;            // (BH + BKV) * nb: largest squared row norm per block
